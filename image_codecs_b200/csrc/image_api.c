@@ -1,0 +1,855 @@
+/*
+ * image_api.c -- the stbi_* entry points of include/image_api.h (host C).
+ *
+ * Mirrors the reference's public layer for the JPEG leg:
+ *   stbi_load* / stbi_info*          convert.c:188-266, image_api.c:74-131
+ *   stbi__load_main (JPEG probe)     image_api.c:3-13, :55
+ *   stbi__load_and_postprocess_8bit  convert.c:78-104 (vertical flip)
+ *   stbi__jpeg_test / _info          jpeg.c:2454-2490
+ * and adds the batched decoder.  All pixel work happens on the GPU through
+ * include/jpeg_cuda_abi.h; there is no CPU decode path in this library.
+ */
+#include "../../include/image_api.h"
+
+#include <pthread.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+#include <unistd.h>
+
+#include "../../include/jpeg_cuda_abi.h"
+#include "jpeg_parse.h"
+
+#define API __attribute__((visibility("default")))
+
+/* ---- failure reason, flip flag (names from the reference's missing header) ---- */
+static __thread const char *tl_reason;
+static int g_flip_on_load;
+
+static void *err_null(const char *why)
+{
+	if (why)
+		tl_reason = why;
+	return NULL;
+}
+static int err_zero(const char *why)
+{
+	if (why)
+		tl_reason = why;
+	return 0;
+}
+
+API const char *stbi_failure_reason(void) { return tl_reason; }
+API void stbi_image_free(void *p) { free(p); }
+API void stbi_set_flip_vertically_on_load(int flag) { g_flip_on_load = flag; }
+
+static double now_ms(void)
+{
+	struct timespec ts;
+	clock_gettime(CLOCK_MONOTONIC, &ts);
+	return 1e3 * (double)ts.tv_sec + 1e-6 * (double)ts.tv_nsec;
+}
+
+/* ===================================================================================== */
+/* batch object                                                                          */
+/* ===================================================================================== */
+struct stbi_jpeg_batch
+{
+	stbi_jpeg_batch_params params;
+	jcu_ctx *ctx;
+	int nthreads;
+	int force_generic; /* IMAGE_CODECS_B200_FORCE_GENERIC=1: route every image through the two-pass path (tests) */
+
+	/* prepared batch */
+	int count, req_comp;
+	jp_result *res; /* per image */
+	int cap_res;
+	int *dev_err;
+	int dev_err_valid;
+
+	/* merged descriptors (host) */
+	jcu_image *images;
+	jcu_scan *scans;
+	uint32_t *segs;
+	jcu_huff_spec *huff;
+	size_t cap_images, cap_scans, cap_segs, cap_huff;
+	int n_scans, n_huff, n_waves;
+	uint32_t n_segs;
+
+	unsigned char *slab; /* pinned bitstream staging */
+	size_t slab_cap, slab_bytes;
+	size_t coef_elems, plane_bytes, out_bytes;
+	int need_clear;
+
+	stbi_jpeg_batch_timings tm;
+};
+
+static int online_cpus(void)
+{
+	long n = sysconf(_SC_NPROCESSORS_ONLN);
+	if (n < 1) n = 1;
+	if (n > 64) n = 64;
+	return (int)n;
+}
+
+API int stbi_jpeg_cuda_device_count(void) { return jcu_device_count(); }
+
+API stbi_jpeg_batch *stbi_jpeg_batch_create(const stbi_jpeg_batch_params *params)
+{
+	stbi_jpeg_batch *b;
+	int rc;
+	if (jcu_device_count() < 1)
+		return (stbi_jpeg_batch *)err_null("no cuda device");
+	b = (stbi_jpeg_batch *)calloc(1, sizeof(*b));
+	if (!b)
+		return (stbi_jpeg_batch *)err_null("outofmem");
+	if (params)
+		b->params = *params;
+	b->nthreads = b->params.host_threads > 0 ? b->params.host_threads : online_cpus();
+	if (b->nthreads > 64) b->nthreads = 64;
+	{
+		const char *fg = getenv("IMAGE_CODECS_B200_FORCE_GENERIC");
+		b->force_generic = fg && fg[0] == '1';
+	}
+	rc = jcu_ctx_create(b->params.device, b->params.profile, b->params.entropy_mode, &b->ctx);
+	if (rc != 0)
+	{
+		free(b);
+		return (stbi_jpeg_batch *)err_null("cuda context");
+	}
+	return b;
+}
+
+static void batch_release_results(stbi_jpeg_batch *b)
+{
+	int i;
+	for (i = 0; i < b->count; ++i)
+		jp_result_free(&b->res[i]);
+	b->count = 0;
+}
+
+API void stbi_jpeg_batch_destroy(stbi_jpeg_batch *b)
+{
+	if (!b)
+		return;
+	batch_release_results(b);
+	jcu_ctx_destroy(b->ctx);
+	jcu_host_free(b->slab);
+	free(b->res);
+	free(b->dev_err);
+	free(b->images);
+	free(b->scans);
+	free(b->segs);
+	free(b->huff);
+	free(b);
+}
+
+/* ---- threaded parse: each worker copies its files into the pinned slab and parses them there ---- */
+typedef struct
+{
+	stbi_jpeg_batch *b;
+	const stbi_uc *const *bufs;
+	const int *lens;
+	const size_t *offs;
+	int tid, nthreads;
+} parse_job;
+
+static void *parse_worker(void *arg)
+{
+	parse_job *j = (parse_job *)arg;
+	stbi_jpeg_batch *b = j->b;
+	int i;
+	for (i = j->tid; i < b->count; i += j->nthreads)
+	{
+		jp_result *r = &b->res[i];
+		size_t len = j->lens[i] > 0 ? (size_t)j->lens[i] : 0;
+		unsigned char *dst = b->slab + j->offs[i];
+		jp_result probe;
+		if (len)
+			memcpy(dst, j->bufs[i], len);
+		/* stbi__load_main: JPEG is recognised by SOI alone (image_api.c:10, jpeg.c:2460) */
+		if (!jp_parse(dst, len, b->req_comp, JP_MODE_TYPE, &probe))
+		{
+			memset(r, 0, sizeof(*r));
+			r->ok = 0;
+			r->reason = "unknown image type";
+			continue;
+		}
+		jp_parse(dst, len, b->req_comp, JP_MODE_LOAD, r);
+		if (r->ok)
+		{
+			int k;
+			if (b->force_generic)
+				r->img.path = JCU_PATH_GENERIC;
+			for (k = 0; k < r->img.decode_n; ++k)
+				if (r->img.hmax % r->img.comp[k].h || r->img.vmax % r->img.comp[k].v)
+				{
+					r->ok = 0;
+					r->img.ok = 0;
+					r->reason = "unsupported sampling"; /* the reference reads outside its planes here */
+				}
+		}
+	}
+	return NULL;
+}
+
+static void *grow_buf(void *p, size_t *cap, size_t need, size_t elem)
+{
+	if (need > *cap)
+	{
+		size_t nc = *cap ? *cap : 64;
+		while (nc < need)
+			nc *= 2;
+		p = realloc(p, nc * elem);
+		*cap = nc;
+	}
+	return p;
+}
+
+#define ALIGN_UP(x, a) (((x) + ((a)-1)) & ~((size_t)(a)-1))
+
+/* parse `count` streams into b->res (threaded) and stage them in the pinned slab */
+static int batch_parse(stbi_jpeg_batch *b, const stbi_uc *const *bufs, const int *lens, int count, int req_comp)
+{
+	size_t *offs, total = 0;
+	int i, nt;
+	double t0 = now_ms();
+	batch_release_results(b);
+	if (count > b->cap_res)
+	{
+		b->res = (jp_result *)realloc(b->res, sizeof(jp_result) * (size_t)count);
+		b->dev_err = (int *)realloc(b->dev_err, sizeof(int) * (size_t)count);
+		b->cap_res = count;
+	}
+	memset(b->res, 0, sizeof(jp_result) * (size_t)count);
+	b->count = count;
+	b->req_comp = req_comp;
+	b->dev_err_valid = 0;
+	offs = (size_t *)malloc(sizeof(size_t) * (size_t)(count + 1));
+	for (i = 0; i < count; ++i)
+	{
+		offs[i] = total;
+		total += ALIGN_UP((size_t)(lens[i] > 0 ? lens[i] : 0) + 16, 16);
+	}
+	offs[count] = total;
+	if (total + 64 > b->slab_cap)
+	{
+		jcu_host_free(b->slab);
+		b->slab_cap = total + total / 4 + 4096;
+		b->slab = (unsigned char *)jcu_host_alloc(b->slab_cap);
+		if (!b->slab)
+		{
+			b->slab_cap = 0;
+			free(offs);
+			b->count = 0;
+			return err_zero("outofmem");
+		}
+	}
+	b->slab_bytes = total;
+
+	nt = b->nthreads;
+	if (nt > count) nt = count;
+	if (nt <= 1)
+	{
+		parse_job j = {b, bufs, lens, offs, 0, 1};
+		parse_worker(&j);
+	}
+	else
+	{
+		pthread_t th[64];
+		parse_job jobs[64];
+		for (i = 0; i < nt; ++i)
+		{
+			parse_job j = {b, bufs, lens, offs, i, nt};
+			jobs[i] = j;
+			pthread_create(&th[i], NULL, parse_worker, &jobs[i]);
+		}
+		for (i = 0; i < nt; ++i)
+			pthread_join(th[i], NULL);
+	}
+	if (req_comp < 0 || req_comp > 4)
+		for (i = 0; i < count; ++i)
+			if (!(b->res[i].reason && !strcmp(b->res[i].reason, "unknown image type")))
+			{
+				b->res[i].ok = 0; /* load_jpeg_image checks req_comp before decoding (jpeg.c:2230) */
+				b->res[i].img.ok = 0;
+				b->res[i].reason = "bad req_comp";
+			}
+
+	/* ---- merge into batch-wide descriptor arrays ---- */
+	{
+		size_t ns = 0, ng = 0, nh = 0, coef = 0, planes = 0, outb = 0;
+		double bits = 0, cbytes = 0;
+		int waves = 0, clear = 0;
+		for (i = 0; i < count; ++i)
+			if (b->res[i].ok)
+			{
+				ns += (size_t)b->res[i].nscans;
+				ng += (size_t)b->res[i].nsegs;
+				nh += (size_t)b->res[i].nhuff;
+			}
+		b->images = (jcu_image *)grow_buf(b->images, &b->cap_images, (size_t)count + 1, sizeof(jcu_image));
+		b->scans = (jcu_scan *)grow_buf(b->scans, &b->cap_scans, ns + 1, sizeof(jcu_scan));
+		b->segs = (uint32_t *)grow_buf(b->segs, &b->cap_segs, ng + 1, sizeof(uint32_t));
+		b->huff = (jcu_huff_spec *)grow_buf(b->huff, &b->cap_huff, nh + 1, sizeof(jcu_huff_spec));
+		ns = ng = nh = 0;
+		for (i = 0; i < count; ++i)
+		{
+			jp_result *r = &b->res[i];
+			jcu_image *im = &b->images[i];
+			int k, s;
+			if (!r->ok)
+			{
+				memset(im, 0, sizeof(*im));
+				continue;
+			}
+			*im = r->img;
+			im->data_off = offs[i];
+			im->data_len = (uint32_t)(lens[i] > 0 ? lens[i] : 0);
+			for (k = 0; k < im->ncomp; ++k)
+			{
+				im->comp[k].coef_off = coef;
+				coef += (size_t)im->comp[k].bw * im->comp[k].bh * 64;
+				if (k < im->decode_n)
+				{
+					im->comp[k].plane_off = planes;
+					if (im->path == JCU_PATH_GENERIC)
+						planes += ALIGN_UP((size_t)im->comp[k].bw * im->comp[k].bh * 64, 16);
+				}
+			}
+			im->out_off = outb;
+			outb += ALIGN_UP((size_t)im->n_out * (size_t)im->width * (size_t)im->height, 256);
+			for (s = 0; s < r->nscans; ++s)
+			{
+				jcu_scan sc = r->scans[s];
+				sc.image = i;
+				for (k = 0; k < 4; ++k)
+				{
+					if (sc.dc_spec[k] >= 0) sc.dc_spec[k] += (int32_t)nh;
+					if (sc.ac_spec[k] >= 0) sc.ac_spec[k] += (int32_t)nh;
+				}
+				sc.seg_first += (uint32_t)ng;
+				b->scans[ns++] = sc;
+			}
+			memcpy(b->segs + ng, r->segs, sizeof(uint32_t) * (size_t)r->nsegs);
+			ng += (size_t)r->nsegs;
+			memcpy(b->huff + nh, r->huff, sizeof(jcu_huff_spec) * (size_t)r->nhuff);
+			nh += (size_t)r->nhuff;
+			if (r->nscans > waves) waves = r->nscans;
+			if (im->progressive) clear = 1;
+			bits += r->entropy_bytes * 8.0;
+			cbytes += 128.0 * (double)r->coef_blocks;
+		}
+		b->n_scans = (int)ns;
+		b->n_segs = (uint32_t)ng;
+		b->n_huff = (int)nh;
+		b->n_waves = waves;
+		b->coef_elems = coef;
+		b->plane_bytes = planes;
+		b->out_bytes = outb;
+		b->need_clear = clear;
+		memset(&b->tm, 0, sizeof(b->tm));
+		b->tm.entropy_bits = bits;
+		b->tm.coef_bytes = cbytes;
+		for (i = 0; i < count; ++i)
+			if (b->res[i].ok)
+				b->tm.out_bytes += (double)b->images[i].n_out * b->images[i].width * b->images[i].height;
+	}
+	free(offs);
+	b->tm.parse_ms = (float)(now_ms() - t0);
+	return 1;
+}
+
+static void batch_report(stbi_jpeg_batch *b, int *xs, int *ys, int *comps, int *status)
+{
+	int i;
+	for (i = 0; i < b->count; ++i)
+	{
+		const jp_result *r = &b->res[i];
+		int ok = r->ok && !(b->dev_err_valid && b->dev_err[i]);
+		if (xs) xs[i] = r->ok ? r->img.width : 0;
+		if (ys) ys[i] = r->ok ? r->img.height : 0;
+		if (comps) comps[i] = r->ok ? r->comps_in_file : 0;
+		if (status) status[i] = ok ? STBI_JPEG_OK : STBI_JPEG_FAILED;
+	}
+}
+
+API int stbi_jpeg_batch_prepare(stbi_jpeg_batch *b, const stbi_uc *const *bufs, const int *lens, int count,
+										  int req_comp, int *xs, int *ys, int *comps, int *status)
+{
+	jcu_batch jb;
+	int i, nok = 0;
+	if (!b || count < 0)
+		return -1;
+	if (!batch_parse(b, bufs, lens, count, req_comp))
+		return -1;
+	memset(&jb, 0, sizeof(jb));
+	jb.n_images = count;
+	jb.images = b->images;
+	jb.n_scans = b->n_scans;
+	jb.scans = b->scans;
+	jb.n_segs = b->n_segs;
+	jb.seg_start = b->segs;
+	jb.n_huff = b->n_huff;
+	jb.huff = b->huff;
+	jb.bitstream = b->slab;
+	jb.bitstream_bytes = b->slab_bytes;
+	jb.coef_elems = b->coef_elems;
+	jb.plane_bytes = b->plane_bytes;
+	jb.out_bytes = b->out_bytes;
+	jb.n_waves = b->n_waves;
+	jb.need_coef_clear = b->need_clear;
+	if (jcu_upload(b->ctx, &jb) != 0)
+	{
+		err_zero("outofmem"); /* device allocation or copy failed: see jcu_error_string */
+		return -1;
+	}
+	batch_report(b, xs, ys, comps, status);
+	for (i = 0; i < count; ++i)
+		nok += b->res[i].ok;
+	return nok;
+}
+
+API int stbi_jpeg_batch_run(stbi_jpeg_batch *b)
+{
+	if (!b)
+		return 0;
+	b->dev_err_valid = 0;
+	if (jcu_run(b->ctx) != 0)
+		return err_zero("cuda launch");
+	return 1;
+}
+
+API int stbi_jpeg_batch_sync(stbi_jpeg_batch *b)
+{
+	jcu_timings t;
+	if (!b)
+		return 0;
+	if (jcu_sync(b->ctx) != 0)
+		return err_zero("cuda sync");
+	if (!b->dev_err_valid && b->count > 0)
+	{
+		if (jcu_image_errors(b->ctx, b->dev_err, b->count) != 0)
+			return err_zero("cuda sync");
+		b->dev_err_valid = 1;
+	}
+	if (jcu_get_timings(b->ctx, &t) == 0)
+	{
+		b->tm.h2d_ms = t.h2d_ms;
+		b->tm.entropy_ms = t.entropy_ms;
+		b->tm.idct_ms = t.idct_ms;
+		b->tm.d2h_ms = t.d2h_ms;
+		b->tm.total_ms = t.total_ms;
+		b->tm.launches = t.launches;
+	}
+	return 1;
+}
+
+API int stbi_jpeg_batch_status(stbi_jpeg_batch *b, int image)
+{
+	if (!b || image < 0 || image >= b->count)
+		return STBI_JPEG_FAILED;
+	return (b->res[image].ok && !(b->dev_err_valid && b->dev_err[image])) ? STBI_JPEG_OK : STBI_JPEG_FAILED;
+}
+
+API const char *stbi_jpeg_batch_reason(stbi_jpeg_batch *b, int image)
+{
+	if (!b || image < 0 || image >= b->count)
+		return "bad image index";
+	if (!b->res[image].ok)
+		return b->res[image].reason ? b->res[image].reason : "corrupt jpeg";
+	if (b->dev_err_valid && b->dev_err[image])
+		return "bad huffman code"; /* jpeg.c:317,351,444,499,521 */
+	return NULL;
+}
+
+API void *stbi_jpeg_batch_device_pixels(stbi_jpeg_batch *b, int image, size_t *nbytes)
+{
+	const jcu_image *im;
+	if (!b || image < 0 || image >= b->count || !b->res[image].ok)
+		return NULL;
+	im = &b->images[image];
+	if (nbytes)
+		*nbytes = (size_t)im->n_out * (size_t)im->width * (size_t)im->height;
+	return (unsigned char *)jcu_device_out(b->ctx) + im->out_off;
+}
+
+/* enqueue the download of one image (no sync) */
+static int batch_enqueue_fetch(stbi_jpeg_batch *b, int image, stbi_uc *out, size_t out_cap)
+{
+	const jcu_image *im = &b->images[image];
+	size_t n = (size_t)im->n_out * (size_t)im->width * (size_t)im->height;
+	if (!b->res[image].ok)
+		return 0;
+	if (n > out_cap)
+	{
+		b->res[image].ok = 0;
+		b->res[image].reason = "output too small";
+		return 0;
+	}
+	return jcu_download(b->ctx, im->out_off, n, out) == 0;
+}
+
+static void flip_rows(stbi_uc *px, int w, int h, int n)
+{
+	/* stbi__vertical_flip (convert.c:37) */
+	size_t row = (size_t)w * n;
+	stbi_uc *tmp = (stbi_uc *)malloc(row);
+	int y;
+	for (y = 0; y < h / 2; ++y)
+	{
+		stbi_uc *a = px + row * y, *c = px + row * (size_t)(h - 1 - y);
+		memcpy(tmp, a, row);
+		memcpy(a, c, row);
+		memcpy(c, tmp, row);
+	}
+	free(tmp);
+}
+
+API int stbi_jpeg_batch_fetch(stbi_jpeg_batch *b, int image, stbi_uc *out, size_t out_cap)
+{
+	if (!b || image < 0 || image >= b->count)
+		return 0;
+	if (!batch_enqueue_fetch(b, image, out, out_cap))
+		return err_zero(b->res[image].reason);
+	if (!stbi_jpeg_batch_sync(b))
+		return 0;
+	if (b->dev_err[image])
+		return err_zero("bad huffman code");
+	if (g_flip_on_load)
+		flip_rows(out, b->images[image].width, b->images[image].height, b->images[image].n_out);
+	return 1;
+}
+
+API int stbi_jpeg_batch_fetch_all(stbi_jpeg_batch *b, stbi_uc *const *outs, const size_t *out_caps)
+{
+	int i, n = 0;
+	if (!b)
+		return -1;
+	for (i = 0; i < b->count; ++i)
+		if (b->res[i].ok)
+			batch_enqueue_fetch(b, i, outs[i], out_caps[i]);
+	if (!stbi_jpeg_batch_sync(b))
+		return -1;
+	for (i = 0; i < b->count; ++i)
+		if (stbi_jpeg_batch_status(b, i) == STBI_JPEG_OK)
+		{
+			if (g_flip_on_load)
+				flip_rows(outs[i], b->images[i].width, b->images[i].height, b->images[i].n_out);
+			++n;
+		}
+	return n;
+}
+
+API int stbi_jpeg_batch_timings_get(stbi_jpeg_batch *b, stbi_jpeg_batch_timings *t)
+{
+	if (!b || !t)
+		return 0;
+	*t = b->tm;
+	return 1;
+}
+
+/* ===================================================================================== */
+/* one-call batched decode with host buffers                                             */
+/* ===================================================================================== */
+API int stbi_jpeg_decode_batch(stbi_jpeg_batch *b, const stbi_uc *const *bufs, const int *lens, int count,
+										 int req_comp, stbi_uc *const *outs, const size_t *out_caps, int *xs, int *ys,
+										 int *comps, int *status)
+{
+	int done = 0, nok = 0, chunk;
+	stbi_jpeg_batch_timings acc;
+	if (!b || count < 0)
+		return -1;
+	memset(&acc, 0, sizeof(acc));
+	if (!outs)
+	{
+		/* sizing pass: host parse only */
+		if (!batch_parse(b, bufs, lens, count, req_comp))
+			return -1;
+		batch_report(b, xs, ys, comps, status);
+		for (done = 0; done < count; ++done)
+			nok += b->res[done].ok;
+		return nok;
+	}
+	chunk = b->params.chunk_images > 0 ? b->params.chunk_images : 64;
+	while (done < count)
+	{
+		int n = count - done < chunk ? count - done : chunk, i;
+		if (stbi_jpeg_batch_prepare(b, bufs + done, lens + done, n, req_comp, NULL, NULL, NULL, NULL) < 0)
+			return -1;
+		if (!stbi_jpeg_batch_run(b))
+			return -1;
+		for (i = 0; i < n; ++i)
+			if (b->res[i].ok)
+				batch_enqueue_fetch(b, i, outs[done + i], out_caps[done + i]);
+		if (!stbi_jpeg_batch_sync(b))
+			return -1;
+		batch_report(b, xs ? xs + done : NULL, ys ? ys + done : NULL, comps ? comps + done : NULL,
+						 status ? status + done : NULL);
+		for (i = 0; i < n; ++i)
+			if (stbi_jpeg_batch_status(b, i) == STBI_JPEG_OK)
+			{
+				if (g_flip_on_load)
+					flip_rows(outs[done + i], b->images[i].width, b->images[i].height, b->images[i].n_out);
+				++nok;
+			}
+		acc.parse_ms += b->tm.parse_ms;
+		acc.h2d_ms += b->tm.h2d_ms;
+		acc.entropy_ms += b->tm.entropy_ms;
+		acc.idct_ms += b->tm.idct_ms;
+		acc.d2h_ms += b->tm.d2h_ms;
+		acc.total_ms += b->tm.total_ms;
+		acc.entropy_bits += b->tm.entropy_bits;
+		acc.coef_bytes += b->tm.coef_bytes;
+		acc.out_bytes += b->tm.out_bytes;
+		acc.launches += b->tm.launches;
+		done += n;
+	}
+	b->tm = acc;
+	return nok;
+}
+
+/* ===================================================================================== */
+/* per-image entry points                                                                */
+/* ===================================================================================== */
+static pthread_mutex_t g_default_lock = PTHREAD_MUTEX_INITIALIZER;
+static stbi_jpeg_batch *g_default;
+
+static stbi_uc *load_from_buffer(const stbi_uc *buffer, size_t len, int *x, int *y, int *comp, int req_comp)
+{
+	jp_result probe;
+	stbi_uc *out = NULL;
+	int ilen, xs = 0, ys = 0, cs = 0, st = 0;
+	/* stbi__load_main (image_api.c:10-13,55): only JPEG is recognised, by its SOI */
+	if (!jp_parse(buffer, len, req_comp, JP_MODE_TYPE, &probe))
+		return (stbi_uc *)err_null("unknown image type");
+	if (req_comp < 0 || req_comp > 4)
+		return (stbi_uc *)err_null("bad req_comp"); /* jpeg.c:2230 */
+	if (len > 0x7fffffffu)
+		return (stbi_uc *)err_null("too large");
+	ilen = (int)len;
+
+	pthread_mutex_lock(&g_default_lock);
+	if (!g_default)
+	{
+		stbi_jpeg_batch_params p;
+		const char *dev = getenv("IMAGE_CODECS_B200_DEVICE");
+		memset(&p, 0, sizeof(p));
+		p.device = dev ? atoi(dev) : 0;
+		p.host_threads = 1;
+		g_default = stbi_jpeg_batch_create(&p);
+	}
+	if (g_default)
+	{
+		const stbi_uc *bufs[1];
+		bufs[0] = buffer;
+		if (stbi_jpeg_batch_prepare(g_default, bufs, &ilen, 1, req_comp, &xs, &ys, &cs, &st) == 1 &&
+			 stbi_jpeg_batch_run(g_default))
+		{
+			int n = req_comp ? req_comp : cs;
+			size_t bytes = (size_t)n * (size_t)xs * (size_t)ys;
+			out = (stbi_uc *)malloc(bytes + 1); /* +1 as stbi__malloc_mad3(n, x, y, 1), jpeg.c:2293 */
+			if (!out)
+				err_null("outofmem");
+			else if (!stbi_jpeg_batch_fetch(g_default, 0, out, bytes))
+			{
+				free(out);
+				out = NULL;
+			}
+		}
+		else if (g_default->count == 1 && !g_default->res[0].ok)
+			err_null(g_default->res[0].reason); /* NULL reason: the reference left it unchanged too */
+	}
+	pthread_mutex_unlock(&g_default_lock);
+	if (!out)
+		return NULL;
+	if (x) *x = xs;
+	if (y) *y = ys;
+	if (comp) *comp = cs;
+	return out;
+}
+
+API stbi_uc *stbi_load_from_memory(stbi_uc const *buffer, int len, int *x, int *y, int *comp, int req_comp)
+{
+	return load_from_buffer(buffer, len > 0 ? (size_t)len : 0, x, y, comp, req_comp);
+}
+
+/* the GPU path needs the whole stream: callbacks / FILE* sources are drained into one buffer
+   (the reference instead refills a 128-byte window, common.c:10) */
+static stbi_uc *drain_callbacks(stbi_io_callbacks const *c, void *user, size_t *len)
+{
+	size_t cap = 1 << 16, n = 0;
+	stbi_uc *buf = (stbi_uc *)malloc(cap);
+	while (buf)
+	{
+		int want = (int)(cap - n > 0x40000000u ? 0x40000000u : cap - n);
+		int got = c->read(user, (char *)buf + n, want);
+		if (got <= 0)
+			break;
+		n += (size_t)got;
+		if (n == cap)
+		{
+			stbi_uc *nb = (stbi_uc *)realloc(buf, cap * 2);
+			if (!nb)
+			{
+				free(buf);
+				return NULL;
+			}
+			buf = nb;
+			cap *= 2;
+		}
+	}
+	*len = n;
+	return buf;
+}
+
+API stbi_uc *stbi_load_from_callbacks(stbi_io_callbacks const *clbk, void *user, int *x, int *y, int *comp, int req_comp)
+{
+	size_t len = 0;
+	stbi_uc *buf = drain_callbacks(clbk, user, &len), *r;
+	if (!buf)
+		return (stbi_uc *)err_null("outofmem");
+	r = load_from_buffer(buf, len, x, y, comp, req_comp);
+	free(buf);
+	return r;
+}
+
+static stbi_uc *drain_file(FILE *f, size_t *len)
+{
+	size_t cap = 1 << 16, n = 0;
+	stbi_uc *buf = (stbi_uc *)malloc(cap);
+	while (buf)
+	{
+		size_t got = fread(buf + n, 1, cap - n, f);
+		n += got;
+		if (n < cap)
+			break;
+		{
+			stbi_uc *nb = (stbi_uc *)realloc(buf, cap * 2);
+			if (!nb)
+			{
+				free(buf);
+				return NULL;
+			}
+			buf = nb;
+			cap *= 2;
+		}
+	}
+	*len = n;
+	return buf;
+}
+
+API stbi_uc *stbi_load_from_file(FILE *f, int *x, int *y, int *comp, int req_comp)
+{
+	size_t len = 0;
+	stbi_uc *buf = drain_file(f, &len), *r;
+	if (!buf)
+		return (stbi_uc *)err_null("outofmem");
+	r = load_from_buffer(buf, len, x, y, comp, req_comp);
+	free(buf);
+	return r; /* the file is left at EOF (the reference seeks back to just after the image, convert.c:208) */
+}
+
+API stbi_uc *stbi_load(char const *filename, int *x, int *y, int *comp, int req_comp)
+{
+	FILE *f = fopen(filename, "rb");
+	stbi_uc *r;
+	if (!f)
+		return (stbi_uc *)err_null("can't fopen");
+	r = stbi_load_from_file(f, x, y, comp, req_comp);
+	fclose(f);
+	return r;
+}
+
+/* ---- info: header-only, no GPU (stbi__jpeg_info_raw, jpeg.c:2466) ---- */
+API int stbi_info_from_memory(stbi_uc const *buffer, int len, int *x, int *y, int *comp)
+{
+	jp_result r;
+	if (!jp_parse(buffer, len > 0 ? (size_t)len : 0, 0, JP_MODE_HEADER, &r))
+		return err_zero("unknown image type"); /* stbi__info_main falls through every codec */
+	if (x) *x = r.img.width;
+	if (y) *y = r.img.height;
+	if (comp) *comp = r.comps_in_file;
+	return 1;
+}
+
+API int stbi_info_from_callbacks(stbi_io_callbacks const *c, void *user, int *x, int *y, int *comp)
+{
+	size_t len = 0;
+	stbi_uc *buf = drain_callbacks(c, user, &len);
+	int ok;
+	if (!buf)
+		return err_zero("outofmem");
+	ok = stbi_info_from_memory(buf, len > 0x7fffffffu ? 0x7fffffff : (int)len, x, y, comp);
+	free(buf);
+	return ok;
+}
+
+API int stbi_info_from_file(FILE *f, int *x, int *y, int *comp)
+{
+	long pos = ftell(f);
+	size_t len = 0;
+	stbi_uc *buf = drain_file(f, &len);
+	int ok;
+	if (!buf)
+		return err_zero("outofmem");
+	ok = stbi_info_from_memory(buf, len > 0x7fffffffu ? 0x7fffffff : (int)len, x, y, comp);
+	free(buf);
+	fseek(f, pos, SEEK_SET); /* image_api.c:92 */
+	return ok;
+}
+
+API int stbi_info(char const *filename, int *x, int *y, int *comp)
+{
+	FILE *f = fopen(filename, "rb");
+	int ok;
+	if (!f)
+		return err_zero("can't fopen");
+	ok = stbi_info_from_file(f, x, y, comp);
+	fclose(f);
+	return ok;
+}
+
+API int stbi_is_16_bit_from_memory(stbi_uc const *buffer, int len)
+{
+	(void)buffer;
+	(void)len;
+	return 0;
+}
+
+API int stbi_jpeg_inspect(stbi_uc const *buffer, int len, int req_comp, long long info[16])
+{
+	jp_result r;
+	size_t n = len > 0 ? (size_t)len : 0;
+	int ok;
+	memset(info, 0, sizeof(long long) * 16);
+	if (!jp_parse(buffer, n, req_comp, JP_MODE_TYPE, &r))
+		return err_zero("unknown image type");
+	if (req_comp < 0 || req_comp > 4)
+		return err_zero("bad req_comp");
+	ok = jp_parse(buffer, n, req_comp, JP_MODE_LOAD, &r);
+	if (ok)
+	{
+		info[0] = r.img.width;
+		info[1] = r.img.height;
+		info[2] = r.comps_in_file;
+		info[3] = r.img.progressive;
+		info[4] = r.nscans;
+		info[5] = r.nsegs;
+		info[6] = r.img.path;
+		info[7] = r.img.color_mode;
+		info[8] = r.img.n_out;
+		info[9] = r.img.decode_n;
+		info[10] = r.img.hmax;
+		info[11] = r.img.vmax;
+		info[12] = r.img.mcu_x;
+		info[13] = r.img.mcu_y;
+		info[14] = r.coef_blocks;
+		info[15] = (long long)r.entropy_bytes;
+	}
+	else
+		err_zero(r.reason);
+	jp_result_free(&r);
+	return ok;
+}

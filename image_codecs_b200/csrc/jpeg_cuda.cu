@@ -1,0 +1,437 @@
+/*
+ * jpeg_cuda.cu -- implementation of include/jpeg_cuda_abi.h: device context, uploads, kernel
+ * launches (entropy waves, output stage), downloads.  sm_100a only; no CPU fallback: every
+ * entry point fails with a CUDA error when no device is usable.
+ */
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "../../include/jpeg_cuda_abi.h"
+#include "jpeg_entropy.cuh"
+#include "jpeg_output.cuh"
+#include "jpeg_fused.cuh"
+
+struct DevBuf
+{
+	void *p = nullptr;
+	size_t cap = 0;
+};
+
+struct jcu_ctx
+{
+	int device = 0;
+	int profile = 0;
+	int entropy_mode = 0;
+	cudaStream_t stream = nullptr;
+	cudaEvent_t ev_h2d0 = nullptr, ev_h2d1 = nullptr, ev_run0 = nullptr, ev_ent1 = nullptr, ev_out1 = nullptr, ev_d2h0 = nullptr,
+					ev_d2h1 = nullptr;
+	bool d2h_open = false;
+	DevBuf bits, images, scans, segs, huff, work, coef, planes, out, err, lists;
+	/* batch metadata kept on the host */
+	int n_images = 0, n_waves = 0;
+	size_t coef_elems = 0, out_bytes = 0;
+	bool need_clear = false;
+	std::vector<EntWork> work_h;
+	std::vector<int> wave_off; /* n_waves + 1 offsets into work_h */
+	std::vector<int32_t> list_h; /* image lists per path, concatenated */
+	int list_off[4] = {0, 0, 0, 0}, list_n[4] = {0, 0, 0, 0};
+	int tiles[4] = {0, 0, 0, 0};
+	int path_n[4] = {3, 3, 3, 3};
+	int max_blocks_generic = 0;
+	long long max_pixels_generic = 0;
+	int launches = 0;
+	int force_generic = 0;
+	char errstr[256] = {0};
+};
+
+static int set_err(jcu_ctx *c, cudaError_t e, const char *where)
+{
+	if (c)
+		snprintf(c->errstr, sizeof(c->errstr), "%s: %s", where, cudaGetErrorString(e));
+	return (int)e;
+}
+#define CK(call)                                   \
+	do                                              \
+	{                                               \
+		cudaError_t e__ = (call);                    \
+		if (e__ != cudaSuccess)                      \
+			return set_err(c, e__, #call);            \
+	} while (0)
+
+static cudaError_t ensure(DevBuf &b, size_t bytes)
+{
+	if (bytes <= b.cap)
+		return cudaSuccess;
+	if (b.p)
+		cudaFree(b.p);
+	b.p = nullptr;
+	b.cap = 0;
+	size_t want = bytes + bytes / 8 + 256;
+	cudaError_t e = cudaMalloc(&b.p, want);
+	if (e == cudaSuccess)
+		b.cap = want;
+	return e;
+}
+
+extern "C" int jcu_device_count(void)
+{
+	int n = 0;
+	if (cudaGetDeviceCount(&n) != cudaSuccess)
+	{
+		cudaGetLastError();
+		return 0;
+	}
+	return n;
+}
+
+extern "C" int jcu_ctx_create(int device, int profile, int entropy_mode, jcu_ctx **out)
+{
+	*out = nullptr;
+	cudaError_t e = cudaSetDevice(device);
+	if (e != cudaSuccess)
+		return (int)e;
+	jcu_ctx *c = new jcu_ctx();
+	c->device = device;
+	c->profile = profile;
+	c->entropy_mode = entropy_mode;
+	const char *fg = getenv("IMAGE_CODECS_B200_FORCE_GENERIC");
+	c->force_generic = fg && fg[0] == '1';
+	e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+	if (e != cudaSuccess)
+	{
+		delete c;
+		return (int)e;
+	}
+	cudaEvent_t *evs[] = {&c->ev_h2d0, &c->ev_h2d1, &c->ev_run0, &c->ev_ent1, &c->ev_out1, &c->ev_d2h0, &c->ev_d2h1};
+	for (auto ev : evs)
+		cudaEventCreate(ev);
+	*out = c;
+	return 0;
+}
+
+extern "C" void jcu_ctx_destroy(jcu_ctx *c)
+{
+	if (!c)
+		return;
+	cudaSetDevice(c->device);
+	cudaStreamSynchronize(c->stream);
+	DevBuf *bufs[] = {&c->bits, &c->images, &c->scans, &c->segs, &c->huff, &c->work, &c->coef, &c->planes, &c->out, &c->err, &c->lists};
+	for (auto b : bufs)
+		if (b->p)
+			cudaFree(b->p);
+	cudaEvent_t evs[] = {c->ev_h2d0, c->ev_h2d1, c->ev_run0, c->ev_ent1, c->ev_out1, c->ev_d2h0, c->ev_d2h1};
+	for (auto ev : evs)
+		if (ev)
+			cudaEventDestroy(ev);
+	cudaStreamDestroy(c->stream);
+	delete c;
+}
+
+extern "C" const char *jcu_error_string(jcu_ctx *c) { return c ? c->errstr : "no context"; }
+
+extern "C" void *jcu_host_alloc(size_t bytes)
+{
+	void *p = nullptr;
+	if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess)
+	{
+		cudaGetLastError();
+		return nullptr;
+	}
+	return p;
+}
+extern "C" void jcu_host_free(void *p)
+{
+	if (p)
+		cudaFreeHost(p);
+}
+
+extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
+{
+	CK(cudaSetDevice(c->device));
+	c->n_images = b->n_images;
+	c->n_waves = b->n_waves;
+	c->coef_elems = b->coef_elems;
+	c->out_bytes = b->out_bytes;
+	c->need_clear = b->need_coef_clear != 0;
+	c->d2h_open = false;
+
+	/* ---- per-path image lists and tile numbering ---- */
+	std::vector<jcu_image> imgs(b->images, b->images + b->n_images);
+	std::vector<int32_t> lists[4];
+	c->max_blocks_generic = 0;
+	c->max_pixels_generic = 0;
+	for (int p = 0; p < 4; ++p)
+		c->tiles[p] = 0;
+	for (int i = 0; i < b->n_images; ++i)
+	{
+		jcu_image &im = imgs[i];
+		if (!im.ok)
+			continue;
+		if (c->force_generic)
+			im.path = JCU_PATH_GENERIC;
+		int p = im.path;
+		lists[p].push_back(i);
+		c->path_n[p] = im.n_out;
+		if (p == JCU_PATH_GENERIC)
+		{
+			for (int k = 0; k < im.decode_n; ++k)
+				c->max_blocks_generic = std::max(c->max_blocks_generic, im.comp[k].bw * im.comp[k].bh);
+			c->max_pixels_generic = std::max(c->max_pixels_generic, (long long)im.width * im.height);
+		}
+		else
+		{
+			int tw, th;
+			fused_tile_dims(p, &tw, &th);
+			im.tiles_x = (im.width + tw - 1) / tw;
+			im.tiles_y = (im.height + th - 1) / th;
+			im.tile_first = c->tiles[p];
+			c->tiles[p] += im.tiles_x * im.tiles_y;
+		}
+	}
+	c->list_h.clear();
+	for (int p = 0; p < 4; ++p)
+	{
+		c->list_off[p] = (int)c->list_h.size();
+		c->list_n[p] = (int)lists[p].size();
+		c->list_h.insert(c->list_h.end(), lists[p].begin(), lists[p].end());
+	}
+
+	/* ---- CTA work items per wave: ENT_THREADS segments of one scan each ---- */
+	c->work_h.clear();
+	c->wave_off.assign((size_t)b->n_waves + 1, 0);
+	for (int w = 0; w < b->n_waves; ++w)
+	{
+		c->wave_off[w] = (int)c->work_h.size();
+		for (int s = 0; s < b->n_scans; ++s)
+		{
+			const jcu_scan &sc = b->scans[s];
+			if (sc.wave != w || !imgs[sc.image].ok)
+				continue;
+			for (uint32_t f = 0; f < sc.nseg; f += ENT_THREADS)
+			{
+				EntWork wk;
+				wk.scan = s;
+				wk.seg_first = f;
+				wk.nseg = std::min<uint32_t>(ENT_THREADS, sc.nseg - f);
+				c->work_h.push_back(wk);
+			}
+		}
+	}
+	c->wave_off[b->n_waves] = (int)c->work_h.size();
+
+	/* ---- device buffers ---- */
+	CK(ensure(c->bits, b->bitstream_bytes + 64));
+	CK(ensure(c->images, sizeof(jcu_image) * std::max(1, b->n_images)));
+	CK(ensure(c->scans, sizeof(jcu_scan) * std::max(1, b->n_scans)));
+	CK(ensure(c->segs, sizeof(uint32_t) * std::max<size_t>(1, b->n_segs)));
+	CK(ensure(c->huff, sizeof(jcu_huff_spec) * std::max(1, b->n_huff)));
+	CK(ensure(c->work, sizeof(EntWork) * std::max<size_t>(1, c->work_h.size())));
+	CK(ensure(c->coef, sizeof(int16_t) * b->coef_elems + 256));
+	CK(ensure(c->planes, b->plane_bytes + 256));
+	CK(ensure(c->out, b->out_bytes + 256));
+	CK(ensure(c->err, sizeof(int32_t) * std::max(1, b->n_images)));
+	CK(ensure(c->lists, sizeof(int32_t) * std::max<size_t>(1, c->list_h.size())));
+
+	if (c->profile)
+		CK(cudaEventRecord(c->ev_h2d0, c->stream));
+	if (b->bitstream_bytes)
+		CK(cudaMemcpyAsync(c->bits.p, b->bitstream, b->bitstream_bytes, cudaMemcpyHostToDevice, c->stream));
+	if (b->n_images)
+		CK(cudaMemcpyAsync(c->images.p, imgs.data(), sizeof(jcu_image) * b->n_images, cudaMemcpyHostToDevice, c->stream));
+	if (b->n_scans)
+		CK(cudaMemcpyAsync(c->scans.p, b->scans, sizeof(jcu_scan) * b->n_scans, cudaMemcpyHostToDevice, c->stream));
+	if (b->n_segs)
+		CK(cudaMemcpyAsync(c->segs.p, b->seg_start, sizeof(uint32_t) * b->n_segs, cudaMemcpyHostToDevice, c->stream));
+	if (b->n_huff)
+		CK(cudaMemcpyAsync(c->huff.p, b->huff, sizeof(jcu_huff_spec) * b->n_huff, cudaMemcpyHostToDevice, c->stream));
+	if (!c->work_h.empty())
+		CK(cudaMemcpyAsync(c->work.p, c->work_h.data(), sizeof(EntWork) * c->work_h.size(), cudaMemcpyHostToDevice, c->stream));
+	if (!c->list_h.empty())
+		CK(cudaMemcpyAsync(c->lists.p, c->list_h.data(), sizeof(int32_t) * c->list_h.size(), cudaMemcpyHostToDevice, c->stream));
+	if (c->profile)
+		CK(cudaEventRecord(c->ev_h2d1, c->stream));
+	/* the staging vector `imgs` is pageable: cudaMemcpyAsync has consumed it before returning */
+	return 0;
+}
+
+extern "C" int jcu_run(jcu_ctx *c)
+{
+	CK(cudaSetDevice(c->device));
+	c->launches = 0;
+	cudaStream_t st = c->stream;
+	if (c->profile)
+		CK(cudaEventRecord(c->ev_run0, st)); /* start of the compute region */
+	CK(cudaMemsetAsync(c->err.p, 0, sizeof(int32_t) * std::max(1, c->n_images), st));
+	if (c->need_clear && c->coef_elems)
+		CK(cudaMemsetAsync(c->coef.p, 0, sizeof(int16_t) * c->coef_elems, st));
+
+	const jcu_image *d_img = (const jcu_image *)c->images.p;
+	const int16_t *d_coef = (const int16_t *)c->coef.p;
+	for (int w = 0; w < c->n_waves; ++w)
+	{
+		int n = c->wave_off[w + 1] - c->wave_off[w];
+		if (n <= 0)
+			continue;
+		k_entropy_segments<<<n, ENT_THREADS, 0, st>>>((const EntWork *)c->work.p + c->wave_off[w], (const jcu_scan *)c->scans.p,
+																	 d_img, (const uint32_t *)c->segs.p, (const jcu_huff_spec *)c->huff.p,
+																	 (const uint8_t *)c->bits.p, (int16_t *)c->coef.p, (int32_t *)c->err.p);
+		c->launches++;
+	}
+	CK(cudaGetLastError());
+	if (c->profile)
+		CK(cudaEventRecord(c->ev_ent1, st));
+
+	/* ---- output stage ---- */
+	if (c->list_n[JCU_PATH_GENERIC] > 0)
+	{
+		const int32_t *lst = (const int32_t *)c->lists.p + c->list_off[JCU_PATH_GENERIC];
+		dim3 g1((unsigned)((c->max_blocks_generic + 127) / 128), (unsigned)c->list_n[JCU_PATH_GENERIC], 4);
+		k_generic_idct<<<g1, 128, 0, st>>>(lst, d_img, d_coef, (uint8_t *)c->planes.p);
+		long long want = (c->max_pixels_generic + 255) / 256;
+		dim3 g2((unsigned)std::min<long long>(std::max<long long>(want, 1), 65535), (unsigned)c->list_n[JCU_PATH_GENERIC], 1);
+		k_generic_color<<<g2, 256, 0, st>>>(lst, d_img, (const uint8_t *)c->planes.p, (uint8_t *)c->out.p);
+		c->launches += 2;
+	}
+	for (int p = 1; p < 4; ++p)
+		if (c->list_n[p] > 0)
+		{
+			const int32_t *lst = (const int32_t *)c->lists.p + c->list_off[p];
+			cudaError_t e = fused_launch(p, c->tiles[p], lst, c->list_n[p], d_img, d_coef, (uint8_t *)c->out.p, st, c->path_n[p]);
+			if (e != cudaSuccess)
+				return set_err(c, e, "fused_launch");
+			c->launches++;
+		}
+	CK(cudaGetLastError());
+	if (c->profile)
+		CK(cudaEventRecord(c->ev_out1, st));
+	return 0;
+}
+
+extern "C" int jcu_sync(jcu_ctx *c)
+{
+	CK(cudaSetDevice(c->device));
+	if (c->profile && c->d2h_open)
+	{
+		CK(cudaEventRecord(c->ev_d2h1, c->stream));
+	}
+	CK(cudaStreamSynchronize(c->stream));
+	return 0;
+}
+
+extern "C" int jcu_download(jcu_ctx *c, size_t off, size_t bytes, void *dst)
+{
+	CK(cudaSetDevice(c->device));
+	if (c->profile && !c->d2h_open)
+	{
+		CK(cudaEventRecord(c->ev_d2h0, c->stream));
+		c->d2h_open = true;
+	}
+	CK(cudaMemcpyAsync(dst, (const uint8_t *)c->out.p + off, bytes, cudaMemcpyDeviceToHost, c->stream));
+	return 0;
+}
+
+extern "C" int jcu_image_errors(jcu_ctx *c, int32_t *errs, int n)
+{
+	CK(cudaSetDevice(c->device));
+	CK(cudaMemcpyAsync(errs, c->err.p, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaStreamSynchronize(c->stream));
+	return 0;
+}
+
+extern "C" void *jcu_device_out(jcu_ctx *c) { return c->out.p; }
+
+extern "C" int jcu_get_timings(jcu_ctx *c, jcu_timings *t)
+{
+	memset(t, 0, sizeof(*t));
+	t->launches = c->launches;
+	if (!c->profile)
+		return 0;
+	CK(cudaSetDevice(c->device));
+	cudaEventElapsedTime(&t->h2d_ms, c->ev_h2d0, c->ev_h2d1);
+	cudaEventElapsedTime(&t->entropy_ms, c->ev_run0, c->ev_ent1);
+	cudaEventElapsedTime(&t->idct_ms, c->ev_ent1, c->ev_out1);
+	cudaEventElapsedTime(&t->total_ms, c->ev_run0, c->ev_out1);
+	if (c->d2h_open)
+		cudaEventElapsedTime(&t->d2h_ms, c->ev_d2h0, c->ev_d2h1);
+	cudaGetLastError();
+	return 0;
+}
+
+/* ---- stage-level test entry points ---- */
+__global__ void k_test_idct(const int16_t *coef, const uint16_t *qt, int n, uint8_t *out)
+{
+	int b = blockIdx.x * blockDim.x + threadIdx.x;
+	if (b >= n)
+		return;
+	int v[64];
+	uint32_t rows[16];
+	load_dequant(coef + (size_t)b * 64, qt, v);
+	idct_block_regs(v, rows);
+	uint32_t *o = reinterpret_cast<uint32_t *>(out + (size_t)b * 64);
+	for (int i = 0; i < 16; ++i)
+		o[i] = rows[i];
+}
+__global__ void k_test_ycbcr(const uint8_t *y, const uint8_t *cb, const uint8_t *cr, int n, int step, uint8_t *out)
+{
+	int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n)
+		return;
+	int r, g, b;
+	ycbcr_to_rgb(y[i], cb[i], cr[i], r, g, b);
+	out[(size_t)i * step] = (uint8_t)r;
+	out[(size_t)i * step + 1] = (uint8_t)g;
+	out[(size_t)i * step + 2] = (uint8_t)b;
+	if (step == 4)
+		out[(size_t)i * step + 3] = 255;
+}
+
+extern "C" int jcu_test_idct_blocks(jcu_ctx *c, const int16_t *coef, const uint16_t *qt, int nblocks, uint8_t *out64)
+{
+	CK(cudaSetDevice(c->device));
+	int16_t *d_c;
+	uint16_t *d_q;
+	uint8_t *d_o;
+	CK(cudaMalloc(&d_c, (size_t)nblocks * 128));
+	CK(cudaMalloc(&d_q, 128));
+	CK(cudaMalloc(&d_o, (size_t)nblocks * 64));
+	CK(cudaMemcpy(d_c, coef, (size_t)nblocks * 128, cudaMemcpyHostToDevice));
+	CK(cudaMemcpy(d_q, qt, 128, cudaMemcpyHostToDevice));
+	k_test_idct<<<(nblocks + 63) / 64, 64, 0, c->stream>>>(d_c, d_q, nblocks, d_o);
+	CK(cudaStreamSynchronize(c->stream));
+	CK(cudaMemcpy(out64, d_o, (size_t)nblocks * 64, cudaMemcpyDeviceToHost));
+	cudaFree(d_c);
+	cudaFree(d_q);
+	cudaFree(d_o);
+	return 0;
+}
+
+extern "C" int jcu_test_ycbcr(jcu_ctx *c, const uint8_t *y, const uint8_t *cb, const uint8_t *cr, int n, int step, uint8_t *out)
+{
+	CK(cudaSetDevice(c->device));
+	uint8_t *d_in, *d_o;
+	CK(cudaMalloc(&d_in, (size_t)n * 3));
+	CK(cudaMalloc(&d_o, (size_t)n * step));
+	CK(cudaMemcpy(d_in, y, n, cudaMemcpyHostToDevice));
+	CK(cudaMemcpy(d_in + n, cb, n, cudaMemcpyHostToDevice));
+	CK(cudaMemcpy(d_in + 2 * (size_t)n, cr, n, cudaMemcpyHostToDevice));
+	k_test_ycbcr<<<(n + 255) / 256, 256, 0, c->stream>>>(d_in, d_in + n, d_in + 2 * (size_t)n, n, step, d_o);
+	CK(cudaStreamSynchronize(c->stream));
+	CK(cudaMemcpy(out, d_o, (size_t)n * step, cudaMemcpyDeviceToHost));
+	cudaFree(d_in);
+	cudaFree(d_o);
+	return 0;
+}
+
+extern "C" int jcu_read_coefs(jcu_ctx *c, size_t elem_off, size_t elems, int16_t *dst)
+{
+	CK(cudaSetDevice(c->device));
+	CK(cudaMemcpyAsync(dst, (const int16_t *)c->coef.p + elem_off, elems * sizeof(int16_t), cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaStreamSynchronize(c->stream));
+	return 0;
+}

@@ -1,0 +1,515 @@
+/*
+ * jpeg_entropy.cuh -- Huffman entropy decode on the device (sm_100a).
+ *
+ * Replaces, for every scan of every image in a batch at once, the reference's serial
+ * stbi__parse_entropy_coded_data (jpeg.c:1155) and its block decoders:
+ *   baseline              stbi__jpeg_decode_block          jpeg.c:308
+ *   progressive DC        stbi__jpeg_decode_block_prog_dc  jpeg.c:372
+ *   progressive AC        stbi__jpeg_decode_block_prog_ac  jpeg.c:406
+ * built on a device bit reader with the byte-stuffing rules of stbi__grow_buffer_unsafe
+ * (jpeg.c:167) and canonical Huffman decode equivalent to stbi__jpeg_huff_decode (jpeg.c:193).
+ *
+ * Parallel decomposition (not in the reference, which is strictly serial):
+ *   - one CTA works on up to ENT_THREADS restart segments of ONE scan of ONE image, so the
+ *     scan's Huffman lookup tables are built once per CTA in shared memory from the raw DHT
+ *     contents;
+ *   - one thread decodes one restart segment (stbi__jpeg_reset, jpeg.c:1142, shows the state
+ *     that resets at a restart: bit buffer, DC predictors, eob_run -- so segments are
+ *     independent).  Streams without restart markers have one segment per scan here; the
+ *     self-synchronising decoder (jpeg_selfsync.cuh) splits those further.
+ *
+ * Coefficients are written RAW (not dequantised), int16, natural (row-major) order, one
+ * 128-byte block at a time: DC already de-predicted.  Truncation to 16 bits matches the
+ * reference's (short) casts because the later (short)(c*q) only depends on c mod 2^16.
+ */
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/jpeg_cuda_abi.h"
+
+#define ENT_THREADS 128
+#define ENT_LUT_BITS 10
+#define ENT_SLOT_WORDS 36 /* 64 int16 = 32 words, +4 pad words: 16B chunks of the 8 lanes of a phase hit distinct banks */
+
+/* zig-zag index -> natural index, with 16 trailing 63s like the reference's padded table
+   (jpeg.c:303-305) so corrupt runs cannot index outside the block */
+__constant__ uint8_t c_natural[80] = {0,	1,	 8,  16, 9,	 2,  3,	10, 17, 24, 32, 25, 18, 11, 4,  5,	12, 19, 26, 33,
+												  40, 48, 41, 34, 27, 20, 13, 6,	 7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36,
+												  29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54,
+												  47, 55, 62, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63};
+
+struct HuffLut
+{
+	uint16_t fast[1 << ENT_LUT_BITS]; /* (length << 8) | symbol, 0 = code longer than ENT_LUT_BITS */
+	uint32_t limit[18];					 /* limit[l] = (first code of length l + count) << (16 - l); [17] = ~0 */
+	int32_t base[17];						 /* symbol index = base[l] + code */
+	uint8_t vals[256];
+};
+
+/* Build one lookup table from raw DHT contents.  Called by all threads of the CTA. */
+__device__ __forceinline__ void hufflut_build(HuffLut *L, const jcu_huff_spec *spec, int tid, int nthreads)
+{
+	__shared__ uint32_t s_first[17]; /* first code of each length */
+	__shared__ uint32_t s_count[17];
+	__shared__ int32_t s_valptr[17];
+	if (tid == 0)
+	{
+		uint32_t code = 0;
+		int k = 0;
+		for (int l = 1; l <= 16; ++l)
+		{
+			uint32_t n = spec->bits[l - 1];
+			s_first[l] = code;
+			s_count[l] = n;
+			s_valptr[l] = k;
+			L->base[l] = k - (int)code;
+			code += n;
+			k += (int)n;
+			L->limit[l] = code << (16 - l);
+			code <<= 1;
+		}
+		L->limit[17] = 0xffffffffu;
+	}
+	for (int i = tid; i < 256; i += nthreads)
+		L->vals[i] = spec->vals[i];
+	__syncthreads();
+	for (int e = tid; e < (1 << ENT_LUT_BITS); e += nthreads)
+	{
+		uint16_t entry = 0;
+		for (int l = 1; l <= ENT_LUT_BITS; ++l)
+		{
+			uint32_t code = (uint32_t)e >> (ENT_LUT_BITS - l);
+			uint32_t rel = code - s_first[l];
+			if (code >= s_first[l] && rel < s_count[l])
+			{
+				entry = (uint16_t)((l << 8) | spec->vals[s_valptr[l] + (int)rel]);
+				break;
+			}
+		}
+		L->fast[e] = entry;
+	}
+	__syncthreads();
+}
+
+/* MSB-first bit reader over one restart segment */
+struct BitReader
+{
+	const uint8_t *p;
+	const uint8_t *end;
+	uint64_t buf; /* valid bits are the top nbits */
+	int nbits;
+	int stopped; /* a marker was reached: feed zero bits from now on (jpeg.c:171-183) */
+};
+
+__device__ __forceinline__ void br_init(BitReader &br, const uint8_t *p, const uint8_t *end)
+{
+	br.p = p;
+	br.end = end;
+	br.buf = 0;
+	br.nbits = 0;
+	br.stopped = 0;
+}
+
+/* top up to more than 56 bits, one byte at a time, with the reference's stuffing rules */
+__device__ __forceinline__ void br_refill(BitReader &br)
+{
+	while (br.nbits <= 56)
+	{
+		uint32_t b = 0;
+		if (!br.stopped && br.p < br.end)
+		{
+			b = *br.p++;
+			if (b == 0xff)
+			{
+				const uint8_t *q = br.p;
+				uint32_t c = q < br.end ? *q : 0u;
+				while (c == 0xff)
+				{
+					++q;
+					c = q < br.end ? *q : 0u;
+				}
+				if (c == 0)
+					br.p = q < br.end ? q + 1 : br.end; /* FF 00: a literal FF */
+				else
+				{
+					br.stopped = 1; /* marker: stop consuming, the FF is not data */
+					b = 0;
+				}
+			}
+		}
+		br.buf |= (uint64_t)b << (56 - br.nbits);
+		br.nbits += 8;
+	}
+}
+
+__device__ __forceinline__ uint32_t br_peek(const BitReader &br, int n) /* 1 <= n <= 32 */
+{
+	return (uint32_t)(br.buf >> (64 - n));
+}
+__device__ __forceinline__ void br_skip(BitReader &br, int n)
+{
+	br.buf <<= n;
+	br.nbits -= n;
+}
+__device__ __forceinline__ uint32_t br_bits(BitReader &br, int n) /* 0 <= n <= 16 */
+{
+	if (n == 0)
+		return 0;
+	if (br.nbits < n)
+		br_refill(br);
+	uint32_t v = br_peek(br, n);
+	br_skip(br, n);
+	return v;
+}
+
+/* returns the symbol, or -1 when no code matches (reference: "bad huffman code") */
+__device__ __forceinline__ int huff_decode(BitReader &br, const HuffLut *L)
+{
+	if (br.nbits < 16)
+		br_refill(br);
+	uint32_t top = br_peek(br, 16);
+	uint32_t e = L->fast[top >> (16 - ENT_LUT_BITS)];
+	if (e)
+	{
+		br_skip(br, (int)(e >> 8));
+		return (int)(e & 255u);
+	}
+	int l = ENT_LUT_BITS + 1;
+	while (top >= L->limit[l])
+		++l;
+	if (l > 16)
+	{
+		br_skip(br, 16);
+		return -1;
+	}
+	int idx = L->base[l] + (int)(top >> (16 - l));
+	br_skip(br, l);
+	return (int)L->vals[idx & 255];
+}
+
+/* receive n bits and sign-extend JPEG-style (stbi__extend_receive, jpeg.c:250) */
+__device__ __forceinline__ int receive_extend(BitReader &br, int n)
+{
+	if (n == 0 || n > 16)
+		return 0;
+	int v = (int)br_bits(br, n);
+	if (v < (1 << (n - 1)))
+		v += (int)(0xffffffffu << n) + 1;
+	return v;
+}
+
+struct ScanShared
+{
+	HuffLut lut[8];  /* [0..3] DC per scan-component slot, [4..7] AC */
+	int lut_of_dc[4]; /* slot -> lut index (slots sharing a spec share a table) */
+	int lut_of_ac[4];
+};
+
+/* one CTA work item */
+struct EntWork
+{
+	int32_t scan;
+	uint32_t seg_first; /* index (within the scan) of this CTA's first segment */
+	uint32_t nseg;
+};
+
+/* ---- progressive block decoders operating directly on the coefficient slab ---- */
+
+__device__ __forceinline__ int prog_ac_first(BitReader &br, const HuffLut *L, int16_t *blk, int ss, int se, int al,
+															int &eob_run)
+{
+	if (eob_run)
+	{
+		--eob_run;
+		return 1;
+	}
+	int k = ss;
+	do
+	{
+		int rs = huff_decode(br, L);
+		if (rs < 0)
+			return 0;
+		int s = rs & 15, r = rs >> 4;
+		if (s == 0)
+		{
+			if (r < 15)
+			{
+				eob_run = 1 << r;
+				if (r)
+					eob_run += (int)br_bits(br, r);
+				--eob_run;
+				break;
+			}
+			k += 16;
+		}
+		else
+		{
+			k += r;
+			int zig = c_natural[k < 79 ? k : 79];
+			++k;
+			blk[zig] = (int16_t)(receive_extend(br, s) * (1 << al));
+		}
+	} while (k <= se);
+	return 1;
+}
+
+__device__ __forceinline__ void refine_one(int16_t *p, int bit)
+{
+	int v = *p;
+	if ((v & bit) == 0)
+		*p = (int16_t)(v > 0 ? v + bit : v - bit);
+}
+
+__device__ __forceinline__ int prog_ac_refine(BitReader &br, const HuffLut *L, int16_t *blk, int ss, int se, int al,
+															 int &eob_run)
+{
+	const int bit = (int)(int16_t)(1 << al);
+	if (eob_run)
+	{
+		--eob_run;
+		for (int k = ss; k <= se; ++k)
+		{
+			int16_t *p = &blk[c_natural[k]];
+			if (*p != 0)
+				if (br_bits(br, 1))
+					refine_one(p, bit);
+		}
+		return 1;
+	}
+	int k = ss;
+	do
+	{
+		int rs = huff_decode(br, L);
+		if (rs < 0)
+			return 0;
+		int s = rs & 15, r = rs >> 4;
+		if (s == 0)
+		{
+			if (r < 15)
+			{
+				eob_run = (1 << r) - 1;
+				if (r)
+					eob_run += (int)br_bits(br, r);
+				r = 64; /* force end of block */
+			}
+		}
+		else
+		{
+			if (s != 1)
+				return 0;
+			s = br_bits(br, 1) ? bit : -bit;
+		}
+		while (k <= se)
+		{
+			int16_t *p = &blk[c_natural[k++]];
+			if (*p != 0)
+			{
+				if (br_bits(br, 1))
+					refine_one(p, bit);
+			}
+			else
+			{
+				if (r == 0)
+				{
+					*p = (int16_t)s;
+					break;
+				}
+				--r;
+			}
+		}
+	} while (k <= se);
+	return 1;
+}
+
+/* baseline block into a zeroed shared-memory slot (natural order, raw values) */
+__device__ __forceinline__ int baseline_block(BitReader &br, const HuffLut *Ldc, const HuffLut *Lac, int16_t *slot,
+															 int &dc_pred)
+{
+	int t = huff_decode(br, Ldc);
+	if (t < 0)
+		return 0;
+	dc_pred += receive_extend(br, t);
+	slot[0] = (int16_t)dc_pred;
+	int k = 1;
+	do
+	{
+		int rs = huff_decode(br, Lac);
+		if (rs < 0)
+			return 0;
+		int s = rs & 15, r = rs >> 4;
+		if (s == 0)
+		{
+			if (rs != 0xf0)
+				break;
+			k += 16;
+		}
+		else
+		{
+			k += r;
+			int zig = c_natural[k];
+			++k;
+			slot[zig] = (int16_t)receive_extend(br, s);
+		}
+	} while (k < 64);
+	return 1;
+}
+
+/*
+ * Entropy-decode kernel: grid = CTA work items of one wave (one scan ordinal across the batch).
+ * Thread t of a CTA decodes restart segment (work.seg_first + t) of the CTA's scan.
+ */
+__global__ void __launch_bounds__(ENT_THREADS)
+k_entropy_segments(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans,
+						 const jcu_image *__restrict__ images, const uint32_t *__restrict__ seg_start,
+						 const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ bitstream,
+						 int16_t *__restrict__ coef, int32_t *__restrict__ img_err)
+{
+	__shared__ ScanShared sh;
+	__shared__ __align__(16) uint32_t s_slots[ENT_THREADS * ENT_SLOT_WORDS];
+
+	const int tid = threadIdx.x;
+	const EntWork w = work[blockIdx.x];
+	const jcu_scan *sc = &scans[w.scan];
+	const jcu_image *im = &images[sc->image];
+	const int kind = sc->kind, ncs = sc->ncomp;
+
+	/* ---- lookup tables, once per CTA ---- */
+	for (int i = 0; i < ncs; ++i)
+	{
+		if (sc->dc_spec[i] >= 0)
+		{
+			int alias = -1;
+			for (int j = 0; j < i; ++j)
+				if (sc->dc_spec[j] == sc->dc_spec[i])
+					alias = sh.lut_of_dc[j];
+			if (alias < 0)
+			{
+				hufflut_build(&sh.lut[i], &huff[sc->dc_spec[i]], tid, ENT_THREADS);
+				alias = i;
+			}
+			if (tid == 0)
+				sh.lut_of_dc[i] = alias;
+		}
+		if (sc->ac_spec[i] >= 0)
+		{
+			int alias = -1;
+			for (int j = 0; j < i; ++j)
+				if (sc->ac_spec[j] == sc->ac_spec[i])
+					alias = sh.lut_of_ac[j];
+			if (alias < 0)
+			{
+				hufflut_build(&sh.lut[4 + i], &huff[sc->ac_spec[i]], tid, ENT_THREADS);
+				alias = 4 + i;
+			}
+			if (tid == 0)
+				sh.lut_of_ac[i] = alias;
+		}
+		__syncthreads();
+	}
+
+	/* ---- this thread's segment ---- */
+	const bool active = (uint32_t)tid < w.nseg;
+	const uint32_t seg = w.seg_first + (uint32_t)tid;
+	const int ri = sc->restart_interval, total = sc->total_units, upr = sc->units_per_row;
+	const int n_units = ri ? ri : total;
+	const int u0 = ri ? (int)seg * ri : 0;
+	const int u1 = ri ? min(u0 + ri, total) : total;
+
+	BitReader br;
+	{
+		const uint8_t *file = bitstream + im->data_off;
+		uint32_t off = active ? seg_start[sc->seg_first + seg] : 0u;
+		br_init(br, file + off, file + im->data_len);
+	}
+	int dc_pred[4] = {0, 0, 0, 0};
+	int eob_run = 0;
+	bool failed = false;
+
+	uint32_t *slot_w = &s_slots[tid * ENT_SLOT_WORDS];
+	int16_t *slot = reinterpret_cast<int16_t *>(slot_w);
+	if (kind == JCU_SCAN_BASELINE)
+	{
+#pragma unroll
+		for (int i = 0; i < 32; ++i)
+			slot_w[i] = 0u;
+	}
+
+	const int ss = sc->ss, se = sc->se, al = sc->al;
+
+	for (int uu = 0; uu < n_units; ++uu)
+	{
+		const int u = u0 + uu;
+		const bool live = active && u < u1 && !failed;
+		const int ux = u % upr, uy = u / upr;
+		for (int i = 0; i < ncs; ++i)
+		{
+			const jcu_comp *cp = &im->comp[sc->comp[i]];
+			const int bh_n = ncs == 1 ? 1 : cp->v, bw_n = ncs == 1 ? 1 : cp->h;
+			const HuffLut *Ldc = &sh.lut[sh.lut_of_dc[i] & 7];
+			const HuffLut *Lac = &sh.lut[sh.lut_of_ac[i] & 7];
+			for (int y = 0; y < bh_n; ++y)
+				for (int x = 0; x < bw_n; ++x)
+				{
+					const int bx = ux * bw_n + x, by = uy * bh_n + y;
+					int16_t *blk = coef + cp->coef_off + ((size_t)by * cp->bw + bx) * 64;
+					if (kind == JCU_SCAN_BASELINE)
+					{
+						bool ok = false;
+						if (live && !failed)
+						{
+							ok = baseline_block(br, Ldc, Lac, slot, dc_pred[i]) != 0;
+							if (!ok)
+								failed = true;
+						}
+						__syncwarp();
+						if (live)
+						{
+							const uint4 *s4 = reinterpret_cast<const uint4 *>(slot_w);
+							uint4 *d4 = reinterpret_cast<uint4 *>(blk);
+#pragma unroll
+							for (int q = 0; q < 8; ++q)
+							{
+								uint4 v = s4[q];
+								if (ok)
+									d4[q] = v;
+								reinterpret_cast<uint4 *>(slot_w)[q] = make_uint4(0u, 0u, 0u, 0u);
+							}
+						}
+					}
+					else if (live && !failed)
+					{
+						int ok = 1;
+						if (kind == JCU_SCAN_PROG_DC_FIRST)
+						{
+							uint4 *d4 = reinterpret_cast<uint4 *>(blk);
+#pragma unroll
+							for (int q = 0; q < 8; ++q)
+								d4[q] = make_uint4(0u, 0u, 0u, 0u);
+							int t = huff_decode(br, Ldc);
+							if (t < 0)
+								ok = 0;
+							else
+							{
+								dc_pred[i] += receive_extend(br, t);
+								blk[0] = (int16_t)(dc_pred[i] * (1 << al));
+							}
+						}
+						else if (kind == JCU_SCAN_PROG_DC_REFINE)
+						{
+							if (br_bits(br, 1))
+								blk[0] = (int16_t)(blk[0] + (int16_t)(1 << al));
+						}
+						else if (kind == JCU_SCAN_PROG_AC_FIRST)
+							ok = prog_ac_first(br, Lac, blk, ss, se, al, eob_run);
+						else
+							ok = prog_ac_refine(br, Lac, blk, ss, se, al, eob_run);
+						if (!ok)
+							failed = true;
+					}
+				}
+		}
+	}
+	if (failed)
+		atomicOr(&img_err[sc->image], 1);
+}

@@ -1,0 +1,172 @@
+/*
+ * jpeg_cuda_abi.h -- the thin C-ABI between the host C code (marker parser, stbi_* entry points,
+ * batch loader) and the hand-written sm_100a CUDA kernels.  extern "C", plain pointers and sizes,
+ * no C++ or torch types.  This is the boundary that replaces, inside the reference,
+ *
+ *   stbi__parse_entropy_coded_data   codec/jpeg.c:1155   (entropy decode of one scan)
+ *   stbi__jpeg_finish                codec/jpeg.c:1326   (progressive dequant + IDCT)
+ *   the row loop of load_jpeg_image  codec/jpeg.c:2301   (upsample + colour + pack)
+ *
+ * i.e. everything below stbi__decode_jpeg_image's marker loop.  The host keeps the marker
+ * parser (jpeg.c:1349-1756) and hands the device: file bytes, raw DHT/DQT contents, per-scan
+ * parameters and the byte offsets of restart segments.
+ */
+#ifndef JPEG_CUDA_ABI_H
+#define JPEG_CUDA_ABI_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* colour/pack modes of the output stage (cases of load_jpeg_image, jpeg.c:2320-2431) */
+enum
+{
+	JCU_CM_Y = 0,			/* replicate / copy component 0            jpeg.c:2373-2378, 2418-2430 */
+	JCU_CM_YCBCR = 1,		/* YCbCr -> RGB                            jpeg.c:2338, 2369 */
+	JCU_CM_RGB = 2,		/* components are R,G,B: pass through      jpeg.c:2325-2335 */
+	JCU_CM_CMYK = 3,		/* CMYK -> RGB via blinn(c, k)             jpeg.c:2343-2353 */
+	JCU_CM_YCCK = 4,		/* YCCK -> RGB -> blinn(255-c, k)          jpeg.c:2355-2366 */
+	JCU_CM_RGB_LUMA = 5, /* compute_y(r,g,b)                        jpeg.c:2382-2394 */
+	JCU_CM_CMYK_LUMA = 6, /* compute_y of CMYK->RGB                 jpeg.c:2396-2408 */
+	JCU_CM_YCCK_LUMA = 7	 /* blinn(255 - Y, K)                      jpeg.c:2409-2417 */
+};
+
+/* scan kinds (the four block decoders of jpeg.c:308-558) */
+enum
+{
+	JCU_SCAN_BASELINE = 0,	  /* stbi__jpeg_decode_block            jpeg.c:308 */
+	JCU_SCAN_PROG_DC_FIRST = 1, /* ..._prog_dc, succ_high == 0         jpeg.c:382 */
+	JCU_SCAN_PROG_DC_REFINE = 2, /* ..._prog_dc, succ_high != 0        jpeg.c:395 */
+	JCU_SCAN_PROG_AC_FIRST = 3, /* ..._prog_ac, succ_high == 0         jpeg.c:412 */
+	JCU_SCAN_PROG_AC_REFINE = 4 /* ..._prog_ac, succ_high != 0         jpeg.c:468 */
+};
+
+/* output-stage kernel selection (decided on the host from the frame header) */
+enum
+{
+	JCU_PATH_GENERIC = 0, /* two-pass: IDCT to planes, then resample+colour (any H,V, any mode) */
+	JCU_PATH_FUSED_420 = 1, /* fused tile kernel, 3 comps 2x2/1x1/1x1, YCbCr -> RGB/RGBA */
+	JCU_PATH_FUSED_444 = 2, /* fused tile kernel, 3 comps 1x1, YCbCr -> RGB/RGBA */
+	JCU_PATH_FUSED_GRAY = 3 /* fused tile kernel, component 0 only -> 1..4 channels */
+};
+
+/* raw DHT contents (jpeg.c:1381-1416): the device builds its own lookup tables from these */
+typedef struct
+{
+	uint8_t bits[16];	 /* number of codes of length 1..16 */
+	uint8_t vals[256]; /* symbols in code order */
+} jcu_huff_spec;
+
+typedef struct
+{
+	int32_t h, v;		 /* sampling factors */
+	int32_t hs, vs;	 /* expansion factors hmax/h, vmax/v (jpeg.c:2273) */
+	int32_t cx, cy;	 /* effective size in samples (jpeg.c:1627) */
+	int32_t bw, bh;	 /* blocks incl. MCU padding = w2/8, h2/8 (jpeg.c:1636) */
+	int32_t cbw, cbh;	 /* blocks covering cx, cy (non-interleaved scans, jpeg.c:1169) */
+	int32_t w_lores;	 /* (img_x + hs - 1) / hs (jpeg.c:2276) */
+	int32_t pad;
+	uint64_t coef_off; /* first coefficient (int16 index) of this component in the coefficient slab */
+	uint64_t plane_off; /* byte offset of this component's sample plane (generic path only) */
+} jcu_comp;
+
+typedef struct
+{
+	int32_t width, height;
+	int32_t ncomp;		  /* components in the frame */
+	int32_t decode_n;	  /* components the output stage needs (jpeg.c:2246) */
+	int32_t n_out;		  /* output channels */
+	int32_t color_mode; /* JCU_CM_* */
+	int32_t path;		  /* JCU_PATH_* */
+	int32_t hmax, vmax, mcu_x, mcu_y;
+	int32_t progressive;
+	int32_t ok;			  /* host verdict: 0 = do not decode (parse failed) */
+	int32_t tile_first; /* first tile index of this image in its path's launch */
+	int32_t tiles_x, tiles_y;
+	jcu_comp comp[4];
+	uint16_t qt[4][64]; /* per COMPONENT, natural order (jpeg.c:1376) */
+	uint64_t out_off;	  /* byte offset of the packed output in the pixel slab */
+	uint64_t data_off;  /* byte offset of the file in the bitstream slab (16-byte aligned) */
+	uint32_t data_len;
+	uint32_t pad2;
+} jcu_image;
+
+typedef struct
+{
+	int32_t image;
+	int32_t kind; /* JCU_SCAN_* */
+	int32_t ncomp;
+	int32_t comp[4];		/* frame component index, in SOS order (jpeg.c:1495) */
+	int32_t dc_spec[4];	/* index into the jcu_huff_spec pool, -1 = undefined */
+	int32_t ac_spec[4];
+	int32_t ss, se, ah, al;
+	int32_t restart_interval; /* in units; 0 = none */
+	int32_t total_units;		  /* MCUs (interleaved) or blocks (single component) */
+	int32_t units_per_row;
+	int32_t wave;				  /* ordinal of the scan within its image; waves run in order */
+	uint32_t seg_first;		  /* first entry in the segment-offset array */
+	uint32_t nseg;
+	uint32_t data_end;		  /* offset (in the file) of the marker that terminates the scan */
+	uint32_t pad;
+} jcu_scan;
+
+typedef struct
+{
+	int32_t n_images;
+	const jcu_image *images;
+	int32_t n_scans;
+	const jcu_scan *scans;
+	uint32_t n_segs;
+	const uint32_t *seg_start; /* per segment: offset in the file of its first entropy-coded byte */
+	int32_t n_huff;
+	const jcu_huff_spec *huff;
+	const uint8_t *bitstream; /* host slab: files concatenated at 16-byte aligned offsets */
+	size_t bitstream_bytes;
+	size_t coef_elems;  /* int16 elements in the coefficient slab */
+	size_t plane_bytes; /* generic-path sample planes */
+	size_t out_bytes;	  /* pixel slab */
+	int32_t n_waves;
+	int32_t need_coef_clear; /* 1 = some image is progressive / multi-scan: zero the coefficient slab */
+} jcu_batch;
+
+typedef struct
+{
+	float h2d_ms, entropy_ms, idct_ms, d2h_ms, total_ms;
+	int32_t launches;
+} jcu_timings;
+
+typedef struct jcu_ctx jcu_ctx;
+
+#ifndef JCU_API
+#define JCU_API __attribute__((visibility("default")))
+#endif
+
+JCU_API int jcu_device_count(void);
+/* all functions below return 0 on success, else a CUDA error code; text via jcu_error_string */
+JCU_API int jcu_ctx_create(int device, int profile, int entropy_mode, jcu_ctx **out);
+JCU_API void jcu_ctx_destroy(jcu_ctx *c);
+JCU_API const char *jcu_error_string(jcu_ctx *c);
+
+JCU_API void *jcu_host_alloc(size_t bytes); /* pinned host memory */
+JCU_API void jcu_host_free(void *p);
+
+JCU_API int jcu_upload(jcu_ctx *c, const jcu_batch *b);								  /* H2D, asynchronous on the ctx stream */
+JCU_API int jcu_run(jcu_ctx *c);															  /* entropy waves + output stage, asynchronous */
+JCU_API int jcu_sync(jcu_ctx *c);
+JCU_API int jcu_download(jcu_ctx *c, size_t off, size_t bytes, void *dst);	  /* async D2H on the ctx stream */
+JCU_API int jcu_image_errors(jcu_ctx *c, int32_t *errs, int n);					  /* per-image device error flags (after sync) */
+JCU_API void *jcu_device_out(jcu_ctx *c);
+JCU_API int jcu_get_timings(jcu_ctx *c, jcu_timings *t);
+
+/* stage-level entry points for the parity tests (host pointers in, host pointers out) */
+JCU_API int jcu_test_idct_blocks(jcu_ctx *c, const int16_t *coef, const uint16_t *qt, int nblocks, uint8_t *out64);
+JCU_API int jcu_test_ycbcr(jcu_ctx *c, const uint8_t *y, const uint8_t *cb, const uint8_t *cr, int n, int step, uint8_t *out);
+JCU_API int jcu_read_coefs(jcu_ctx *c, size_t elem_off, size_t elems, int16_t *dst); /* coefficient slab after run */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

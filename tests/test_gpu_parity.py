@@ -1,0 +1,109 @@
+"""GPU parity tests proper: CUDA path vs the oracle, through the C-ABI (bit-exact)."""
+import os
+
+import numpy as np
+import pytest
+
+import image_codecs_b200 as ic
+from tests import streams as S
+
+pytestmark = pytest.mark.gpu
+
+
+def _check(oracle, got, data, req_comp, tag):
+    want, x, y, c = oracle.load_from_memory(data, req_comp)
+    assert want is not None, f"oracle failed on {tag}: {oracle.failure_reason()}"
+    assert got is not None, f"gpu failed on {tag}"
+    assert got.shape == want.shape, tag
+    if not np.array_equal(got, want):
+        d = np.argwhere(got != want)
+        raise AssertionError(f"{tag}: {len(d)} differing bytes, first at {d[0]}: got {got[tuple(d[0])]} want {want[tuple(d[0])]}")
+
+
+def test_idct_kernel_matches_reference(oracle):
+    lib = ic.lib()
+    import ctypes as C
+
+    ctx = C.c_void_p()
+    assert lib.jcu_ctx_create(0, 0, 0, C.byref(ctx)) == 0
+    rng = np.random.default_rng(1)
+    n = 4096
+    coef = np.zeros((n, 64), dtype=np.int16)
+    # sparse low-frequency blocks, dense blocks, extreme values, DC-only columns
+    for i in range(n):
+        k = rng.integers(1, 64)
+        idx = rng.choice(64, size=k, replace=False)
+        amp = [8, 64, 512, 2048, 32767][i % 5]
+        coef[i, idx] = rng.integers(-amp, amp + 1, size=k)
+    qt = rng.integers(1, 64, size=64).astype(np.uint16)
+    out = np.zeros((n, 64), dtype=np.uint8)
+    assert lib.jcu_test_idct_blocks(ctx, coef.ctypes.data, qt.ctypes.data, n, out.ctypes.data) == 0
+    lib.jcu_ctx_destroy(ctx)
+    deq = (coef.astype(np.int32) * qt.astype(np.int32)).astype(np.int16)
+    for i in range(n):
+        want = oracle.idct_block(deq[i])
+        assert np.array_equal(out[i].reshape(8, 8), want), f"block {i}"
+
+
+def test_ycbcr_kernel_matches_reference(oracle):
+    lib = ic.lib()
+    import ctypes as C
+
+    ctx = C.c_void_p()
+    assert lib.jcu_ctx_create(0, 0, 0, C.byref(ctx)) == 0
+    # every (Cb, Cr) pair at 16 luma levels + every luma at 256 chroma pairs
+    y, cb, cr = np.meshgrid(np.arange(0, 256, 17), np.arange(256), np.arange(256), indexing="ij")
+    y, cb, cr = (a.astype(np.uint8).ravel() for a in (y, cb, cr))
+    out = np.zeros((y.size, 3), dtype=np.uint8)
+    assert lib.jcu_test_ycbcr(ctx, y.ctypes.data, cb.ctypes.data, cr.ctypes.data, y.size, 3, out.ctypes.data) == 0
+    lib.jcu_ctx_destroy(ctx)
+    want = oracle.ycbcr_row(y, cb, cr, 3)
+    assert np.array_equal(out, want)
+
+
+@pytest.mark.parametrize("req_comp", [0, 3])
+def test_batch_matrix_bit_exact(oracle, decoder, req_comp):
+    cases = S.small_matrix()
+    datas = [S.stream(f, w, h, k) for f, w, h, k in cases]
+    outs = decoder.decode(datas, req_comp)
+    for (f, w, h, k), data, got in zip(cases, datas, outs):
+        _check(oracle, got, data, req_comp, f"{f} {w}x{h} kind{k} req{req_comp}")
+
+
+@pytest.mark.parametrize("req_comp", [1, 2, 4])
+def test_batch_req_comp_variants(oracle, decoder, req_comp):
+    cases = [c for c in S.small_matrix() if c[1:3] in ((233, 177), (17, 9))]
+    datas = [S.stream(f, w, h, k) for f, w, h, k in cases]
+    outs = decoder.decode(datas, req_comp)
+    for (f, w, h, k), data, got in zip(cases, datas, outs):
+        _check(oracle, got, data, req_comp, f"{f} {w}x{h} kind{k} req{req_comp}")
+
+
+def test_generic_path_matches_too(oracle):
+    """The two-pass generic path must agree with the fused kernels' formats as well."""
+    os.environ["IMAGE_CODECS_B200_FORCE_GENERIC"] = "1"
+    try:
+        d = ic.BatchDecoder(device=0)
+    finally:
+        del os.environ["IMAGE_CODECS_B200_FORCE_GENERIC"]
+    cases = [c for c in S.small_matrix() if c[0] in ("420", "444", "gray", "420_rst16", "420_prog")]
+    datas = [S.stream(f, w, h, k) for f, w, h, k in cases]
+    for rc in (0, 4):
+        outs = d.decode(datas, rc)
+        for (f, w, h, k), data, got in zip(cases, datas, outs):
+            _check(oracle, got, data, rc, f"generic {f} {w}x{h} req{rc}")
+    d.close()
+
+
+def test_per_image_api(oracle):
+    for fmt, w, h in [("420", 233, 177), ("gray", 64, 48), ("420_prog", 129, 65)]:
+        data = S.stream(fmt, w, h, 0)
+        for rc in (0, 1, 3, 4):
+            got, x, y, c = ic.stbi_load_from_memory(data, rc)
+            want, ox, oy, oc = oracle.load_from_memory(data, rc)
+            assert (x, y, c) == (ox, oy, oc)
+            assert np.array_equal(got, want), (fmt, rc)
+    assert ic.stbi_load_from_memory(b"not a jpeg", 0)[0] is None
+    assert ic.failure_reason() == "unknown image type"
+    assert ic.stbi_load_from_memory(S.stream("420", 64, 48, 0), 7)[0] is None
+    assert ic.failure_reason() == "bad req_comp"

@@ -305,6 +305,12 @@ static int batch_parse(stbi_jpeg_batch *b, const stbi_uc *const *bufs, const int
 				continue;
 			}
 			*im = r->img;
+			{
+				int q;
+				for (k = 0; k < 4; ++k)
+					for (q = 0; q < 64; ++q)
+						im->qt_out[k][q] = im->progressive ? im->qt[k][q] : 1;
+			}
 			im->data_off = offs[i];
 			im->data_len = (uint32_t)(lens[i] > 0 ? lens[i] : 0);
 			for (k = 0; k < im->ncomp; ++k)

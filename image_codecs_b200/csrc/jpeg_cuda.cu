@@ -43,6 +43,8 @@ struct jcu_ctx
 	int list_off[4] = {0, 0, 0, 0}, list_n[4] = {0, 0, 0, 0};
 	int tiles[4] = {0, 0, 0, 0};
 	int path_n[4] = {3, 3, 3, 3};
+	int path_deq[4] = {0, 0, 0, 0};
+	int path_maxtiles[4] = {0, 0, 0, 0};
 	int max_blocks_generic = 0;
 	long long max_pixels_generic = 0;
 	int launches = 0;
@@ -167,7 +169,7 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 	c->max_blocks_generic = 0;
 	c->max_pixels_generic = 0;
 	for (int p = 0; p < 4; ++p)
-		c->tiles[p] = 0;
+		c->tiles[p] = c->path_deq[p] = c->path_maxtiles[p] = 0;
 	for (int i = 0; i < b->n_images; ++i)
 	{
 		jcu_image &im = imgs[i];
@@ -178,6 +180,7 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 		int p = im.path;
 		lists[p].push_back(i);
 		c->path_n[p] = im.n_out;
+		c->path_deq[p] |= im.progressive;
 		if (p == JCU_PATH_GENERIC)
 		{
 			for (int k = 0; k < im.decode_n; ++k)
@@ -192,6 +195,7 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 			im.tiles_y = (im.height + th - 1) / th;
 			im.tile_first = c->tiles[p];
 			c->tiles[p] += im.tiles_x * im.tiles_y;
+			c->path_maxtiles[p] = std::max(c->path_maxtiles[p], im.tiles_x * im.tiles_y);
 		}
 	}
 	c->list_h.clear();
@@ -302,7 +306,7 @@ extern "C" int jcu_run(jcu_ctx *c)
 		if (c->list_n[p] > 0)
 		{
 			const int32_t *lst = (const int32_t *)c->lists.p + c->list_off[p];
-			cudaError_t e = fused_launch(p, c->tiles[p], lst, c->list_n[p], d_img, d_coef, (uint8_t *)c->out.p, st, c->path_n[p]);
+			cudaError_t e = fused_launch(p, c->path_maxtiles[p], lst, c->list_n[p], d_img, d_coef, (uint8_t *)c->out.p, st, c->path_n[p], c->path_deq[p]);
 			if (e != cudaSuccess)
 				return set_err(c, e, "fused_launch");
 			c->launches++;

@@ -11,16 +11,21 @@
  *
  * Parallel decomposition (not in the reference, which is strictly serial):
  *   - one CTA works on up to ENT_THREADS restart segments of ONE scan of ONE image, so the
- *     scan's Huffman lookup tables are built once per CTA in shared memory from the raw DHT
- *     contents;
+ *     scan's lookup tables are built once per CTA in shared memory from the raw DHT contents;
  *   - one thread decodes one restart segment (stbi__jpeg_reset, jpeg.c:1142, shows the state
  *     that resets at a restart: bit buffer, DC predictors, eob_run -- so segments are
  *     independent).  Streams without restart markers have one segment per scan here; the
  *     self-synchronising decoder (jpeg_selfsync.cuh) splits those further.
  *
- * Coefficients are written RAW (not dequantised), int16, natural (row-major) order, one
- * 128-byte block at a time: DC already de-predicted.  Truncation to 16 bits matches the
- * reference's (short) casts because the later (short)(c*q) only depends on c mod 2^16.
+ * Output: int16 coefficients, natural (row-major) order, one 128-byte block at a time, DC
+ * de-predicted.  Baseline scans store (short)(value * dequant) exactly as the reference does at
+ * decode time (jpeg.c:325,345,365); progressive scans store raw values and the output stage
+ * applies the 16-bit-wrapping dequantisation of stbi__jpeg_dequantize (jpeg.c:1319).
+ *
+ * Lookup (this repo's own format, one 32-bit entry per 9-bit prefix):
+ *   bits 0-4  bits to consume (0 = code longer than 9 bits -> canonical search)
+ *   bits 5-8  run            bits 9-12  magnitude bits still to read
+ *   bit 13    value resolved: code + magnitude fitted in 9 bits, bits 16-31 = extended value
  */
 #pragma once
 #include <cuda_runtime.h>
@@ -29,7 +34,7 @@
 #include "../../include/jpeg_cuda_abi.h"
 
 #define ENT_THREADS 128
-#define ENT_LUT_BITS 10
+#define ENT_LUT_BITS 9
 #define ENT_SLOT_WORDS 36 /* 64 int16 = 32 words, +4 pad words: 16B chunks of the 8 lanes of a phase hit distinct banks */
 
 /* zig-zag index -> natural index, with 16 trailing 63s like the reference's padded table
@@ -41,14 +46,16 @@ __constant__ uint8_t c_natural[80] = {0,	1,	 8,  16, 9,	 2,  3,	10, 17, 24, 32, 
 
 struct HuffLut
 {
-	uint16_t fast[1 << ENT_LUT_BITS]; /* (length << 8) | symbol, 0 = code longer than ENT_LUT_BITS */
-	uint32_t limit[18];					 /* limit[l] = (first code of length l + count) << (16 - l); [17] = ~0 */
-	int32_t base[17];						 /* symbol index = base[l] + code */
+	uint32_t fast[1 << ENT_LUT_BITS];
+	uint32_t limit[18]; /* limit[l] = (first code of length l + count) << (16 - l); [17] = ~0 */
+	int32_t base[17];	  /* symbol index = base[l] + code */
 	uint8_t vals[256];
 };
 
+#define LUT_RESOLVED 0x2000u
+
 /* Build one lookup table from raw DHT contents.  Called by all threads of the CTA. */
-__device__ __forceinline__ void hufflut_build(HuffLut *L, const jcu_huff_spec *spec, int tid, int nthreads)
+__device__ __forceinline__ void hufflut_build(HuffLut *L, const jcu_huff_spec *spec, bool is_dc, int tid, int nthreads)
 {
 	__shared__ uint32_t s_first[17]; /* first code of each length */
 	__shared__ uint32_t s_count[17];
@@ -76,14 +83,25 @@ __device__ __forceinline__ void hufflut_build(HuffLut *L, const jcu_huff_spec *s
 	__syncthreads();
 	for (int e = tid; e < (1 << ENT_LUT_BITS); e += nthreads)
 	{
-		uint16_t entry = 0;
+		uint32_t entry = 0;
 		for (int l = 1; l <= ENT_LUT_BITS; ++l)
 		{
 			uint32_t code = (uint32_t)e >> (ENT_LUT_BITS - l);
 			uint32_t rel = code - s_first[l];
 			if (code >= s_first[l] && rel < s_count[l])
 			{
-				entry = (uint16_t)((l << 8) | spec->vals[s_valptr[l] + (int)rel]);
+				int sym = spec->vals[s_valptr[l] + (int)rel];
+				int r = is_dc ? 0 : (sym >> 4);
+				int s = is_dc ? (sym > 15 ? 0 : sym) : (sym & 15); /* DC sizes > 15 decode to 0 (jpeg.c:259) */
+				if (s && l + s <= ENT_LUT_BITS)
+				{
+					int mag = (e >> (ENT_LUT_BITS - l - s)) & ((1 << s) - 1);
+					if (mag < (1 << (s - 1)))
+						mag += (int)(0xffffffffu << s) + 1;
+					entry = (uint32_t)(l + s) | ((uint32_t)r << 5) | LUT_RESOLVED | ((uint32_t)mag << 16);
+				}
+				else
+					entry = (uint32_t)l | ((uint32_t)r << 5) | ((uint32_t)s << 9);
 				break;
 			}
 		}
@@ -111,10 +129,10 @@ __device__ __forceinline__ void br_init(BitReader &br, const uint8_t *p, const u
 	br.stopped = 0;
 }
 
-/* top up to more than 56 bits, one byte at a time, with the reference's stuffing rules */
-__device__ __forceinline__ void br_refill(BitReader &br)
+/* one byte with the reference's stuffing rules: FF 00 -> FF, FF FF.. fill, FF xx -> stop */
+__device__ __noinline__ void br_refill_slow(BitReader &br)
 {
-	while (br.nbits <= 56)
+	do
 	{
 		uint32_t b = 0;
 		if (!br.stopped && br.p < br.end)
@@ -130,16 +148,37 @@ __device__ __forceinline__ void br_refill(BitReader &br)
 					c = q < br.end ? *q : 0u;
 				}
 				if (c == 0)
-					br.p = q < br.end ? q + 1 : br.end; /* FF 00: a literal FF */
+					br.p = q < br.end ? q + 1 : br.end;
 				else
 				{
-					br.stopped = 1; /* marker: stop consuming, the FF is not data */
+					br.stopped = 1;
 					b = 0;
 				}
 			}
 		}
 		br.buf |= (uint64_t)b << (56 - br.nbits);
 		br.nbits += 8;
+	} while (br.nbits <= 56 && (br.stopped || br.p >= br.end || ((uintptr_t)br.p & 3) != 0));
+}
+
+/* top up to more than 32 valid bits: aligned 32-bit loads while no byte of the word is 0xFF */
+__device__ __forceinline__ void br_refill(BitReader &br)
+{
+	while (br.nbits <= 32)
+	{
+		if (!br.stopped && ((uintptr_t)br.p & 3) == 0 && br.p + 4 <= br.end)
+		{
+			const uint32_t w = *reinterpret_cast<const uint32_t *>(br.p);
+			const uint32_t ff = ((w & 0x7f7f7f7fu) + 0x01010101u) & w & 0x80808080u;
+			if (ff == 0)
+			{
+				br.buf |= (uint64_t)__byte_perm(w, 0, 0x0123) << (32 - br.nbits);
+				br.nbits += 32;
+				br.p += 4;
+				continue;
+			}
+		}
+		br_refill_slow(br);
 	}
 }
 
@@ -163,18 +202,10 @@ __device__ __forceinline__ uint32_t br_bits(BitReader &br, int n) /* 0 <= n <= 1
 	return v;
 }
 
-/* returns the symbol, or -1 when no code matches (reference: "bad huffman code") */
-__device__ __forceinline__ int huff_decode(BitReader &br, const HuffLut *L)
+/* canonical search for codes longer than ENT_LUT_BITS; returns the symbol or -1 ("bad huffman code") */
+__device__ __noinline__ int huff_decode_long(BitReader &br, const HuffLut *L)
 {
-	if (br.nbits < 16)
-		br_refill(br);
 	uint32_t top = br_peek(br, 16);
-	uint32_t e = L->fast[top >> (16 - ENT_LUT_BITS)];
-	if (e)
-	{
-		br_skip(br, (int)(e >> 8));
-		return (int)(e & 255u);
-	}
 	int l = ENT_LUT_BITS + 1;
 	while (top >= L->limit[l])
 		++l;
@@ -186,6 +217,33 @@ __device__ __forceinline__ int huff_decode(BitReader &br, const HuffLut *L)
 	int idx = L->base[l] + (int)(top >> (16 - l));
 	br_skip(br, l);
 	return (int)L->vals[idx & 255];
+}
+
+/* plain symbol decode (progressive paths) */
+__device__ __forceinline__ int huff_decode(BitReader &br, const HuffLut *L)
+{
+	if (br.nbits <= 32)
+		br_refill(br);
+	uint32_t e = L->fast[br_peek(br, ENT_LUT_BITS)];
+	if ((e & 31u) == 0)
+		return huff_decode_long(br, L);
+	if (e & LUT_RESOLVED)
+	{
+		/* the table folded the magnitude bits in: undo that, callers want the bare symbol */
+		int s = 0;
+		/* code length = total - s, where s is recoverable from the value's magnitude */
+		int v = (int)e >> 16;
+		int a = v < 0 ? -v : v;
+		while (a)
+		{
+			++s;
+			a >>= 1;
+		}
+		br_skip(br, (int)(e & 31u) - s);
+		return (int)(((e >> 5) & 15u) << 4) | s;
+	}
+	br_skip(br, (int)(e & 31u));
+	return (int)((((e >> 5) & 15u) << 4) | ((e >> 9) & 15u));
 }
 
 /* receive n bits and sign-extend JPEG-style (stbi__extend_receive, jpeg.c:250) */
@@ -201,9 +259,11 @@ __device__ __forceinline__ int receive_extend(BitReader &br, int n)
 
 struct ScanShared
 {
-	HuffLut lut[8];  /* [0..3] DC per scan-component slot, [4..7] AC */
+	HuffLut lut[8];	/* [0..3] DC per scan-component slot, [4..7] AC */
 	int lut_of_dc[4]; /* slot -> lut index (slots sharing a spec share a table) */
 	int lut_of_ac[4];
+	uint16_t q[4][64]; /* quant table per scan-component slot, natural order (baseline) */
+	uint8_t zz[80];
 };
 
 /* one CTA work item */
@@ -216,8 +276,8 @@ struct EntWork
 
 /* ---- progressive block decoders operating directly on the coefficient slab ---- */
 
-__device__ __forceinline__ int prog_ac_first(BitReader &br, const HuffLut *L, int16_t *blk, int ss, int se, int al,
-															int &eob_run)
+__device__ __forceinline__ int prog_ac_first(BitReader &br, const HuffLut *L, const uint8_t *zz, int16_t *blk, int ss,
+															int se, int al, int &eob_run)
 {
 	if (eob_run)
 	{
@@ -246,7 +306,7 @@ __device__ __forceinline__ int prog_ac_first(BitReader &br, const HuffLut *L, in
 		else
 		{
 			k += r;
-			int zig = c_natural[k < 79 ? k : 79];
+			int zig = zz[k < 79 ? k : 79];
 			++k;
 			blk[zig] = (int16_t)(receive_extend(br, s) * (1 << al));
 		}
@@ -261,8 +321,8 @@ __device__ __forceinline__ void refine_one(int16_t *p, int bit)
 		*p = (int16_t)(v > 0 ? v + bit : v - bit);
 }
 
-__device__ __forceinline__ int prog_ac_refine(BitReader &br, const HuffLut *L, int16_t *blk, int ss, int se, int al,
-															 int &eob_run)
+__device__ __forceinline__ int prog_ac_refine(BitReader &br, const HuffLut *L, const uint8_t *zz, int16_t *blk, int ss,
+															 int se, int al, int &eob_run)
 {
 	const int bit = (int)(int16_t)(1 << al);
 	if (eob_run)
@@ -270,7 +330,7 @@ __device__ __forceinline__ int prog_ac_refine(BitReader &br, const HuffLut *L, i
 		--eob_run;
 		for (int k = ss; k <= se; ++k)
 		{
-			int16_t *p = &blk[c_natural[k]];
+			int16_t *p = &blk[zz[k]];
 			if (*p != 0)
 				if (br_bits(br, 1))
 					refine_one(p, bit);
@@ -302,7 +362,7 @@ __device__ __forceinline__ int prog_ac_refine(BitReader &br, const HuffLut *L, i
 		}
 		while (k <= se)
 		{
-			int16_t *p = &blk[c_natural[k++]];
+			int16_t *p = &blk[zz[k++]];
 			if (*p != 0)
 			{
 				if (br_bits(br, 1))
@@ -322,35 +382,89 @@ __device__ __forceinline__ int prog_ac_refine(BitReader &br, const HuffLut *L, i
 	return 1;
 }
 
-/* baseline block into a zeroed shared-memory slot (natural order, raw values) */
-__device__ __forceinline__ int baseline_block(BitReader &br, const HuffLut *Ldc, const HuffLut *Lac, int16_t *slot,
+/* baseline block into a zeroed shared-memory slot: natural order, dequantised, truncated to
+   16 bits like the reference's (short) casts (jpeg.c:325,345,365) */
+__device__ __forceinline__ int baseline_block(BitReader &br, const HuffLut *Ldc, const HuffLut *Lac,
+															 const uint16_t *__restrict__ q, const uint8_t *__restrict__ zz, int16_t *slot,
 															 int &dc_pred)
 {
-	int t = huff_decode(br, Ldc);
-	if (t < 0)
-		return 0;
-	dc_pred += receive_extend(br, t);
-	slot[0] = (int16_t)dc_pred;
-	int k = 1;
-	do
+	/* DC */
 	{
-		int rs = huff_decode(br, Lac);
-		if (rs < 0)
-			return 0;
-		int s = rs & 15, r = rs >> 4;
-		if (s == 0)
+		if (br.nbits <= 32)
+			br_refill(br);
+		const uint32_t e = Ldc->fast[br_peek(br, ENT_LUT_BITS)];
+		int diff;
+		if ((e & 31u) == 0)
 		{
-			if (rs != 0xf0)
-				break;
-			k += 16;
+			int t = huff_decode_long(br, Ldc);
+			if (t < 0)
+				return 0;
+			diff = receive_extend(br, t > 15 ? 0 : t);
 		}
 		else
 		{
-			k += r;
-			int zig = c_natural[k];
-			++k;
-			slot[zig] = (int16_t)receive_extend(br, s);
+			br_skip(br, (int)(e & 31u));
+			if (e & LUT_RESOLVED)
+				diff = (int)e >> 16;
+			else
+			{
+				const int s = (int)((e >> 9) & 15u);
+				diff = 0;
+				if (s)
+				{
+					diff = (int)br_peek(br, s);
+					br_skip(br, s);
+					if (diff < (1 << (s - 1)))
+						diff += (int)(0xffffffffu << s) + 1;
+				}
+			}
 		}
+		dc_pred += diff;
+		slot[0] = (int16_t)(dc_pred * (int)q[0]);
+	}
+	/* AC */
+	int k = 1;
+	do
+	{
+		if (br.nbits <= 32)
+			br_refill(br); /* > 32 bits: a 16-bit code plus 15 magnitude bits never needs a second refill */
+		uint32_t e = Lac->fast[br_peek(br, ENT_LUT_BITS)];
+		int r, s, val;
+		if ((e & 31u) == 0)
+		{
+			int rs = huff_decode_long(br, Lac);
+			if (rs < 0)
+				return 0;
+			r = rs >> 4;
+			s = rs & 15;
+			e = 0;
+		}
+		else
+		{
+			br_skip(br, (int)(e & 31u));
+			r = (int)((e >> 5) & 15u);
+			s = (int)((e >> 9) & 15u);
+		}
+		if (e & LUT_RESOLVED)
+			val = (int)e >> 16;
+		else
+		{
+			if (s == 0)
+			{
+				if (r != 15)
+					break; /* EOB */
+				k += 16;	 /* ZRL */
+				continue;
+			}
+			val = (int)br_peek(br, s);
+			br_skip(br, s);
+			if (val < (1 << (s - 1)))
+				val += (int)(0xffffffffu << s) + 1;
+		}
+		k += r;
+		const int zig = zz[k];
+		++k;
+		slot[zig] = (int16_t)(val * (int)q[zig]);
 	} while (k < 64);
 	return 1;
 }
@@ -375,6 +489,10 @@ k_entropy_segments(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 	const int kind = sc->kind, ncs = sc->ncomp;
 
 	/* ---- lookup tables, once per CTA ---- */
+	if (tid < 80)
+		sh.zz[tid] = c_natural[tid];
+	for (int i = tid; i < ncs * 64; i += ENT_THREADS)
+		sh.q[i >> 6][i & 63] = im->qt[sc->comp[i >> 6]][i & 63];
 	for (int i = 0; i < ncs; ++i)
 	{
 		if (sc->dc_spec[i] >= 0)
@@ -385,7 +503,7 @@ k_entropy_segments(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 					alias = sh.lut_of_dc[j];
 			if (alias < 0)
 			{
-				hufflut_build(&sh.lut[i], &huff[sc->dc_spec[i]], tid, ENT_THREADS);
+				hufflut_build(&sh.lut[i], &huff[sc->dc_spec[i]], true, tid, ENT_THREADS);
 				alias = i;
 			}
 			if (tid == 0)
@@ -399,7 +517,7 @@ k_entropy_segments(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 					alias = sh.lut_of_ac[j];
 			if (alias < 0)
 			{
-				hufflut_build(&sh.lut[4 + i], &huff[sc->ac_spec[i]], tid, ENT_THREADS);
+				hufflut_build(&sh.lut[4 + i], &huff[sc->ac_spec[i]], false, tid, ENT_THREADS);
 				alias = 4 + i;
 			}
 			if (tid == 0)
@@ -442,12 +560,14 @@ k_entropy_segments(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 		const int u = u0 + uu;
 		const bool live = active && u < u1 && !failed;
 		const int ux = u % upr, uy = u / upr;
+#pragma unroll 1
 		for (int i = 0; i < ncs; ++i)
 		{
 			const jcu_comp *cp = &im->comp[sc->comp[i]];
 			const int bh_n = ncs == 1 ? 1 : cp->v, bw_n = ncs == 1 ? 1 : cp->h;
 			const HuffLut *Ldc = &sh.lut[sh.lut_of_dc[i] & 7];
 			const HuffLut *Lac = &sh.lut[sh.lut_of_ac[i] & 7];
+			int dcp = dc_pred[i];
 			for (int y = 0; y < bh_n; ++y)
 				for (int x = 0; x < bw_n; ++x)
 				{
@@ -458,7 +578,7 @@ k_entropy_segments(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 						bool ok = false;
 						if (live && !failed)
 						{
-							ok = baseline_block(br, Ldc, Lac, slot, dc_pred[i]) != 0;
+							ok = baseline_block(br, Ldc, Lac, sh.q[i], sh.zz, slot, dcp) != 0;
 							if (!ok)
 								failed = true;
 						}
@@ -491,8 +611,8 @@ k_entropy_segments(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 								ok = 0;
 							else
 							{
-								dc_pred[i] += receive_extend(br, t);
-								blk[0] = (int16_t)(dc_pred[i] * (1 << al));
+								dcp += receive_extend(br, t);
+								blk[0] = (int16_t)(dcp * (1 << al));
 							}
 						}
 						else if (kind == JCU_SCAN_PROG_DC_REFINE)
@@ -501,13 +621,14 @@ k_entropy_segments(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 								blk[0] = (int16_t)(blk[0] + (int16_t)(1 << al));
 						}
 						else if (kind == JCU_SCAN_PROG_AC_FIRST)
-							ok = prog_ac_first(br, Lac, blk, ss, se, al, eob_run);
+							ok = prog_ac_first(br, Lac, sh.zz, blk, ss, se, al, eob_run);
 						else
-							ok = prog_ac_refine(br, Lac, blk, ss, se, al, eob_run);
+							ok = prog_ac_refine(br, Lac, sh.zz, blk, ss, se, al, eob_run);
 						if (!ok)
 							failed = true;
 					}
 				}
+			dc_pred[i] = dcp;
 		}
 	}
 	if (failed)

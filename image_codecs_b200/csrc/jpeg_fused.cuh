@@ -134,35 +134,156 @@ __device__ __forceinline__ uint32_t rgb_pack(int y, int cb, int cr)
 #define F420_CBH 6
 #define F420_CW (F420_CBW * 8)
 #define F420_CH (F420_CBH * 8)
+#define F420_NCH (F420_CBW * F420_CBH)		/* chroma block positions per component */
+#define F420_SLOTS (128 + 2 * F420_NCH)	/* staged coefficient blocks per tile */
+#define F420_SMEM_COEF (F420_SLOTS * 128)
+#define F420_SMEM_Y (F420_TH * F420_TW)
+#define F420_SMEM_C (F420_CH * F420_CW * 4)
+#define F420_SMEM_BYTES (F420_SMEM_COEF + F420_SMEM_Y + F420_SMEM_C + 3 * 128)
 
-template <int N>
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc)
+{
+	unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+/* saturate two s32 to u8 and pack below the low half of c: result bytes = [sat(lo), sat(hi), c.b0, c.b1] */
+__device__ __forceinline__ uint32_t pack_sat_u8(int hi, int lo, uint32_t c)
+{
+	uint32_t d;
+	asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(hi), "r"(lo), "r"(c));
+	return d;
+}
+/* four s32 -> four saturated bytes [b0, b1, b2, b3] */
+__device__ __forceinline__ uint32_t pack4_sat_u8(int b0, int b1, int b2, int b3)
+{
+	return pack_sat_u8(b1, b0, pack_sat_u8(b3, b2, 0u));
+}
+
+/* 64 coefficients of one staged block (swizzled 16-byte chunks) -> sign-extended ints; DEQ applies
+   (short)(c*q) from the tile's quant table in shared memory (progressive; jpeg.c:1323) */
+template <bool DEQ>
+__device__ __forceinline__ void load_block_smem(const uint4 *__restrict__ slot, int swz, const uint16_t *__restrict__ q,
+																int (&v)[64])
+{
+#pragma unroll
+	for (int j = 0; j < 8; ++j)
+	{
+		const uint4 w = slot[j ^ swz];
+		const uint32_t ws[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+		for (int i = 0; i < 4; ++i)
+		{
+			int c0 = (int)(int16_t)(ws[i] & 0xffffu);
+			int c1 = ((int)ws[i]) >> 16;
+			if (DEQ)
+			{
+				c0 = (int)(int16_t)(c0 * (int)q[j * 8 + 2 * i]);
+				c1 = (int)(int16_t)(c1 * (int)q[j * 8 + 2 * i + 1]);
+			}
+			v[j * 8 + 2 * i] = c0;
+			v[j * 8 + 2 * i + 1] = c1;
+		}
+	}
+}
+
+/* IDCT of 64 ints in v -> 8 rows of 8 saturated samples, two words per row */
+__device__ __forceinline__ void idct_block_packed(int (&v)[64], uint32_t (&rows)[16])
+{
+	int o[8];
+#pragma unroll
+	for (int c = 0; c < 8; ++c)
+	{
+		idct_1d(v[c], v[c + 8], v[c + 16], v[c + 24], v[c + 32], v[c + 40], v[c + 48], v[c + 56], 512, o);
+#pragma unroll
+		for (int r = 0; r < 8; ++r)
+			v[c + 8 * r] = o[r] >> 10;
+	}
+#pragma unroll
+	for (int r = 0; r < 8; ++r)
+	{
+		idct_1d(v[8 * r], v[8 * r + 1], v[8 * r + 2], v[8 * r + 3], v[8 * r + 4], v[8 * r + 5], v[8 * r + 6],
+				  v[8 * r + 7], 65536 + (128 << 17), o);
+		rows[2 * r] = pack4_sat_u8(o[0] >> 17, o[1] >> 17, o[2] >> 17, o[3] >> 17);
+		rows[2 * r + 1] = pack4_sat_u8(o[4] >> 17, o[5] >> 17, o[6] >> 17, o[7] >> 17);
+	}
+}
+
+/*
+ * grid: (max tiles per image, images on this path).  DEQ = coefficients are raw (progressive);
+ * otherwise the entropy stage already stored (short)(c*q) as the reference does for baseline
+ * (jpeg.c:325,345,365).
+ */
+template <int N, bool DEQ>
 __global__ void __launch_bounds__(FUSED_THREADS, 2)
-k_fused_420(const int32_t *__restrict__ list, int nlist, const jcu_image *__restrict__ images,
+k_fused_420(const int32_t *__restrict__ list, const jcu_image *__restrict__ images,
 				const int16_t *__restrict__ coef, uint8_t *__restrict__ out)
 {
-	__shared__ __align__(16) uint8_t sY[F420_TH][F420_TW];
-	__shared__ __align__(16) uint32_t sC[F420_CH][F420_CW]; /* Cb | Cr << 16 */
+	extern __shared__ __align__(16) unsigned char f420_smem[];
+	uint4 *sCoef = reinterpret_cast<uint4 *>(f420_smem);																		  /* [F420_SLOTS * 8] */
+	uint8_t(*sY)[F420_TW] = reinterpret_cast<uint8_t(*)[F420_TW]>(f420_smem + F420_SMEM_COEF);				  /* [F420_TH] */
+	uint32_t(*sC)[F420_CW] = reinterpret_cast<uint32_t(*)[F420_CW]>(f420_smem + F420_SMEM_COEF + F420_SMEM_Y); /* 16*(Cb|Cr<<16) */
+	uint16_t(*sQ)[64] = reinterpret_cast<uint16_t(*)[64]>(f420_smem + F420_SMEM_COEF + F420_SMEM_Y + F420_SMEM_C);
 
-	int local;
-	const jcu_image *im = fused_locate(list, nlist, images, blockIdx.x, local);
-	const int tx = local % im->tiles_x, ty = local / im->tiles_x;
+	const jcu_image *im = &images[list[blockIdx.y]];
+	const int tiles_x = im->tiles_x;
+	if ((int)blockIdx.x >= tiles_x * im->tiles_y)
+		return;
+	const int tx = blockIdx.x % tiles_x, ty = blockIdx.x / tiles_x;
 	const int W = im->width, H = im->height;
 	const int tid = threadIdx.x;
+	const int ybw = im->comp[0].bw, ybh = im->comp[0].bh, cbw = im->comp[1].bw, cbh = im->comp[1].bh;
 
-	/* ---- phase 1: IDCT ---- */
+	/* ---- phase 0: stage the tile's coefficient blocks (own + chroma halo ring) ---- */
+	{
+		const int16_t *base0 = coef + im->comp[0].coef_off;
+		const int16_t *base1 = coef + im->comp[1].coef_off;
+		const int16_t *base2 = coef + im->comp[2].coef_off;
+#pragma unroll
+		for (int it = 0; it < (F420_SLOTS * 8 + FUSED_THREADS - 1) / FUSED_THREADS; ++it)
+		{
+			const int id = tid + it * FUSED_THREADS;
+			const int slot = id >> 3, j = id & 7;
+			if (slot < F420_SLOTS)
+			{
+				const int16_t *src = nullptr;
+				if (slot < 128)
+				{
+					const int bx = tx * 16 + (slot & 15), by = ty * 8 + (slot >> 4);
+					if (bx < ybw && by < ybh)
+						src = base0 + ((size_t)by * ybw + bx) * 64;
+				}
+				else
+				{
+					const int idx = slot - 128;
+					const int ci = idx >= F420_NCH, pos = idx - ci * F420_NCH;
+					const int bx = tx * 8 - 1 + pos % F420_CBW, by = ty * 4 - 1 + pos / F420_CBW;
+					if (bx >= 0 && by >= 0 && bx < cbw && by < cbh)
+						src = (ci ? base2 : base1) + ((size_t)by * cbw + bx) * 64;
+				}
+				if (src)
+					cp_async16(&sCoef[slot * 8 + (j ^ (slot & 7))], src + j * 8);
+			}
+		}
+		if (DEQ)
+			for (int i = tid; i < 192; i += FUSED_THREADS)
+				sQ[i >> 6][i & 63] = im->qt_out[i >> 6][i & 63];
+		cp_async_wait_all();
+	}
+	__syncthreads();
+
+	/* ---- phase 1: one thread = one block: dequant, column pass, row pass ---- */
 	{
 		int v[64];
 		uint32_t rows[16];
 		if (tid < 128)
 		{
-			/* luma: 16 x 8 blocks */
-			const jcu_comp *cp = &im->comp[0];
 			const int lbx = tid & 15, lby = tid >> 4;
-			const int bx = tx * 16 + lbx, by = ty * 8 + lby;
-			if (bx < cp->bw && by < cp->bh)
+			if (tx * 16 + lbx < ybw && ty * 8 + lby < ybh)
 			{
-				load_dequant(coef + cp->coef_off + ((size_t)by * cp->bw + bx) * 64, im->qt[0], v);
-				idct_block_regs(v, rows);
+				load_block_smem<DEQ>(&sCoef[tid * 8], tid & 7, sQ[0], v);
+				idct_block_packed(v, rows);
 #pragma unroll
 				for (int r = 0; r < 8; ++r)
 					*reinterpret_cast<uint2 *>(&sY[lby * 8 + r][lbx * 8]) = make_uint2(rows[2 * r], rows[2 * r + 1]);
@@ -170,17 +291,18 @@ k_fused_420(const int32_t *__restrict__ list, int nlist, const jcu_image *__rest
 		}
 		else
 		{
-			/* chroma: lane pairs (Cb, Cr) of one block position, halo ring included */
+			/* lanes (2p, 2p+1) = (Cb, Cr) of chroma position p; they swap rows by shuffle and store
+			   16*(Cb | Cr<<16) so the upsampling filter handles both components in one register */
 			const int item = tid - 128;
-			const int ci = 1 + (item & 1), pos = item >> 1;
+			const int ci = item & 1, pos = item >> 1;
+			const int slot = 128 + ci * F420_NCH + pos;
 			const int lbx = pos % F420_CBW, lby = pos / F420_CBW;
-			const jcu_comp *cp = &im->comp[ci];
 			const int bx = tx * 8 - 1 + lbx, by = ty * 4 - 1 + lby;
-			const bool have = item < 2 * F420_CBW * F420_CBH && bx >= 0 && by >= 0 && bx < cp->bw && by < cp->bh;
+			const bool have = pos < F420_NCH && bx >= 0 && by >= 0 && bx < cbw && by < cbh;
 			if (have)
 			{
-				load_dequant(coef + cp->coef_off + ((size_t)by * cp->bw + bx) * 64, im->qt[ci], v);
-				idct_block_regs(v, rows);
+				load_block_smem<DEQ>(&sCoef[slot * 8], slot & 7, sQ[1 + ci], v);
+				idct_block_packed(v, rows);
 			}
 			else
 			{
@@ -188,30 +310,26 @@ k_fused_420(const int32_t *__restrict__ list, int nlist, const jcu_image *__rest
 				for (int i = 0; i < 16; ++i)
 					rows[i] = 0;
 			}
-			/* exchange with the partner lane; even lane (Cb) packs rows 0-3, odd lane (Cr) rows 4-7 */
-			const bool is_cr = (item & 1) != 0;
+			const bool is_cr = ci != 0;
 #pragma unroll
 			for (int r = 0; r < 8; ++r)
 			{
-				uint32_t plo = __shfl_xor_sync(0xffffffffu, rows[2 * r], 1);
-				uint32_t phi = __shfl_xor_sync(0xffffffffu, rows[2 * r + 1], 1);
+				const uint32_t plo = __shfl_xor_sync(0xffffffffu, rows[2 * r], 1);
+				const uint32_t phi = __shfl_xor_sync(0xffffffffu, rows[2 * r + 1], 1);
 				const bool mine = is_cr ? (r >= 4) : (r < 4);
 				if (mine && have)
 				{
-					uint32_t cb_lo = is_cr ? plo : rows[2 * r], cb_hi = is_cr ? phi : rows[2 * r + 1];
-					uint32_t cr_lo = is_cr ? rows[2 * r] : plo, cr_hi = is_cr ? rows[2 * r + 1] : phi;
+					const uint32_t cb_lo = is_cr ? plo : rows[2 * r], cb_hi = is_cr ? phi : rows[2 * r + 1];
+					const uint32_t cr_lo = is_cr ? rows[2 * r] : plo, cr_hi = is_cr ? rows[2 * r + 1] : phi;
 					uint4 a, b;
-					a.x = __byte_perm(cb_lo, cr_lo, 0x0400);
-					a.y = __byte_perm(cb_lo, cr_lo, 0x0501);
-					a.z = __byte_perm(cb_lo, cr_lo, 0x0602);
-					a.w = __byte_perm(cb_lo, cr_lo, 0x0703);
-					b.x = __byte_perm(cb_hi, cr_hi, 0x0400);
-					b.y = __byte_perm(cb_hi, cr_hi, 0x0501);
-					b.z = __byte_perm(cb_hi, cr_hi, 0x0602);
-					b.w = __byte_perm(cb_hi, cr_hi, 0x0703);
-					/* keep only byte 0 and byte 2 of each word: (cb) | (cr << 16) */
-					a.x &= 0x00ff00ffu; a.y &= 0x00ff00ffu; a.z &= 0x00ff00ffu; a.w &= 0x00ff00ffu;
-					b.x &= 0x00ff00ffu; b.y &= 0x00ff00ffu; b.z &= 0x00ff00ffu; b.w &= 0x00ff00ffu;
+					a.x = (__byte_perm(cb_lo, cr_lo, 0x0400) & 0x00ff00ffu) << 4;
+					a.y = (__byte_perm(cb_lo, cr_lo, 0x0501) & 0x00ff00ffu) << 4;
+					a.z = (__byte_perm(cb_lo, cr_lo, 0x0602) & 0x00ff00ffu) << 4;
+					a.w = (__byte_perm(cb_lo, cr_lo, 0x0703) & 0x00ff00ffu) << 4;
+					b.x = (__byte_perm(cb_hi, cr_hi, 0x0400) & 0x00ff00ffu) << 4;
+					b.y = (__byte_perm(cb_hi, cr_hi, 0x0501) & 0x00ff00ffu) << 4;
+					b.z = (__byte_perm(cb_hi, cr_hi, 0x0602) & 0x00ff00ffu) << 4;
+					b.w = (__byte_perm(cb_hi, cr_hi, 0x0703) & 0x00ff00ffu) << 4;
 					uint4 *dst = reinterpret_cast<uint4 *>(&sC[lby * 8 + r][lbx * 8]);
 					dst[0] = a;
 					dst[1] = b;
@@ -221,12 +339,30 @@ k_fused_420(const int32_t *__restrict__ list, int nlist, const jcu_image *__rest
 	}
 	__syncthreads();
 
-	/* ---- phase 2: upsample + colour + store ---- */
-	const jcu_comp *cc = &im->comp[1];
-	const int wl = cc->w_lores, cy = cc->cy;
+	/* ---- clamp-to-edge on the REAL chroma width (w_lores, jpeg.c:2276): replicate one column
+	   past each image edge so phase 2 needs no per-sample clamps ---- */
+	const int wl = im->comp[1].w_lores, cy = im->comp[1].cy;
 	const int crow0 = ty * 32 - 8, ccol0 = tx * 64 - 8; /* global chroma coords of sC[0][0] */
+	{
+		const int last = wl - 1 - ccol0; /* local column of the last real chroma sample */
+		const bool left = tx == 0, right = last + 1 < F420_CW && last >= 0 && last < 8 + 64;
+		if (left || right)
+		{
+			if (tid < F420_CH)
+			{
+				if (left)
+					sC[tid][7] = sC[tid][8];
+				if (right)
+					sC[tid][last + 1] = sC[tid][last];
+			}
+			__syncthreads();
+		}
+	}
+
+	/* ---- phase 2: one task = 16 pixels of one row ---- */
 	const bool vec_ok = (N == 4) ? ((W & 3) == 0) : ((W & 15) == 0);
 	uint8_t *obase = out + im->out_off;
+#pragma unroll 1
 	for (int task = tid; task < (F420_TH * F420_TW) / 16; task += FUSED_THREADS)
 	{
 		const int ly = task >> 3, g = task & 7;
@@ -236,31 +372,81 @@ k_fused_420(const int32_t *__restrict__ list, int nlist, const jcu_image *__rest
 		const int k = gy >> 1;
 		const int nr = min(k, cy - 1) - crow0;
 		const int fr = ((gy & 1) ? min(k + 1, cy - 1) : max(k - 1, 0)) - crow0;
-		/* t[j] for chroma columns i0-1 .. i0+8, clamped to the real width */
+		/* t[j] = 16 * (3*near + far) for chroma columns i0-1 .. i0+8 (both components packed) */
 		uint32_t t[10];
-		const int i0 = gx0 >> 1;
-#pragma unroll
-		for (int j = 0; j < 10; ++j)
 		{
-			int ci = min(max(i0 - 1 + j, 0), wl - 1) - ccol0;
-			t[j] = 3u * sC[nr][ci] + sC[fr][ci];
+			const uint32_t *np = &sC[nr][7 + g * 8], *fp = &sC[fr][7 + g * 8];
+			const uint4 n0 = *reinterpret_cast<const uint4 *>(np + 1), n1 = *reinterpret_cast<const uint4 *>(np + 5);
+			const uint4 f0 = *reinterpret_cast<const uint4 *>(fp + 1), f1 = *reinterpret_cast<const uint4 *>(fp + 5);
+			t[0] = 3u * np[0] + fp[0];
+			t[1] = 3u * n0.x + f0.x;
+			t[2] = 3u * n0.y + f0.y;
+			t[3] = 3u * n0.z + f0.z;
+			t[4] = 3u * n0.w + f0.w;
+			t[5] = 3u * n1.x + f1.x;
+			t[6] = 3u * n1.y + f1.y;
+			t[7] = 3u * n1.z + f1.z;
+			t[8] = 3u * n1.w + f1.w;
+			t[9] = 3u * np[9] + fp[9];
 		}
 		const uint4 yv = *reinterpret_cast<const uint4 *>(&sY[ly][g * 16]);
 		const uint32_t yw[4] = {yv.x, yv.y, yv.z, yv.w};
-		uint32_t px[16];
+		int R[16], G[16], B[16];
 #pragma unroll
-		for (int j = 0; j < 8; ++j)
+		for (int p = 0; p < 16; ++p)
 		{
-			/* even pixel 2i uses t[i-1], odd pixel 2i+1 uses t[i+1]  (jpeg.c:1832-1833) */
-			uint32_t ce = ((3u * t[j + 1] + t[j] + 0x00080008u) >> 4) & 0x00ff00ffu;
-			uint32_t co = ((3u * t[j + 1] + t[j + 2] + 0x00080008u) >> 4) & 0x00ff00ffu;
-			int y0 = (int)((yw[j >> 1] >> (16 * (j & 1))) & 255u);
-			int y1 = (int)((yw[j >> 1] >> (16 * (j & 1) + 8)) & 255u);
-			px[2 * j] = rgb_pack(y0, (int)(ce & 255u), (int)(ce >> 16));
-			px[2 * j + 1] = rgb_pack(y1, (int)(co & 255u), (int)(co >> 16));
+			const int j = p >> 1;
+			/* (3*t[i] + t[i-1 or i+1] + 8) >> 4 (jpeg.c:1832-1833), here scaled by 16 so that the two
+			   results sit in bytes 1 and 3; xor 0x80 turns them into signed (c - 128) */
+			const uint32_t c16 = (3u * t[j + 1] + ((p & 1) ? t[j + 2] : t[j]) + 0x00800080u) ^ 0x80008000u;
+			const int cb = (int)(int8_t)(c16 >> 8);
+			const int cr = ((int)c16) >> 24;
+			const int y = (int)((yw[p >> 2] >> (8 * (p & 3))) & 255u);
+			/* stbi__YCbCr_to_RGB_row (jpeg.c:1981-1990) with the common factor 2^8 divided out */
+			const int yf = y * 4096 + 2048;
+			R[p] = (yf + cr * 5743) >> 12;
+			G[p] = (yf + cr * -2925 + ((cb * -1410) & ~255)) >> 12;
+			B[p] = (yf + cb * 7258) >> 12;
 		}
 		const int count = min(16, W - gx0);
-		store_pixels<N>(obase + ((size_t)gy * W + gx0) * N, px, count, vec_ok);
+		uint8_t *o = obase + ((size_t)gy * W + gx0) * N;
+		if (vec_ok && count == 16)
+		{
+			if (N == 3)
+			{
+#pragma unroll
+				for (int q = 0; q < 4; ++q)
+				{
+					const int a = 4 * q;
+					uint32_t *ow = reinterpret_cast<uint32_t *>(o) + 3 * q;
+					ow[0] = pack4_sat_u8(R[a], G[a], B[a], R[a + 1]);
+					ow[1] = pack4_sat_u8(G[a + 1], B[a + 1], R[a + 2], G[a + 2]);
+					ow[2] = pack4_sat_u8(B[a + 2], R[a + 3], G[a + 3], B[a + 3]);
+				}
+			}
+			else
+			{
+#pragma unroll
+				for (int q = 0; q < 4; ++q)
+					reinterpret_cast<uint4 *>(o)[q] =
+						 make_uint4(pack4_sat_u8(R[4 * q], G[4 * q], B[4 * q], 255), pack4_sat_u8(R[4 * q + 1], G[4 * q + 1], B[4 * q + 1], 255),
+										pack4_sat_u8(R[4 * q + 2], G[4 * q + 2], B[4 * q + 2], 255),
+										pack4_sat_u8(R[4 * q + 3], G[4 * q + 3], B[4 * q + 3], 255));
+			}
+		}
+		else
+		{
+#pragma unroll
+			for (int p = 0; p < 16; ++p)
+				if (p < count)
+				{
+					o[N * p] = (uint8_t)clamp_u8(R[p]);
+					o[N * p + 1] = (uint8_t)clamp_u8(G[p]);
+					o[N * p + 2] = (uint8_t)clamp_u8(B[p]);
+					if (N == 4)
+						o[N * p + 3] = 255;
+				}
+		}
 	}
 }
 
@@ -269,14 +455,15 @@ k_fused_420(const int32_t *__restrict__ list, int nlist, const jcu_image *__rest
 /* ===================================================================================== */
 template <int N>
 __global__ void __launch_bounds__(FUSED_THREADS, 2)
-k_fused_444(const int32_t *__restrict__ list, int nlist, const jcu_image *__restrict__ images,
+k_fused_444(const int32_t *__restrict__ list, const jcu_image *__restrict__ images,
 				const int16_t *__restrict__ coef, uint8_t *__restrict__ out)
 {
 	__shared__ __align__(16) uint8_t sP[3][F444_TH][F444_TW];
 
-	int local;
-	const jcu_image *im = fused_locate(list, nlist, images, blockIdx.x, local);
-	const int tx = local % im->tiles_x, ty = local / im->tiles_x;
+	const jcu_image *im = &images[list[blockIdx.y]];
+	if ((int)blockIdx.x >= im->tiles_x * im->tiles_y)
+		return;
+	const int tx = blockIdx.x % im->tiles_x, ty = blockIdx.x / im->tiles_x;
 	const int W = im->width, H = im->height;
 	const int tid = threadIdx.x;
 
@@ -290,7 +477,7 @@ k_fused_444(const int32_t *__restrict__ list, int nlist, const jcu_image *__rest
 		const int bx = tx * 16 + lbx, by = ty * 4 + lby;
 		if (bx < cp->bw && by < cp->bh)
 		{
-			load_dequant(coef + cp->coef_off + ((size_t)by * cp->bw + bx) * 64, im->qt[ci], v);
+			load_dequant(coef + cp->coef_off + ((size_t)by * cp->bw + bx) * 64, im->qt_out[ci], v);
 			idct_block_regs(v, rows);
 #pragma unroll
 			for (int r = 0; r < 8; ++r)
@@ -328,14 +515,15 @@ k_fused_444(const int32_t *__restrict__ list, int nlist, const jcu_image *__rest
 /* ===================================================================================== */
 template <int N>
 __global__ void __launch_bounds__(FUSED_THREADS, 2)
-k_fused_gray(const int32_t *__restrict__ list, int nlist, const jcu_image *__restrict__ images,
+k_fused_gray(const int32_t *__restrict__ list, const jcu_image *__restrict__ images,
 				 const int16_t *__restrict__ coef, uint8_t *__restrict__ out)
 {
 	__shared__ __align__(16) uint8_t sY[FGRAY_TH][FGRAY_TW];
 
-	int local;
-	const jcu_image *im = fused_locate(list, nlist, images, blockIdx.x, local);
-	const int tx = local % im->tiles_x, ty = local / im->tiles_x;
+	const jcu_image *im = &images[list[blockIdx.y]];
+	if ((int)blockIdx.x >= im->tiles_x * im->tiles_y)
+		return;
+	const int tx = blockIdx.x % im->tiles_x, ty = blockIdx.x / im->tiles_x;
 	const int W = im->width, H = im->height;
 	const int tid = threadIdx.x;
 	{
@@ -346,7 +534,7 @@ k_fused_gray(const int32_t *__restrict__ list, int nlist, const jcu_image *__res
 		const int bx = tx * 32 + lbx, by = ty * 8 + lby;
 		if (bx < cp->bw && by < cp->bh)
 		{
-			load_dequant(coef + cp->coef_off + ((size_t)by * cp->bw + bx) * 64, im->qt[0], v);
+			load_dequant(coef + cp->coef_off + ((size_t)by * cp->bw + bx) * 64, im->qt_out[0], v);
 			idct_block_regs(v, rows);
 #pragma unroll
 			for (int r = 0; r < 8; ++r)
@@ -409,36 +597,39 @@ k_fused_gray(const int32_t *__restrict__ list, int nlist, const jcu_image *__res
 	}
 }
 
-/* host-side dispatch: one launch per path, grid = tiles of all images on that path.
-   n_out is uniform per batch (req_comp applies to the whole call) except that gray files
-   and colour files can differ; the list is therefore split by the caller per (path, n). */
-static inline cudaError_t fused_launch(int path, int tiles, const int32_t *list, int nlist, const jcu_image *images,
-													const int16_t *coef, uint8_t *out, cudaStream_t st, int n_out)
+/* host-side dispatch: one launch per path; grid = (max tiles per image, images on the path).
+   n_out is uniform per path within one call (req_comp applies to the whole call). */
+static inline cudaError_t fused_launch(int path, int max_tiles, const int32_t *list, int nlist, const jcu_image *images,
+													const int16_t *coef, uint8_t *out, cudaStream_t st, int n_out, int deq)
 {
-	if (tiles <= 0)
+	if (max_tiles <= 0 || nlist <= 0)
 		return cudaSuccess;
-	dim3 grid((unsigned)tiles), block(FUSED_THREADS);
+	dim3 grid((unsigned)max_tiles, (unsigned)nlist), block(FUSED_THREADS);
 	switch (path)
 	{
 	case JCU_PATH_FUSED_420:
-		if (n_out == 4)
-			k_fused_420<4><<<grid, block, 0, st>>>(list, nlist, images, coef, out);
-		else
-			k_fused_420<3><<<grid, block, 0, st>>>(list, nlist, images, coef, out);
+	{
+		void (*k)(const int32_t *, const jcu_image *, const int16_t *, uint8_t *) =
+			 n_out == 4 ? (deq ? k_fused_420<4, true> : k_fused_420<4, false>) : (deq ? k_fused_420<3, true> : k_fused_420<3, false>);
+		cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, F420_SMEM_BYTES);
+		if (e != cudaSuccess)
+			return e;
+		k<<<grid, block, F420_SMEM_BYTES, st>>>(list, images, coef, out);
 		break;
+	}
 	case JCU_PATH_FUSED_444:
 		if (n_out == 4)
-			k_fused_444<4><<<grid, block, 0, st>>>(list, nlist, images, coef, out);
+			k_fused_444<4><<<grid, block, 0, st>>>(list, images, coef, out);
 		else
-			k_fused_444<3><<<grid, block, 0, st>>>(list, nlist, images, coef, out);
+			k_fused_444<3><<<grid, block, 0, st>>>(list, images, coef, out);
 		break;
 	default:
 		switch (n_out)
 		{
-		case 1: k_fused_gray<1><<<grid, block, 0, st>>>(list, nlist, images, coef, out); break;
-		case 2: k_fused_gray<2><<<grid, block, 0, st>>>(list, nlist, images, coef, out); break;
-		case 3: k_fused_gray<3><<<grid, block, 0, st>>>(list, nlist, images, coef, out); break;
-		default: k_fused_gray<4><<<grid, block, 0, st>>>(list, nlist, images, coef, out); break;
+		case 1: k_fused_gray<1><<<grid, block, 0, st>>>(list, images, coef, out); break;
+		case 2: k_fused_gray<2><<<grid, block, 0, st>>>(list, images, coef, out); break;
+		case 3: k_fused_gray<3><<<grid, block, 0, st>>>(list, images, coef, out); break;
+		default: k_fused_gray<4><<<grid, block, 0, st>>>(list, images, coef, out); break;
 		}
 		break;
 	}

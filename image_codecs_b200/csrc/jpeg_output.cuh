@@ -157,7 +157,7 @@ k_generic_idct(const int32_t *__restrict__ list, const jcu_image *__restrict__ i
 		return;
 	int v[64];
 	uint32_t rows[16];
-	load_dequant(coef + cp->coef_off + (size_t)b * 64, im->qt[ci], v);
+	load_dequant(coef + cp->coef_off + (size_t)b * 64, im->qt_out[ci], v);
 	idct_block_regs(v, rows);
 	const int bx = b % cp->bw, by = b / cp->bw;
 	uint8_t *dst = planes + cp->plane_off + ((size_t)by * 8) * ((size_t)cp->bw * 8) + (size_t)bx * 8;

@@ -87,7 +87,8 @@ typedef struct
 	int32_t tile_first; /* first tile index of this image in its path's launch */
 	int32_t tiles_x, tiles_y;
 	jcu_comp comp[4];
-	uint16_t qt[4][64]; /* per COMPONENT, natural order (jpeg.c:1376) */
+	uint16_t qt[4][64]; /* per COMPONENT, natural order (jpeg.c:1376): applied by the entropy stage for baseline */
+	uint16_t qt_out[4][64]; /* table the OUTPUT stage applies: = qt for progressive (jpeg.c:1341), all ones for baseline */
 	uint64_t out_off;	  /* byte offset of the packed output in the pixel slab */
 	uint64_t data_off;  /* byte offset of the file in the bitstream slab (16-byte aligned) */
 	uint32_t data_len;

@@ -1,0 +1,98 @@
+"""CPU tests: the oracle and the test-side stream generator against the committed golden fixtures
+(tests/golden/, produced by the reference's own jpeg.c through tests/golden/make_golden.py)."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from tests import streams as S
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def sha(b) -> str:
+    return hashlib.sha256(bytes(b)).hexdigest()[:24]
+
+
+@pytest.fixture(scope="module")
+def golden():
+    return json.load(open(os.path.join(GOLD, "golden.json")))
+
+
+def test_stream_generator_is_deterministic(golden):
+    """The seeded generator must reproduce the exact bytes the golden hashes were taken from."""
+    for ent in golden["matrix"]:
+        data = S.stream(ent["fmt"], ent["w"], ent["h"], ent["kind"])
+        assert len(data) == ent["stream_len"], ent["fmt"]
+        assert sha(data) == ent["stream_sha"], (ent["fmt"], ent["w"], ent["h"])
+
+
+def test_oracle_matches_golden_matrix(oracle, golden):
+    """Whichever oracle is loaded (reference build or port) must reproduce the reference's bytes."""
+    for ent in golden["matrix"]:
+        data = S.stream(ent["fmt"], ent["w"], ent["h"], ent["kind"])
+        for rc, want in ent["decoded"].items():
+            px, x, y, c = oracle.load_from_memory(data, int(rc))
+            assert px is not None, (ent["fmt"], rc, oracle.failure_reason())
+            assert (x, y, c) == (want["x"], want["y"], want["comp"])
+            assert sha(px.tobytes()) == want["sha"], (oracle.kind, ent["fmt"], ent["w"], ent["h"], rc)
+
+
+def test_oracle_matches_golden_vectors(oracle):
+    vec = np.load(os.path.join(GOLD, "vectors.npz"))
+    names = sorted(k[: -len("_stream")] for k in vec.files if k.endswith("_stream"))
+    assert names
+    for name in names:
+        data = vec[name + "_stream"].tobytes()
+        for rc in (0, 3):
+            px, _, _, _ = oracle.load_from_memory(data, rc)
+            assert np.array_equal(px, vec[f"{name}_rc{rc}"]), (name, rc)
+
+
+def test_oracle_kernels_match_golden(oracle):
+    k = np.load(os.path.join(GOLD, "kernels.npz"))
+    for c, want in zip(k["coef"], k["idct"]):
+        assert np.array_equal(oracle.idct_block(c), want)
+    ycc = k["ycc"]
+    assert np.array_equal(oracle.ycbcr_row(ycc[:, 0].copy(), ycc[:, 1].copy(), ycc[:, 2].copy(), 3), k["rgb"])
+    assert np.array_equal(oracle.resample_row(2, k["near"], k["far"], 2), k["hv2"])
+    assert np.array_equal(oracle.resample_row(1, k["near"], k["far"], 2), k["h2"])
+    assert np.array_equal(oracle.resample_row(0, k["near"], k["far"], 1), k["v2"])
+
+
+def test_probe_stream_decodes_to_golden_hash(oracle, golden):
+    """512x512 q90 stream written by the reference's jpeg_write.c (BASELINE.json configs[0])."""
+    from oracle import oracle_lib
+
+    data = np.load(os.path.join(GOLD, "probe512.npz"))["stream"].tobytes()
+    p = golden["probe"]
+    assert len(data) == p["stream_len"] == p["survey_expected"]["stream_len"]
+    px, x, y, c = oracle.load_from_memory(data, 3)
+    assert (x, y, c) == (512, 512, 3)
+    assert oracle_lib.fnv1a64(px.tobytes()) == p["decoded_fnv1a64"]
+
+
+def test_same_coefficients_any_container(oracle):
+    """SURVEY.md section 4 invariant: baseline / restart / optimised-Huffman / progressive / non-interleaved
+    encodings of the same quantised coefficients decode to identical bytes."""
+    ref = None
+    for fmt in ("420", "420_rst16", "420_rst1", "420_opt", "420_prog", "420_prog_rst5", "420_nonint", "420_dri_late"):
+        px, _, _, _ = oracle.load_from_memory(S.stream(fmt, 233, 177, 0), 3)
+        assert px is not None, fmt
+        if ref is None:
+            ref = px
+        assert np.array_equal(px, ref), fmt
+
+
+def test_reference_build_agrees_with_its_sse2_build():
+    """generic-C and SSE2 kernels agree on encoder-produced streams."""
+    from oracle import oracle_lib
+
+    if not (oracle_lib.available("reference") and oracle_lib.available("reference_sse2")):
+        pytest.skip("oracle/_ref not built")
+    a, b = oracle_lib.load("reference"), oracle_lib.load("reference_sse2")
+    for fmt, w, h in [("420", 233, 177), ("444", 64, 48), ("gray", 129, 65), ("420_prog", 64, 48)]:
+        d = S.stream(fmt, w, h, 1)
+        assert np.array_equal(a.load_from_memory(d, 3)[0], b.load_from_memory(d, 3)[0])

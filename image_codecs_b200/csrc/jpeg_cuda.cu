@@ -14,6 +14,7 @@
 
 #include "../../include/jpeg_cuda_abi.h"
 #include "jpeg_entropy.cuh"
+#include "jpeg_entropy_baseline.cuh"
 #include "jpeg_output.cuh"
 #include "jpeg_fused.cuh"
 
@@ -39,6 +40,7 @@ struct jcu_ctx
 	bool need_clear = false;
 	std::vector<EntWork> work_h;
 	std::vector<int> wave_off; /* n_waves + 1 offsets into work_h */
+	std::vector<int> wave_nbase; /* per wave: leading work items that are baseline scans */
 	std::vector<int32_t> list_h; /* image lists per path, concatenated */
 	int list_off[4] = {0, 0, 0, 0}, list_n[4] = {0, 0, 0, 0};
 	int tiles[4] = {0, 0, 0, 0};
@@ -209,22 +211,28 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 	/* ---- CTA work items per wave: ENT_THREADS segments of one scan each ---- */
 	c->work_h.clear();
 	c->wave_off.assign((size_t)b->n_waves + 1, 0);
+	c->wave_nbase.assign((size_t)b->n_waves, 0);
 	for (int w = 0; w < b->n_waves; ++w)
 	{
 		c->wave_off[w] = (int)c->work_h.size();
-		for (int s = 0; s < b->n_scans; ++s)
+		for (int pass = 0; pass < 2; ++pass) /* baseline scans first (k_entropy_baseline), then the rest */
 		{
-			const jcu_scan &sc = b->scans[s];
-			if (sc.wave != w || !imgs[sc.image].ok)
-				continue;
-			for (uint32_t f = 0; f < sc.nseg; f += ENT_THREADS)
+			for (int s = 0; s < b->n_scans; ++s)
 			{
-				EntWork wk;
-				wk.scan = s;
-				wk.seg_first = f;
-				wk.nseg = std::min<uint32_t>(ENT_THREADS, sc.nseg - f);
-				c->work_h.push_back(wk);
+				const jcu_scan &sc = b->scans[s];
+				if (sc.wave != w || !imgs[sc.image].ok || (sc.kind == JCU_SCAN_BASELINE) != (pass == 0))
+					continue;
+				for (uint32_t f = 0; f < sc.nseg; f += ENT_THREADS)
+				{
+					EntWork wk;
+					wk.scan = s;
+					wk.seg_first = f;
+					wk.nseg = std::min<uint32_t>(ENT_THREADS, sc.nseg - f);
+					c->work_h.push_back(wk);
+				}
 			}
+			if (pass == 0)
+				c->wave_nbase[w] = (int)c->work_h.size() - c->wave_off[w];
 		}
 	}
 	c->wave_off[b->n_waves] = (int)c->work_h.size();
@@ -279,13 +287,22 @@ extern "C" int jcu_run(jcu_ctx *c)
 	const int16_t *d_coef = (const int16_t *)c->coef.p;
 	for (int w = 0; w < c->n_waves; ++w)
 	{
-		int n = c->wave_off[w + 1] - c->wave_off[w];
-		if (n <= 0)
-			continue;
-		k_entropy_segments<<<n, ENT_THREADS, 0, st>>>((const EntWork *)c->work.p + c->wave_off[w], (const jcu_scan *)c->scans.p,
-																	 d_img, (const uint32_t *)c->segs.p, (const jcu_huff_spec *)c->huff.p,
-																	 (const uint8_t *)c->bits.p, (int16_t *)c->coef.p, (int32_t *)c->err.p);
-		c->launches++;
+		const int n = c->wave_off[w + 1] - c->wave_off[w], nb = c->wave_nbase[w];
+		const EntWork *wk = (const EntWork *)c->work.p + c->wave_off[w];
+		if (nb > 0)
+		{
+			k_entropy_baseline<<<nb, ENTB_THREADS, 0, st>>>(wk, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p,
+																			(const jcu_huff_spec *)c->huff.p, (const uint8_t *)c->bits.p,
+																			(int16_t *)c->coef.p, (int32_t *)c->err.p);
+			c->launches++;
+		}
+		if (n - nb > 0)
+		{
+			k_entropy_segments<<<n - nb, ENT_THREADS, 0, st>>>(wk + nb, (const jcu_scan *)c->scans.p, d_img,
+																				(const uint32_t *)c->segs.p, (const jcu_huff_spec *)c->huff.p,
+																				(const uint8_t *)c->bits.p, (int16_t *)c->coef.p, (int32_t *)c->err.p);
+			c->launches++;
+		}
 	}
 	CK(cudaGetLastError());
 	if (c->profile)

@@ -37,17 +37,25 @@
 #define ENTB_SLOT_WORDS 36 /* 64 int16 + 4 pad words (bank spread of the 16-byte flush reads) */
 #define ENTB_MAX_MCU_BLOCKS 64
 
-struct EntbLut
+#define ENTB_DC_BITS 9
+#define ENTB_AC_BITS 11
+
+/* 16-bit lookup entry: len (5) | size (4) << 5 | kadv (7) << 9 ; 0 = code longer than the table's prefix */
+template <int BITS>
+struct EntbLutT
 {
-	uint32_t fast[512]; /* len (5) | size (4) << 5 | kadv (7) << 9 ; len == 0: code longer than 9 bits */
-	uint32_t limit[18]; /* canonical search, as HuffLut */
-	int32_t base[17];
+	uint16_t fast[1 << BITS];
+	uint32_t limit[18]; /* limit[l] = (first code of length l + count) << (16 - l); [17] = ~0 */
+	int32_t base[17];	  /* symbol index = base[l] + code */
 	uint8_t vals[256];
 };
+typedef EntbLutT<ENTB_DC_BITS> EntbDc;
+typedef EntbLutT<ENTB_AC_BITS> EntbAc;
 
 struct EntbShared
 {
-	EntbLut lut[8];				 /* [0..3] DC per scan-component slot, [4..7] AC */
+	EntbDc dc[4];					 /* per scan-component slot */
+	EntbAc ac[4];
 	uint32_t zq[4][128];			 /* per slot: natural index | quantiser << 16, indexed by zig-zag position;
 											 positions 64..127 alias natural 63 like the reference's padded table (jpeg.c:303) */
 	uint32_t blk[ENTB_MAX_MCU_BLOCKS]; /* per block of an MCU: slot | dx << 4 | dy << 8 | dc lut << 12 | ac lut << 16 */
@@ -72,7 +80,8 @@ __device__ __forceinline__ uint32_t entb_entry(int sym, int l, bool is_dc)
 	return (uint32_t)l | ((uint32_t)size << 5) | ((uint32_t)kadv << 9);
 }
 
-__device__ __forceinline__ void entb_lut_build(EntbLut *L, const jcu_huff_spec *spec, bool is_dc, int tid, int nthreads)
+template <int BITS>
+__device__ __forceinline__ void entb_lut_build(EntbLutT<BITS> *L, const jcu_huff_spec *spec, bool is_dc, int tid, int nthreads)
 {
 	__shared__ uint32_t s_first[17];
 	__shared__ uint32_t s_count[17];
@@ -99,12 +108,12 @@ __device__ __forceinline__ void entb_lut_build(EntbLut *L, const jcu_huff_spec *
 	for (int i = tid; i < 256; i += nthreads)
 		L->vals[i] = spec->vals[i];
 	__syncthreads();
-	for (int e = tid; e < 512; e += nthreads)
+	for (int e = tid; e < (1 << BITS); e += nthreads)
 	{
 		uint32_t entry = 0;
-		for (int l = 1; l <= 9; ++l)
+		for (int l = 1; l <= BITS; ++l)
 		{
-			uint32_t code = (uint32_t)e >> (9 - l);
+			uint32_t code = (uint32_t)e >> (BITS - l);
 			uint32_t rel = code - s_first[l];
 			if (code >= s_first[l] && rel < s_count[l])
 			{
@@ -112,77 +121,60 @@ __device__ __forceinline__ void entb_lut_build(EntbLut *L, const jcu_huff_spec *
 				break;
 			}
 		}
-		L->fast[e] = entry;
+		L->fast[e] = (uint16_t)entry;
 	}
 	__syncthreads();
 }
 
-/* ---- bit reader: 64-bit MSB-aligned buffer, next aligned word already in a register ---- */
+
+/* ---- bit reader: 64-bit MSB-aligned buffer over one file (base pointer is CTA-uniform),
+ *      next aligned word already in a register ---- */
 struct EBR
 {
-	const uint8_t *p;
-	const uint8_t *end;
+	uint32_t pos, len; /* byte offset in the file; file length */
 	uint64_t buf;
 	int nbits;
-	uint32_t w; /* word at p if p is 4-aligned and p + 4 <= end, else 0xffffffff (forces the byte path) */
+	uint32_t w; /* word at pos if pos is 4-aligned and pos + 4 <= len, else 0xffffffff (forces the byte path) */
 };
 
-__device__ __forceinline__ uint32_t ebr_prefetch(const uint8_t *p, const uint8_t *end)
+__device__ __forceinline__ uint32_t ebr_prefetch(const uint8_t *__restrict__ base, uint32_t pos, uint32_t len)
 {
-	return ((((uintptr_t)p & 3) == 0) && p + 4 <= end) ? __ldg(reinterpret_cast<const uint32_t *>(p)) : 0xffffffffu;
+	return (((pos & 3u) == 0u) && pos + 4u <= len) ? __ldg(reinterpret_cast<const uint32_t *>(base + pos)) : 0xffffffffu;
 }
 
 /* byte path with the stuffing rules of stbi__grow_buffer_unsafe (jpeg.c:167-187): FF 00 -> FF, FF FF.. fill,
-   FF xx -> marker: stop consuming (p = end) and feed zero bits; past the end of the file reads 0 (common.c:39) */
-__device__ __forceinline__ void ebr_slow(EBR &br)
+   FF xx -> marker: stop consuming (pos = len) and feed zero bits; past the end of the file reads 0 (common.c:39).
+   Loops until at least 32 bits are valid and the reader is back on an aligned word (or out of data). */
+__device__ __forceinline__ void ebr_slow(const uint8_t *__restrict__ base, EBR &br)
 {
 	do
 	{
 		uint32_t b = 0;
-		if (br.p < br.end)
+		if (br.pos < br.len)
 		{
-			b = *br.p++;
+			b = base[br.pos++];
 			if (b == 0xff)
 			{
-				const uint8_t *q = br.p;
-				uint32_t c = q < br.end ? *q : 0u;
+				uint32_t q = br.pos;
+				uint32_t c = q < br.len ? base[q] : 0u;
 				while (c == 0xff)
 				{
 					++q;
-					c = q < br.end ? *q : 0u;
+					c = q < br.len ? base[q] : 0u;
 				}
 				if (c == 0)
-					br.p = q < br.end ? q + 1 : br.end;
+					br.pos = q < br.len ? q + 1 : br.len;
 				else
 				{
-					br.p = br.end;
+					br.pos = br.len;
 					b = 0;
 				}
 			}
 		}
 		br.buf |= (uint64_t)b << (56 - br.nbits);
 		br.nbits += 8;
-	} while (br.nbits <= 56 && (br.p >= br.end || ((uintptr_t)br.p & 3) != 0));
-	br.w = ebr_prefetch(br.p, br.end);
-}
-
-/* make at least 32 bits valid */
-__device__ __forceinline__ void ebr_refill(EBR &br)
-{
-	while (br.nbits < 32)
-	{
-		const uint32_t w = br.w;
-		const uint32_t ff = ((w & 0x7f7f7f7fu) + 0x01010101u) & w & 0x80808080u;
-		if (ff == 0)
-		{
-			br.buf |= (uint64_t)__byte_perm(w, 0, 0x0123) << (32 - br.nbits);
-			br.nbits += 32;
-			br.p += 4;
-			br.w = ebr_prefetch(br.p, br.end);
-		}
-		else
-			ebr_slow(br);
-	}
+	} while (br.nbits <= 56 && (br.nbits < 32 || br.pos >= br.len || (br.pos & 3u) != 0u));
+	br.w = ebr_prefetch(base, br.pos, br.len);
 }
 
 __device__ __forceinline__ uint32_t shr_clamp(uint32_t x, uint32_t n) /* n >= 32 gives 0 (PTX shr semantics) */
@@ -195,22 +187,40 @@ __device__ __forceinline__ uint32_t shr_clamp(uint32_t x, uint32_t n) /* n >= 32
 /*
  * One Huffman symbol plus its magnitude bits.  Returns false for "bad huffman code" (jpeg.c:317,351).
  * value = extended magnitude (0 when the symbol carries no bits); kadv = k advance (AC tables).
+ * The refill is predicated, not branched: nearly every lock-step iteration has SOME lane short of
+ * bits, so a branch would serialise a 3-lane refill against the rest of the warp every time.
  */
-__device__ __forceinline__ bool entb_symbol(EBR &br, const EntbLut *__restrict__ L, bool is_dc, int &value, int &kadv)
+template <int BITS, bool IS_DC>
+__device__ __forceinline__ bool entb_symbol(const uint8_t *__restrict__ base, EBR &br, const EntbLutT<BITS> *__restrict__ L,
+														  int &value, int &kadv)
 {
-	if (br.nbits < 32)
-		ebr_refill(br);
+	{
+		const bool need = br.nbits < 32;
+		const uint32_t w = br.w;
+		const uint32_t ff = ((w & 0x7f7f7f7fu) + 0x01010101u) & w & 0x80808080u;
+		if (need && ff)
+			ebr_slow(base, br); /* leaves >= 32 bits */
+		else
+		{
+			const uint64_t ins = (uint64_t)__byte_perm(w, 0, 0x0123) << ((32 - br.nbits) & 63);
+			br.buf |= need ? ins : 0ull;
+			br.nbits += need ? 32 : 0;
+			br.pos += need ? 4u : 0u;
+			if (need)
+				br.w = ebr_prefetch(base, br.pos, br.len);
+		}
+	}
 	const uint32_t top = (uint32_t)(br.buf >> 32);
-	uint32_t e = L->fast[top >> 23];
-	if ((e & 31u) == 0)
+	uint32_t e = L->fast[top >> (32 - BITS)];
+	if (e == 0)
 	{
 		const uint32_t t16 = top >> 16;
-		int l = 10;
+		int l = BITS + 1;
 		while (t16 >= L->limit[l])
 			++l;
 		if (l > 16)
 			return false;
-		e = entb_entry(L->vals[(L->base[l] + (int)(t16 >> (16 - l))) & 255], l, is_dc);
+		e = entb_entry(L->vals[(L->base[l] + (int)(t16 >> (16 - l))) & 255], l, IS_DC);
 	}
 	const int len = (int)(e & 31u), size = (int)((e >> 5) & 15u);
 	kadv = (int)(e >> 9);
@@ -246,13 +256,13 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 	const jcu_image *im = &images[sc->image];
 	const int ncs = sc->ncomp;
 
-	/* ---- per-scan tables, once per CTA ---- */
-	int lut_dc[4], lut_ac[4]; /* resolved at compile time after unrolling: no dynamic indexing below */
+	/* ---- per-scan tables, once per CTA (slots sharing a DHT table share one lookup) ---- */
+	int lut_dc[4], lut_ac[4]; /* indices resolved after unrolling: no dynamic indexing */
 #pragma unroll
 	for (int i = 0; i < 4; ++i)
 	{
 		lut_dc[i] = i;
-		lut_ac[i] = 4 + i;
+		lut_ac[i] = i;
 		if (i < ncs)
 		{
 #pragma unroll
@@ -261,13 +271,13 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 				{
 					if (sc->dc_spec[j] == sc->dc_spec[i] && lut_dc[i] == i)
 						lut_dc[i] = lut_dc[j];
-					if (sc->ac_spec[j] == sc->ac_spec[i] && lut_ac[i] == 4 + i)
+					if (sc->ac_spec[j] == sc->ac_spec[i] && lut_ac[i] == i)
 						lut_ac[i] = lut_ac[j];
 				}
 			if (lut_dc[i] == i && sc->dc_spec[i] >= 0)
-				entb_lut_build(&sh.lut[i], &huff[sc->dc_spec[i]], true, tid, ENTB_THREADS);
-			if (lut_ac[i] == 4 + i && sc->ac_spec[i] >= 0)
-				entb_lut_build(&sh.lut[4 + i], &huff[sc->ac_spec[i]], false, tid, ENTB_THREADS);
+				entb_lut_build(&sh.dc[i], &huff[sc->dc_spec[i]], true, tid, ENTB_THREADS);
+			if (lut_ac[i] == i && sc->ac_spec[i] >= 0)
+				entb_lut_build(&sh.ac[i], &huff[sc->ac_spec[i]], false, tid, ENTB_THREADS);
 		}
 	}
 	for (int i = tid; i < ncs * 128; i += ENTB_THREADS)
@@ -279,21 +289,22 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 	if (tid == 0)
 	{
 		int n = 0;
-		for (int i = 0; i < ncs; ++i)
-		{
-			const jcu_comp *cp = &im->comp[sc->comp[i]];
-			const int hn = ncs == 1 ? 1 : cp->h, vn = ncs == 1 ? 1 : cp->v;
-			s_coff[i] = cp->coef_off;
-			s_bw[i] = cp->bw;
-			s_hn[i] = hn;
-			s_vn[i] = vn;
-			const int ld = i == 0 ? lut_dc[0] : i == 1 ? lut_dc[1] : i == 2 ? lut_dc[2] : lut_dc[3];
-			const int la = i == 0 ? lut_ac[0] : i == 1 ? lut_ac[1] : i == 2 ? lut_ac[2] : lut_ac[3];
-			for (int y = 0; y < vn; ++y)
-				for (int x = 0; x < hn; ++x)
-					if (n < ENTB_MAX_MCU_BLOCKS)
-						sh.blk[n++] = (uint32_t)i | ((uint32_t)x << 4) | ((uint32_t)y << 8) | ((uint32_t)ld << 12) | ((uint32_t)la << 16);
-		}
+#pragma unroll
+		for (int i = 0; i < 4; ++i)
+			if (i < ncs)
+			{
+				const jcu_comp *cp = &im->comp[sc->comp[i]];
+				const int hn = ncs == 1 ? 1 : cp->h, vn = ncs == 1 ? 1 : cp->v;
+				s_coff[i] = cp->coef_off;
+				s_bw[i] = cp->bw;
+				s_hn[i] = hn;
+				s_vn[i] = vn;
+				for (int y = 0; y < vn; ++y)
+					for (int x = 0; x < hn; ++x)
+						if (n < ENTB_MAX_MCU_BLOCKS)
+							sh.blk[n++] = (uint32_t)i | ((uint32_t)x << 4) | ((uint32_t)y << 8) | ((uint32_t)lut_dc[i] << 12) |
+											  ((uint32_t)lut_ac[i] << 16);
+			}
 		sh.nblk = n;
 	}
 	__syncthreads();
@@ -306,17 +317,14 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 	const int u0 = ri ? (int)seg * ri : 0;
 	const int u1 = ri ? min(u0 + ri, total) : total;
 	const int nblk = sh.nblk;
+	const uint8_t *__restrict__ base = bitstream + im->data_off;
 
 	EBR br;
-	{
-		const uint8_t *file = bitstream + im->data_off;
-		const uint32_t off = active ? seg_start[sc->seg_first + seg] : im->data_len;
-		br.p = file + off;
-		br.end = file + im->data_len;
-		br.buf = 0;
-		br.nbits = 0;
-		br.w = ebr_prefetch(br.p, br.end);
-	}
+	br.len = im->data_len;
+	br.pos = active ? seg_start[sc->seg_first + seg] : br.len;
+	br.buf = 0;
+	br.nbits = 0;
+	br.w = ebr_prefetch(base, br.pos, br.len);
 	int dc0 = 0, dc1 = 0, dc2 = 0, dc3 = 0;
 	bool failed = false;
 
@@ -335,15 +343,15 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 		{
 			const uint32_t ent = sh.blk[b];
 			const int s = (int)(ent & 15u);
-			const EntbLut *Ldc = &sh.lut[(ent >> 12) & 7u];
-			const EntbLut *Lac = &sh.lut[(ent >> 16) & 7u];
+			const EntbDc *Ldc = &sh.dc[(ent >> 12) & 3u];
+			const EntbAc *Lac = &sh.ac[(ent >> 16) & 3u];
 			const uint32_t *zq = sh.zq[s];
 			const bool live = live_u && !failed;
 			bool ok = false;
 			if (live)
 			{
 				int diff, kadv;
-				ok = entb_symbol(br, Ldc, true, diff, kadv);
+				ok = entb_symbol<ENTB_DC_BITS, true>(base, br, Ldc, diff, kadv);
 				if (ok)
 				{
 					int dcp = s == 0 ? dc0 : s == 1 ? dc1 : s == 2 ? dc2 : dc3;
@@ -357,7 +365,7 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 					do
 					{
 						int val;
-						if (!entb_symbol(br, Lac, false, val, kadv))
+						if (!entb_symbol<ENTB_AC_BITS, false>(base, br, Lac, val, kadv))
 						{
 							ok = false;
 							break;

@@ -421,7 +421,17 @@ extern "C" int jcu_test_idct_blocks(jcu_ctx *c, const int16_t *coef, const uint1
 	CK(cudaMalloc(&d_c, (size_t)nblocks * 128));
 	CK(cudaMalloc(&d_q, 128));
 	CK(cudaMalloc(&d_o, (size_t)nblocks * 64));
-	CK(cudaMemcpy(d_c, coef, (size_t)nblocks * 128, cudaMemcpyHostToDevice));
+	{
+		/* callers pass natural-order blocks: store them in the slab layout (jpeg_coef_layout.cuh) */
+		std::vector<int16_t> sw((size_t)nblocks * 64);
+		for (int b = 0; b < nblocks; ++b)
+		{
+			const unsigned key = coef_key(d_c + (size_t)b * 64);
+			for (int r = 0; r < 8; ++r)
+				memcpy(&sw[(size_t)b * 64 + ((r ^ (int)key) * 8)], coef + (size_t)b * 64 + r * 8, 16);
+		}
+		CK(cudaMemcpy(d_c, sw.data(), (size_t)nblocks * 128, cudaMemcpyHostToDevice));
+	}
 	CK(cudaMemcpy(d_q, qt, 128, cudaMemcpyHostToDevice));
 	k_test_idct<<<(nblocks + 63) / 64, 64, 0, c->stream>>>(d_c, d_q, nblocks, d_o);
 	CK(cudaStreamSynchronize(c->stream));
@@ -454,5 +464,14 @@ extern "C" int jcu_read_coefs(jcu_ctx *c, size_t elem_off, size_t elems, int16_t
 	CK(cudaSetDevice(c->device));
 	CK(cudaMemcpyAsync(dst, (const int16_t *)c->coef.p + elem_off, elems * sizeof(int16_t), cudaMemcpyDeviceToHost, c->stream));
 	CK(cudaStreamSynchronize(c->stream));
+	/* undo the slab's chunk permutation (jpeg_coef_layout.cuh); callers pass whole blocks */
+	for (size_t b = 0; b + 64 <= elems; b += 64)
+	{
+		const unsigned key = coef_key((const int16_t *)c->coef.p + elem_off + b);
+		int16_t tmp[64];
+		memcpy(tmp, dst + b, sizeof(tmp));
+		for (int r = 0; r < 8; ++r)
+			memcpy(dst + b + r * 8, tmp + ((r ^ (int)key) * 8), 16);
+	}
 	return 0;
 }

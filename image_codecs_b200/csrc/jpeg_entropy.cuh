@@ -32,6 +32,7 @@
 #include <stdint.h>
 
 #include "../../include/jpeg_cuda_abi.h"
+#include "jpeg_coef_layout.cuh"
 
 #define ENT_THREADS 128
 #define ENT_LUT_BITS 9
@@ -308,7 +309,7 @@ __device__ __forceinline__ int prog_ac_first(BitReader &br, const HuffLut *L, co
 			k += r;
 			int zig = zz[k < 79 ? k : 79];
 			++k;
-			blk[zig] = (int16_t)(receive_extend(br, s) * (1 << al));
+			blk[coef_pos(zig, coef_key(blk))] = (int16_t)(receive_extend(br, s) * (1 << al));
 		}
 	} while (k <= se);
 	return 1;
@@ -330,7 +331,7 @@ __device__ __forceinline__ int prog_ac_refine(BitReader &br, const HuffLut *L, c
 		--eob_run;
 		for (int k = ss; k <= se; ++k)
 		{
-			int16_t *p = &blk[zz[k]];
+			int16_t *p = &blk[coef_pos(zz[k], coef_key(blk))];
 			if (*p != 0)
 				if (br_bits(br, 1))
 					refine_one(p, bit);
@@ -362,7 +363,7 @@ __device__ __forceinline__ int prog_ac_refine(BitReader &br, const HuffLut *L, c
 		}
 		while (k <= se)
 		{
-			int16_t *p = &blk[zz[k++]];
+			int16_t *p = &blk[coef_pos(zz[k++], coef_key(blk))];
 			if (*p != 0)
 			{
 				if (br_bits(br, 1))
@@ -592,7 +593,7 @@ k_entropy_segments(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 							{
 								uint4 v = s4[q];
 								if (ok)
-									d4[q] = v;
+									d4[q ^ coef_key(blk)] = v;
 								reinterpret_cast<uint4 *>(slot_w)[q] = make_uint4(0u, 0u, 0u, 0u);
 							}
 						}
@@ -612,13 +613,16 @@ k_entropy_segments(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 							else
 							{
 								dcp += receive_extend(br, t);
-								blk[0] = (int16_t)(dcp * (1 << al));
+								blk[coef_pos(0, coef_key(blk))] = (int16_t)(dcp * (1 << al));
 							}
 						}
 						else if (kind == JCU_SCAN_PROG_DC_REFINE)
 						{
 							if (br_bits(br, 1))
-								blk[0] = (int16_t)(blk[0] + (int16_t)(1 << al));
+							{
+								int16_t *p0 = &blk[coef_pos(0, coef_key(blk))];
+								*p0 = (int16_t)(*p0 + (int16_t)(1 << al));
+							}
 						}
 						else if (kind == JCU_SCAN_PROG_AC_FIRST)
 							ok = prog_ac_first(br, Lac, sh.zz, blk, ss, se, al, eob_run);

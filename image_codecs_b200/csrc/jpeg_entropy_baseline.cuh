@@ -383,12 +383,13 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 				const int bx = ux * s_hn[s] + (int)((ent >> 4) & 15u), by = uy * s_vn[s] + (int)((ent >> 8) & 15u);
 				uint4 *d4 = reinterpret_cast<uint4 *>(coef + s_coff[s] + ((size_t)by * s_bw[s] + bx) * 64);
 				uint4 *s4 = reinterpret_cast<uint4 *>(slot_w);
+				const unsigned key = coef_key(d4);
 #pragma unroll
 				for (int q = 0; q < 8; ++q)
 				{
 					const uint4 v = s4[q];
 					if (ok)
-						d4[q] = v;
+						d4[q ^ key] = v; /* slab chunk permutation (jpeg_coef_layout.cuh) */
 					s4[q] = make_uint4(0u, 0u, 0u, 0u);
 				}
 			}

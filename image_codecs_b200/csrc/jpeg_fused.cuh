@@ -263,7 +263,7 @@ k_fused_420(const int32_t *__restrict__ list, const jcu_image *__restrict__ imag
 						src = (ci ? base2 : base1) + ((size_t)by * cbw + bx) * 64;
 				}
 				if (src)
-					cp_async16(&sCoef[slot * 8 + (j ^ (slot & 7))], src + j * 8);
+					cp_async16(&sCoef[slot * 8 + (j ^ (slot & 7))], src + ((j ^ (int)coef_key(src)) * 8));
 			}
 		}
 		if (DEQ)

@@ -18,6 +18,7 @@
 #include <stdint.h>
 
 #include "../../include/jpeg_cuda_abi.h"
+#include "jpeg_coef_layout.cuh"
 
 /* ---- 1-D inverse DCT butterfly, 12-bit constants f2f(x) = (int)(x*4096+0.5) (jpeg.c:574-613).
  * `bias` is added to the four even-part sums (x0..x3 in the reference): 512 in the column pass,
@@ -94,10 +95,11 @@ __device__ __forceinline__ void load_dequant(const int16_t *__restrict__ blk, co
 															int (&v)[64])
 {
 	const uint4 *p = reinterpret_cast<const uint4 *>(blk);
+	const unsigned key = coef_key(blk);
 #pragma unroll
 	for (int q = 0; q < 8; ++q)
 	{
-		uint4 w = p[q];
+		uint4 w = p[q ^ key]; /* chunk permutation of the slab layout (jpeg_coef_layout.cuh) */
 		uint32_t ws[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
 		for (int j = 0; j < 4; ++j)

@@ -17,6 +17,7 @@
 #include "jpeg_entropy_baseline.cuh"
 #include "jpeg_output.cuh"
 #include "jpeg_fused.cuh"
+#include "jpeg_fused420.cuh"
 
 struct DevBuf
 {
@@ -51,6 +52,7 @@ struct jcu_ctx
 	long long max_pixels_generic = 0;
 	int launches = 0;
 	int force_generic = 0;
+	int rows_per_band = 8; /* 4:2:0 strip kernel: MCU rows per CTA, chosen per batch */
 	char errstr[256] = {0};
 };
 
@@ -172,6 +174,16 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 	c->max_pixels_generic = 0;
 	for (int p = 0; p < 4; ++p)
 		c->tiles[p] = c->path_deq[p] = c->path_maxtiles[p] = 0;
+	{
+		/* band height of the 4:2:0 strip kernel: tall bands amortise the two-row chroma prologue, but the
+		   grid must still fill 148 SMs x 2 CTAs several times over */
+		long long strip_rows = 0;
+		for (int i = 0; i < b->n_images; ++i)
+			if (imgs[i].ok && !c->force_generic && imgs[i].path == JCU_PATH_FUSED_420)
+				strip_rows += (long long)((imgs[i].mcu_x + S420_MS - 1) / S420_MS) * imgs[i].mcu_y;
+		long long rb = strip_rows / (148 * 2 * 8);
+		c->rows_per_band = (int)std::min<long long>(std::max<long long>(rb, 2), 24);
+	}
 	for (int i = 0; i < b->n_images; ++i)
 	{
 		jcu_image &im = imgs[i];
@@ -195,6 +207,11 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 			fused_tile_dims(p, &tw, &th);
 			im.tiles_x = (im.width + tw - 1) / tw;
 			im.tiles_y = (im.height + th - 1) / th;
+			if (p == JCU_PATH_FUSED_420)
+			{
+				im.tiles_x = (im.mcu_x + S420_MS - 1) / S420_MS;						/* strips */
+				im.tiles_y = (im.mcu_y + c->rows_per_band - 1) / c->rows_per_band; /* bands */
+			}
 			im.tile_first = c->tiles[p];
 			c->tiles[p] += im.tiles_x * im.tiles_y;
 			c->path_maxtiles[p] = std::max(c->path_maxtiles[p], im.tiles_x * im.tiles_y);
@@ -323,7 +340,11 @@ extern "C" int jcu_run(jcu_ctx *c)
 		if (c->list_n[p] > 0)
 		{
 			const int32_t *lst = (const int32_t *)c->lists.p + c->list_off[p];
-			cudaError_t e = fused_launch(p, c->path_maxtiles[p], lst, c->list_n[p], d_img, d_coef, (uint8_t *)c->out.p, st, c->path_n[p], c->path_deq[p]);
+			cudaError_t e = p == JCU_PATH_FUSED_420
+									  ? fused420_launch(c->path_maxtiles[p], lst, c->list_n[p], d_img, d_coef, (uint8_t *)c->out.p, st,
+															  c->path_n[p], c->path_deq[p], c->rows_per_band)
+									  : fused_launch(p, c->path_maxtiles[p], lst, c->list_n[p], d_img, d_coef, (uint8_t *)c->out.p, st,
+														  c->path_n[p], c->path_deq[p]);
 			if (e != cudaSuccess)
 				return set_err(c, e, "fused_launch");
 			c->launches++;

@@ -1,0 +1,439 @@
+/*
+ * jpeg_fused420.cuh -- fused output stage for 4:2:0 YCbCr (sm_100a), strip-persistent edition.
+ *
+ * One kernel does dequantise -> integer 8x8 IDCT (stbi__idct_block, jpeg.c:615) -> h2v2 chroma
+ * upsample (stbi__resample_row_hv_2, jpeg.c:1816, row selection jpeg.c:2301-2318) -> YCbCr->RGB
+ * (stbi__YCbCr_to_RGB_row, jpeg.c:1976) -> packed RGB/RGBA stores, touching HBM only to read each
+ * coefficient block once and write each pixel once.
+ *
+ * Work decomposition.  A CTA owns a vertical STRIP of one image (<= S420_MS MCUs wide) inside a
+ * BAND of MCU rows and walks down it one MCU row per iteration:
+ *
+ *   TMA    one thread arms an mbarrier and issues <= 4 bulk copies (cp.async.bulk, SASS UBLKCP): the
+ *          two luma block rows of MCU row r and the Cb / Cr block rows of MCU row r+1 (plus one
+ *          halo block each side).  Block rows are contiguous in the slab, so a row is ONE copy.
+ *   IDCT   one thread = one 8x8 block, all 64 coefficients in registers (column pass, row pass);
+ *          luma of row r goes to the sY sample plane, chroma of row r+1 to a 2-slot ring.  Cb and
+ *          Cr of one position sit in adjacent lanes and swap half their rows by warp shuffle, so
+ *          the ring holds ONE word per chroma sample: 16*Cb+8 | (16*(Cr-128)+8) << 16.
+ *   pixel  one task = 8 pixels of one row: the h2v2 filter runs on both chroma fields of the word at
+ *          once (3*near+far, then 3*t[i]+t[i+-1]; the +8 per sample becomes the filter's rounding
+ *          term and the x16 puts the result in bytes 1 and 3), colour, saturating pack, store.
+ *
+ * The h2v2 filter reaches one chroma row above and below an MCU row (jpeg.c:11).  Walking DOWN the
+ * image removes that halo from the hot loop: chroma of row r+1 is computed one iteration early
+ * (its first row is the lower neighbour of row r), and the last row of row r-1 is kept in a line
+ * buffer.  Only the band's first row pays a prologue (two chroma-only iterations) and each strip
+ * pays one halo block column per side; nothing is spilled to HBM and no block is re-read from HBM
+ * except those halo columns (L2 hits).  Image edges clamp on the REAL component size (w_lores, cy --
+ * never the MCU padding) by replicating one column in the ring.
+ *
+ * No tensor cores: the IDCT must reproduce the reference's fixed-point rounding (north_star).
+ * Algorithmic HBM bytes: 128 B x coefficient blocks + n B x pixels.
+ */
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/jpeg_cuda_abi.h"
+#include "jpeg_coef_layout.cuh"
+#include "jpeg_output.cuh"
+
+#define S420_THREADS 256
+#define S420_MS 40									  /* MCUs per strip (640 px) */
+#define S420_MC (S420_MS + 2)						  /* chroma block positions incl. one halo each side */
+#define S420_SLOTS (4 * S420_MS + 2 * S420_MC) /* staged coefficient blocks per iteration (244) */
+#define S420_YW (S420_MS * 16)					  /* luma sample row, bytes */
+#define S420_CW 340									  /* chroma ring row stride in words (>= 8 * S420_MC, == 20 mod 32) */
+#define S420_OFF_Y (S420_SLOTS * 128)
+#define S420_OFF_C (S420_OFF_Y + 16 * S420_YW)
+#define S420_OFF_P (S420_OFF_C + 2 * 8 * S420_CW * 4)
+#define S420_OFF_Q (S420_OFF_P + 2 * S420_CW * 4)
+#define S420_OFF_BAR (S420_OFF_Q + 3 * 64 * 2)
+#define S420_SMEM_BYTES (S420_OFF_BAR + 16)
+
+/* ---- mbarrier + bulk async copy (TMA, non-tensor form) ---- */
+__device__ __forceinline__ uint32_t s420_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void s420_mbar_init(uint64_t *bar, unsigned count)
+{
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s420_smem_u32(bar)), "r"(count) : "memory");
+	asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void s420_mbar_expect_tx(uint64_t *bar, unsigned bytes)
+{
+	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s420_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void s420_mbar_wait(uint64_t *bar, unsigned parity)
+{
+	asm volatile(
+		 "{\n"
+		 ".reg .pred p;\n"
+		 "WAIT_%=:\n"
+		 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+		 "@p bra DONE_%=;\n"
+		 "bra WAIT_%=;\n"
+		 "DONE_%=:\n"
+		 "}\n" ::"r"(s420_smem_u32(bar)),
+		 "r"(parity)
+		 : "memory");
+}
+/* global -> shared bulk copy, completion counted in bytes on the mbarrier; size multiple of 16 */
+__device__ __forceinline__ void s420_bulk_g2s(void *dst_smem, const void *src_gmem, unsigned bytes, uint64_t *bar)
+{
+	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(s420_smem_u32(dst_smem)),
+					 "l"(src_gmem), "r"(bytes), "r"(s420_smem_u32(bar))
+					 : "memory");
+}
+
+/* saturate two s32 to u8 and pack below the low half of c: result bytes = [sat(lo), sat(hi), c.b0, c.b1] */
+__device__ __forceinline__ uint32_t s420_pack2(int hi, int lo, uint32_t c)
+{
+	uint32_t d;
+	asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(hi), "r"(lo), "r"(c));
+	return d;
+}
+__device__ __forceinline__ uint32_t s420_pack4(int b0, int b1, int b2, int b3) { return s420_pack2(b1, b0, s420_pack2(b3, b2, 0u)); }
+
+/* 64 coefficients of one staged block -> sign-extended ints.  `key` undoes the slab's chunk
+   permutation (the copy in shared memory is byte-identical to HBM); DEQ applies (short)(c*q) for
+   progressive files (stbi__jpeg_dequantize, jpeg.c:1323) */
+template <bool DEQ>
+__device__ __forceinline__ void s420_load_block(const uint4 *__restrict__ slot, unsigned key, const uint16_t *__restrict__ q,
+																int (&v)[64])
+{
+#pragma unroll
+	for (int j = 0; j < 8; ++j)
+	{
+		const uint4 w = slot[j ^ key];
+		const uint32_t ws[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+		for (int i = 0; i < 4; ++i)
+		{
+			int c0 = (int)(int16_t)(ws[i] & 0xffffu);
+			int c1 = ((int)ws[i]) >> 16;
+			if (DEQ)
+			{
+				c0 = (int)(int16_t)(c0 * (int)q[j * 8 + 2 * i]);
+				c1 = (int)(int16_t)(c1 * (int)q[j * 8 + 2 * i + 1]);
+			}
+			v[j * 8 + 2 * i] = c0;
+			v[j * 8 + 2 * i + 1] = c1;
+		}
+	}
+}
+
+/* column pass + row pass (jpeg.c:615-679) on registers -> 8 rows of 8 saturated samples, two words per row */
+__device__ __forceinline__ void s420_idct(int (&v)[64], uint32_t (&rows)[16])
+{
+	int o[8];
+#pragma unroll
+	for (int c = 0; c < 8; ++c)
+	{
+		idct_1d(v[c], v[c + 8], v[c + 16], v[c + 24], v[c + 32], v[c + 40], v[c + 48], v[c + 56], 512, o);
+#pragma unroll
+		for (int r = 0; r < 8; ++r)
+			v[c + 8 * r] = o[r] >> 10;
+	}
+#pragma unroll
+	for (int r = 0; r < 8; ++r)
+	{
+		idct_1d(v[8 * r], v[8 * r + 1], v[8 * r + 2], v[8 * r + 3], v[8 * r + 4], v[8 * r + 5], v[8 * r + 6], v[8 * r + 7],
+				  65536 + (128 << 17), o);
+		rows[2 * r] = s420_pack4(o[0] >> 17, o[1] >> 17, o[2] >> 17, o[3] >> 17);
+		rows[2 * r + 1] = s420_pack4(o[4] >> 17, o[5] >> 17, o[6] >> 17, o[7] >> 17);
+	}
+}
+
+/* four chroma samples (bytes of cbw / crw) -> four ring words 16*Cb+8 | (16*(Cr-128)+8) << 16 */
+__device__ __forceinline__ uint4 s420_chroma_words(uint32_t cbw, uint32_t crw)
+{
+	const uint32_t K = 0xF8080008u; /* 8 | (8 - 16*128) << 16 */
+	uint4 r;
+	r.x = (__byte_perm(cbw, crw, 0x0400) & 0x00ff00ffu) * 16u + K;
+	r.y = (__byte_perm(cbw, crw, 0x0501) & 0x00ff00ffu) * 16u + K;
+	r.z = (__byte_perm(cbw, crw, 0x0602) & 0x00ff00ffu) * 16u + K;
+	r.w = (__byte_perm(cbw, crw, 0x0703) & 0x00ff00ffu) * 16u + K;
+	return r;
+}
+
+/*
+ * grid: (max strips*bands per image, images on this path).  DEQ = coefficients are raw (progressive);
+ * otherwise the entropy stage already stored (short)(c*q) as the reference does for baseline.
+ */
+template <int N, bool DEQ>
+__global__ void __launch_bounds__(S420_THREADS, 2)
+k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__ images, const int16_t *__restrict__ coef,
+					  uint8_t *__restrict__ out, int rows_per_band)
+{
+	extern __shared__ __align__(128) unsigned char s420_smem[];
+	uint4 *sCoef = reinterpret_cast<uint4 *>(s420_smem);
+	uint8_t *sY = s420_smem + S420_OFF_Y;											  /* [16][S420_YW] */
+	uint32_t *sC = reinterpret_cast<uint32_t *>(s420_smem + S420_OFF_C);	  /* [2][8][S420_CW] */
+	uint32_t *sP = reinterpret_cast<uint32_t *>(s420_smem + S420_OFF_P);	  /* [2][S420_CW] */
+	uint16_t(*sQ)[64] = reinterpret_cast<uint16_t(*)[64]>(s420_smem + S420_OFF_Q);
+	uint64_t *bar = reinterpret_cast<uint64_t *>(s420_smem + S420_OFF_BAR);
+
+	const jcu_image *im = &images[list[blockIdx.y]];
+	const int strips = im->tiles_x;
+	if ((int)blockIdx.x >= strips * im->tiles_y)
+		return;
+	const int strip = blockIdx.x % strips, band = blockIdx.x / strips;
+	const int tid = threadIdx.x;
+	const int W = im->width, H = im->height;
+	const int mcu_y = im->mcu_y;
+	const int ybw = im->comp[0].bw, cbw = im->comp[1].bw;
+	const int wl = im->comp[1].w_lores, cy = im->comp[1].cy;
+	const int m0 = strip * S420_MS, Ms = min(S420_MS, im->mcu_x - m0), Mc = Ms + 2;
+	const int r0 = band * rows_per_band, r1 = min(r0 + rows_per_band, mcu_y);
+	const int c0 = max(m0 - 1, 0), c1 = min(m0 + Ms + 1, cbw);
+	const int rc_last = min(r1, mcu_y - 1); /* last chroma MCU row this band touches */
+	const int16_t *baseY = coef + im->comp[0].coef_off;
+	const int16_t *baseCb = coef + im->comp[1].coef_off;
+	const int16_t *baseCr = coef + im->comp[2].coef_off;
+
+	if (tid == 0)
+		s420_mbar_init(bar, 1);
+	if (DEQ)
+		for (int i = tid; i < 192; i += S420_THREADS)
+			sQ[i >> 6][i & 63] = im->qt_out[i >> 6][i & 63];
+	__syncthreads();
+
+	/* thread 0: arm the barrier and issue the bulk copies of iteration r */
+	auto issue = [&](int r) {
+		const bool doY = r >= r0, doC = (r + 1) <= rc_last;
+		const unsigned ybytes = (unsigned)(2 * Ms * 128), cbytes = (unsigned)((c1 - c0) * 128);
+		s420_mbar_expect_tx(bar, (doY ? 2u * ybytes : 0u) + (doC ? 2u * cbytes : 0u));
+		unsigned char *dst = reinterpret_cast<unsigned char *>(sCoef);
+		if (doY)
+		{
+			const int16_t *s0 = baseY + ((size_t)(2 * r) * ybw + 2 * m0) * 64;
+			s420_bulk_g2s(dst, s0, ybytes, bar);
+			s420_bulk_g2s(dst + ybytes, s0 + (size_t)ybw * 64, ybytes, bar);
+		}
+		if (doC)
+		{
+			const size_t off = ((size_t)(r + 1) * cbw + c0) * 64;
+			const unsigned d = (unsigned)((4 * Ms + (c0 - (m0 - 1))) * 128);
+			s420_bulk_g2s(dst + d, baseCb + off, cbytes, bar);
+			s420_bulk_g2s(dst + d + Mc * 128, baseCr + off, cbytes, bar);
+		}
+	};
+	const int r_start = max(r0 - 2, -1);
+	if (tid == 0)
+		issue(r_start);
+	unsigned parity = 0;
+
+	/* this thread's IDCT task, the same every iteration */
+	const int nY = 4 * Ms;
+	const bool isY = tid < nY;
+	const int ct = tid - nY, cpos = ct >> 1, ci = ct & 1;
+	const int cbx = m0 - 1 + cpos;
+	const bool cvalid = !isY && ct < 2 * Mc && cbx >= 0 && cbx < cbw;
+	const int slot = isY ? tid : (nY + ci * Mc + cpos);
+	const int yrow = (isY && tid >= 2 * Ms) ? 1 : 0, lbx = tid - yrow * 2 * Ms;
+	const bool chroma_warp = (tid | 31) >= nY; /* warp-uniform: this warp holds chroma lanes */
+
+	const bool vec_ok = (N == 4) ? ((W & 3) == 0) : ((W & 7) == 0);
+	uint8_t *obase = out + im->out_off;
+	const int G = 2 * Ms; /* 8-pixel groups per row of the strip */
+	const int ly_first = tid / G, g_first = tid - ly_first * G;
+	const int dly = S420_THREADS / G, dg = S420_THREADS - dly * G;
+
+#pragma unroll 1
+	for (int r = r_start; r < r1; ++r)
+	{
+		const bool doY = r >= r0, doC = (r + 1) <= rc_last;
+		s420_mbar_wait(bar, parity);
+		parity ^= 1u;
+
+		/* ---- IDCT phase: luma of MCU row r, chroma of MCU row r+1 ---- */
+		{
+			int v[64];
+			uint32_t rows[16];
+			if ((isY && doY) || (cvalid && doC))
+			{
+				const int16_t *g = isY ? baseY + ((size_t)(2 * r + yrow) * ybw + 2 * m0 + lbx) * 64
+											  : (ci ? baseCr : baseCb) + ((size_t)(r + 1) * cbw + cbx) * 64;
+				s420_load_block<DEQ>(&sCoef[slot * 8], coef_key(g), sQ[isY ? 0 : 1 + ci], v);
+				s420_idct(v, rows);
+			}
+			else
+			{
+#pragma unroll
+				for (int i = 0; i < 16; ++i)
+					rows[i] = 0u;
+			}
+			if (isY && doY)
+			{
+				uint8_t *d = sY + (yrow * 8) * S420_YW + lbx * 8;
+#pragma unroll
+				for (int rr = 0; rr < 8; ++rr)
+					*reinterpret_cast<uint2 *>(d + rr * S420_YW) = make_uint2(rows[2 * rr], rows[2 * rr + 1]);
+			}
+			if (chroma_warp)
+			{
+				/* lanes (2p, 2p+1) = (Cb, Cr) of one position: the Cb lane keeps rows 0-3, the Cr lane rows 4-7 */
+				const bool store = cvalid && doC;
+				uint32_t *dbase = sC + (((r + 1) & 1) * 8 + (ci ? 4 : 0)) * S420_CW + cpos * 8;
+#pragma unroll
+				for (int rr = 0; rr < 4; ++rr)
+				{
+					const uint32_t send_lo = ci ? rows[2 * rr] : rows[2 * (rr + 4)];
+					const uint32_t send_hi = ci ? rows[2 * rr + 1] : rows[2 * (rr + 4) + 1];
+					const uint32_t got_lo = __shfl_xor_sync(0xffffffffu, send_lo, 1);
+					const uint32_t got_hi = __shfl_xor_sync(0xffffffffu, send_hi, 1);
+					const uint32_t cb_lo = ci ? got_lo : rows[2 * rr], cb_hi = ci ? got_hi : rows[2 * rr + 1];
+					const uint32_t cr_lo = ci ? rows[2 * (rr + 4)] : got_lo, cr_hi = ci ? rows[2 * (rr + 4) + 1] : got_hi;
+					if (store)
+					{
+						uint4 *d = reinterpret_cast<uint4 *>(dbase + rr * S420_CW);
+						d[0] = s420_chroma_words(cb_lo, cr_lo);
+						d[1] = s420_chroma_words(cb_hi, cr_hi);
+					}
+				}
+				/* clamp-to-edge on the real chroma width (w_lores, jpeg.c:2276): replicate one column past
+				   each image edge; the same thread wrote the source sample, so no barrier is needed */
+				if (store && (cbx == 0 || cbx == cbw - 1))
+				{
+					const int e = wl - cbx * 8; /* samples of the last block that are real: 1..8 */
+#pragma unroll
+					for (int rr = 0; rr < 4; ++rr)
+					{
+						uint32_t *d = dbase + rr * S420_CW;
+						if (cbx == 0)
+							d[-1] = d[0];
+						if (cbx == cbw - 1)
+							d[e] = d[e - 1];
+					}
+				}
+			}
+		}
+		__syncthreads();
+		if (tid == 0 && r + 1 < r1)
+			issue(r + 1);
+
+		/* ---- pixel phase: MCU row r ---- */
+		if (doY)
+		{
+			const uint32_t *sCc = sC + (r & 1) * 8 * S420_CW, *sCn = sC + ((r + 1) & 1) * 8 * S420_CW;
+			const uint32_t *sPv = sP + (r & 1) * S420_CW;
+			int ly = ly_first, g = g_first;
+#pragma unroll 1
+			while (ly < 16)
+			{
+				const int gy = r * 16 + ly, gx0 = m0 * 16 + g * 8;
+				if (gy < H && gx0 < W)
+				{
+					const int lk = ly >> 1, k = r * 8 + lk;
+					const uint32_t *np = sCc + lk * S420_CW;
+					const uint32_t *fp;
+					if (ly & 1)
+						fp = (k + 1 > cy - 1) ? np : (lk < 7 ? np + S420_CW : sCn);
+					else
+						fp = (lk > 0) ? np - S420_CW : (r == 0 ? np : sPv);
+					const int col = 8 + g * 4;
+					uint32_t t[6];
+					{
+						const uint4 n4 = *reinterpret_cast<const uint4 *>(np + col), f4 = *reinterpret_cast<const uint4 *>(fp + col);
+						t[0] = 3u * np[col - 1] + fp[col - 1];
+						t[1] = 3u * n4.x + f4.x;
+						t[2] = 3u * n4.y + f4.y;
+						t[3] = 3u * n4.z + f4.z;
+						t[4] = 3u * n4.w + f4.w;
+						t[5] = 3u * np[col + 4] + fp[col + 4];
+					}
+					const uint2 yv = *reinterpret_cast<const uint2 *>(sY + ly * S420_YW + g * 8);
+					int R[8], Gc[8], B[8];
+#pragma unroll
+					for (int p = 0; p < 8; ++p)
+					{
+						const int j = p >> 1;
+						/* (3*t[i] + t[i-1 or i+1] + 8) >> 4 (jpeg.c:1832-1833) on both fields at once */
+						const uint32_t c16 = 3u * t[j + 1] + ((p & 1) ? t[j + 2] : t[j]);
+						const int cr = ((int)c16) >> 24;				/* Cr - 128 */
+						const int cb = (int)((c16 >> 8) & 255u); /* Cb (unsigned) */
+						const int y = (int)(((p < 4 ? yv.x : yv.y) >> (8 * (p & 3))) & 255u);
+						/* stbi__YCbCr_to_RGB_row (jpeg.c:1981-1990) with the common factor 2^8 divided out;
+						   the -128 of Cb is folded into the constants */
+						const int yf = y * 4096 + 2048;
+						R[p] = (yf + cr * 5743) >> 12;
+						Gc[p] = (yf + cr * -2925 + ((cb * -1410 + 180480) & ~255)) >> 12;
+						B[p] = (yf + cb * 7258 - 929024) >> 12;
+					}
+					const int count = min(8, W - gx0);
+					uint8_t *o = obase + ((size_t)gy * W + gx0) * N;
+					if (vec_ok && count == 8)
+					{
+						if (N == 3)
+						{
+							uint32_t w[6];
+#pragma unroll
+							for (int q = 0; q < 2; ++q)
+							{
+								const int a = 4 * q;
+								w[3 * q] = s420_pack4(R[a], Gc[a], B[a], R[a + 1]);
+								w[3 * q + 1] = s420_pack4(Gc[a + 1], B[a + 1], R[a + 2], Gc[a + 2]);
+								w[3 * q + 2] = s420_pack4(B[a + 2], R[a + 3], Gc[a + 3], B[a + 3]);
+							}
+							uint2 *ow = reinterpret_cast<uint2 *>(o); /* 24 bytes, 8-byte aligned when W % 8 == 0 */
+							ow[0] = make_uint2(w[0], w[1]);
+							ow[1] = make_uint2(w[2], w[3]);
+							ow[2] = make_uint2(w[4], w[5]);
+						}
+						else
+						{
+#pragma unroll
+							for (int q = 0; q < 2; ++q)
+								reinterpret_cast<uint4 *>(o)[q] = make_uint4(
+									 s420_pack4(R[4 * q], Gc[4 * q], B[4 * q], 255), s420_pack4(R[4 * q + 1], Gc[4 * q + 1], B[4 * q + 1], 255),
+									 s420_pack4(R[4 * q + 2], Gc[4 * q + 2], B[4 * q + 2], 255),
+									 s420_pack4(R[4 * q + 3], Gc[4 * q + 3], B[4 * q + 3], 255));
+						}
+					}
+					else
+					{
+#pragma unroll
+						for (int p = 0; p < 8; ++p)
+							if (p < count)
+							{
+								o[N * p] = (uint8_t)clamp_u8(R[p]);
+								o[N * p + 1] = (uint8_t)clamp_u8(Gc[p]);
+								o[N * p + 2] = (uint8_t)clamp_u8(B[p]);
+								if (N == 4)
+									o[N * p + 3] = 255;
+							}
+					}
+				}
+				g += dg;
+				ly += dly;
+				if (g >= G)
+				{
+					g -= G;
+					++ly;
+				}
+			}
+		}
+		/* keep the last chroma row of MCU row r for the top halo of row r+1 */
+		if (r >= 0 && r + 1 < r1)
+			for (int c = tid; c < S420_CW; c += S420_THREADS)
+				sP[((r + 1) & 1) * S420_CW + c] = sC[((r & 1) * 8 + 7) * S420_CW + c];
+		__syncthreads();
+	}
+}
+
+/* host-side launch: grid = (max strips*bands per image, images on the path) */
+static inline cudaError_t fused420_launch(int max_tiles, const int32_t *list, int nlist, const jcu_image *images, const int16_t *coef,
+														uint8_t *out, cudaStream_t st, int n_out, int deq, int rows_per_band)
+{
+	if (max_tiles <= 0 || nlist <= 0)
+		return cudaSuccess;
+	void (*k)(const int32_t *, const jcu_image *, const int16_t *, uint8_t *, int) =
+		 n_out == 4 ? (deq ? k_fused420_strip<4, true> : k_fused420_strip<4, false>)
+						: (deq ? k_fused420_strip<3, true> : k_fused420_strip<3, false>);
+	cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, S420_SMEM_BYTES);
+	if (e != cudaSuccess)
+		return e;
+	k<<<dim3((unsigned)max_tiles, (unsigned)nlist), S420_THREADS, S420_SMEM_BYTES, st>>>(list, images, coef, out, rows_per_band);
+	return cudaGetLastError();
+}

@@ -107,3 +107,34 @@ def test_per_image_api(oracle):
     assert ic.failure_reason() == "unknown image type"
     assert ic.stbi_load_from_memory(S.stream("420", 64, 48, 0), 7)[0] is None
     assert ic.failure_reason() == "bad req_comp"
+
+
+@pytest.mark.parametrize("rows_per_band", [0, 1, 5, 64])
+def test_fused_420_strips_and_bands(oracle, rows_per_band):
+    """4:2:0 strip kernel: images wider than one 640-pixel strip (2 and 3 strips, a 1-MCU last strip,
+    widths that are not multiples of 16 or 8), bands of 1 / 5 / all MCU rows, RGB and RGBA, baseline and
+    progressive (decode-time vs output-time dequantisation)."""
+    if rows_per_band:
+        os.environ["IMAGE_CODECS_B200_ROWS_PER_BAND"] = str(rows_per_band)
+    try:
+        cases = [("420_rst16", 1300, 100, 0), ("420", 650, 50, 1), ("420", 641, 33, 2), ("420_rst1", 1924, 70, 0),
+                 ("420_prog", 1283, 47, 1), ("420_opt", 656, 129, 2), ("420", 1280, 16, 0), ("420", 1288, 200, 1)]
+        datas = [S.stream(f, w, h, k) for f, w, h, k in cases]
+        d = ic.BatchDecoder(device=0)
+        for rc in (3, 4):
+            outs = d.decode(datas, rc)
+            for (f, w, h, k), data, got in zip(cases, datas, outs):
+                _check(oracle, got, data, rc, f"strip {f} {w}x{h} req{rc} rpb{rows_per_band}")
+        d.close()
+    finally:
+        os.environ.pop("IMAGE_CODECS_B200_ROWS_PER_BAND", None)
+
+
+def test_full_size_1080p_420_rst16(oracle, decoder):
+    """BASELINE.json configs[1] geometry: 1920x1080 4:2:0 q90 restart interval 16 (two distinct images)."""
+    from tools import testenc as te
+
+    datas = te.encode_many(2, 1920, 1080, kind=-1, base_seed=4242, quality=90, subsampling="420", restart_interval=16)
+    outs = decoder.decode(datas, 3)
+    for i, (data, got) in enumerate(zip(datas, outs)):
+        _check(oracle, got, data, 3, f"1080p #{i}")

@@ -157,6 +157,38 @@ __device__ __forceinline__ uint4 s420_chroma_words(uint32_t cbw, uint32_t crw)
 	return r;
 }
 
+/* ---- pinned instruction selection for the pixel phase: NVVM otherwise re-associates the colour sums and
+ *      re-adds the rounding constant once per channel ---- */
+__device__ __forceinline__ int s420_mad(int a, int b, int c)
+{
+	int d;
+	asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+	return d;
+}
+template <int SEL>
+__device__ __forceinline__ int s420_byte(uint32_t w) /* PRMT: selected byte -> bits 0-7, zeros above */
+{
+	int d;
+	asm("prmt.b32 %0, %1, 0, %2;" : "=r"(d) : "r"(w), "n"(SEL));
+	return d;
+}
+
+/* one pixel: chroma word c16 (Cb in byte 1, Cr-128 signed in byte 3), luma byte -> r, g, b (not yet clamped).
+   stbi__YCbCr_to_RGB_row (jpeg.c:1981-1990) with the common factor 2^8 divided out; Cb's -128 folded into constants */
+template <int YSEL>
+__device__ __forceinline__ void s420_colour(uint32_t c16, uint32_t yw, int &r, int &g, int &b)
+{
+	const int cr = ((int)c16) >> 24;
+	const int cb = s420_byte<0x4441>(c16);
+	const int y = s420_byte<0x4440 + YSEL>(yw);
+	const int yf = s420_mad(y, 4096, 2048);
+	const int yfb = s420_mad(y, 4096, 2048 - 128 * 7258);
+	r = s420_mad(cr, 5743, yf) >> 12;
+	b = s420_mad(cb, 7258, yfb) >> 12;
+	const int m = s420_mad(cb, -1410, 128 * 1410) & ~255;
+	g = (s420_mad(cr, -2925, yf) + m) >> 12;
+}
+
 /*
  * grid: (max strips*bands per image, images on this path).  DEQ = coefficients are raw (progressive);
  * otherwise the entropy stage already stored (short)(c*q) as the reference does for baseline.
@@ -173,6 +205,7 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 	uint32_t *sP = reinterpret_cast<uint32_t *>(s420_smem + S420_OFF_P);	  /* [2][S420_CW] */
 	uint16_t(*sQ)[64] = reinterpret_cast<uint16_t(*)[64]>(s420_smem + S420_OFF_Q);
 	uint64_t *bar = reinterpret_cast<uint64_t *>(s420_smem + S420_OFF_BAR);
+	__shared__ int2 sRow[16]; /* per pixel row of the current MCU row: word offsets (from sC) of its near / far chroma rows */
 
 	const jcu_image *im = &images[list[blockIdx.y]];
 	const int strips = im->tiles_x;
@@ -235,6 +268,7 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 	const bool chroma_warp = (tid | 31) >= nY; /* warp-uniform: this warp holds chroma lanes */
 
 	const bool vec_ok = (N == 4) ? ((W & 3) == 0) : ((W & 7) == 0);
+	const bool full_w = vec_ok && (m0 + Ms) * 16 <= W; /* CTA-uniform: every 8-pixel group of the strip is whole */
 	uint8_t *obase = out + im->out_off;
 	const int G = 2 * Ms; /* 8-pixel groups per row of the strip */
 	const int ly_first = tid / G, g_first = tid - ly_first * G;
@@ -247,6 +281,18 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 		s420_mbar_wait(bar, parity);
 		parity ^= 1u;
 
+		/* row selection of the h2v2 resampler (jpeg.c:2301-2318) for the 16 pixel rows of MCU row r */
+		if (tid < 16 && doY)
+		{
+			const int ly = tid, lk = ly >> 1, k = r * 8 + lk;
+			const int nr = ((r & 1) * 8 + lk) * S420_CW;
+			int fr;
+			if (ly & 1)
+				fr = (k + 1 > cy - 1) ? nr : (lk < 7 ? nr + S420_CW : (((r + 1) & 1) * 8) * S420_CW);
+			else
+				fr = (lk > 0) ? nr - S420_CW : (r == 0 ? nr : (16 + (r & 1)) * S420_CW); /* line buffer sP follows sC */
+			sRow[ly] = make_int2(nr, (r * 16 + ly < H) ? fr : -1);
+		}
 		/* ---- IDCT phase: luma of MCU row r, chroma of MCU row r+1 ---- */
 		{
 			int v[64];
@@ -313,57 +359,42 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 		if (tid == 0 && r + 1 < r1)
 			issue(r + 1);
 
-		/* ---- pixel phase: MCU row r ---- */
+		/* ---- pixel phase: MCU row r, one task = 8 pixels of one row ---- */
 		if (doY)
 		{
-			const uint32_t *sCc = sC + (r & 1) * 8 * S420_CW, *sCn = sC + ((r + 1) & 1) * 8 * S420_CW;
-			const uint32_t *sPv = sP + (r & 1) * S420_CW;
+			uint8_t *orow0 = obase + ((size_t)r * 16 * W + (size_t)m0 * 16) * N;
 			int ly = ly_first, g = g_first;
 #pragma unroll 1
 			while (ly < 16)
 			{
-				const int gy = r * 16 + ly, gx0 = m0 * 16 + g * 8;
-				if (gy < H && gx0 < W)
+				const int2 rw = sRow[ly]; /* word offsets of the near / far chroma rows; far < 0: row beyond the image */
+				const int gx0 = m0 * 16 + g * 8;
+				if (rw.y >= 0 && (full_w || gx0 < W))
 				{
-					const int lk = ly >> 1, k = r * 8 + lk;
-					const uint32_t *np = sCc + lk * S420_CW;
-					const uint32_t *fp;
-					if (ly & 1)
-						fp = (k + 1 > cy - 1) ? np : (lk < 7 ? np + S420_CW : sCn);
-					else
-						fp = (lk > 0) ? np - S420_CW : (r == 0 ? np : sPv);
-					const int col = 8 + g * 4;
+					const uint32_t *np = sC + rw.x + 8 + g * 4, *fp = sC + rw.y + 8 + g * 4;
 					uint32_t t[6];
 					{
-						const uint4 n4 = *reinterpret_cast<const uint4 *>(np + col), f4 = *reinterpret_cast<const uint4 *>(fp + col);
-						t[0] = 3u * np[col - 1] + fp[col - 1];
+						const uint4 n4 = *reinterpret_cast<const uint4 *>(np), f4 = *reinterpret_cast<const uint4 *>(fp);
+						t[0] = 3u * np[-1] + fp[-1];
 						t[1] = 3u * n4.x + f4.x;
 						t[2] = 3u * n4.y + f4.y;
 						t[3] = 3u * n4.z + f4.z;
 						t[4] = 3u * n4.w + f4.w;
-						t[5] = 3u * np[col + 4] + fp[col + 4];
+						t[5] = 3u * np[4] + fp[4];
 					}
 					const uint2 yv = *reinterpret_cast<const uint2 *>(sY + ly * S420_YW + g * 8);
 					int R[8], Gc[8], B[8];
-#pragma unroll
-					for (int p = 0; p < 8; ++p)
-					{
-						const int j = p >> 1;
-						/* (3*t[i] + t[i-1 or i+1] + 8) >> 4 (jpeg.c:1832-1833) on both fields at once */
-						const uint32_t c16 = 3u * t[j + 1] + ((p & 1) ? t[j + 2] : t[j]);
-						const int cr = ((int)c16) >> 24;				/* Cr - 128 */
-						const int cb = (int)((c16 >> 8) & 255u); /* Cb (unsigned) */
-						const int y = (int)(((p < 4 ? yv.x : yv.y) >> (8 * (p & 3))) & 255u);
-						/* stbi__YCbCr_to_RGB_row (jpeg.c:1981-1990) with the common factor 2^8 divided out;
-						   the -128 of Cb is folded into the constants */
-						const int yf = y * 4096 + 2048;
-						R[p] = (yf + cr * 5743) >> 12;
-						Gc[p] = (yf + cr * -2925 + ((cb * -1410 + 180480) & ~255)) >> 12;
-						B[p] = (yf + cb * 7258 - 929024) >> 12;
-					}
-					const int count = min(8, W - gx0);
-					uint8_t *o = obase + ((size_t)gy * W + gx0) * N;
-					if (vec_ok && count == 8)
+					/* (3*t[i] + t[i-1 or i+1] + 8) >> 4 (jpeg.c:1832-1833) on both chroma fields at once */
+					s420_colour<0>(3u * t[1] + t[0], yv.x, R[0], Gc[0], B[0]);
+					s420_colour<1>(3u * t[1] + t[2], yv.x, R[1], Gc[1], B[1]);
+					s420_colour<2>(3u * t[2] + t[1], yv.x, R[2], Gc[2], B[2]);
+					s420_colour<3>(3u * t[2] + t[3], yv.x, R[3], Gc[3], B[3]);
+					s420_colour<0>(3u * t[3] + t[2], yv.y, R[4], Gc[4], B[4]);
+					s420_colour<1>(3u * t[3] + t[4], yv.y, R[5], Gc[5], B[5]);
+					s420_colour<2>(3u * t[4] + t[3], yv.y, R[6], Gc[6], B[6]);
+					s420_colour<3>(3u * t[4] + t[5], yv.y, R[7], Gc[7], B[7]);
+					uint8_t *o = orow0 + (unsigned)(ly * W + g * 8) * N;
+					if (full_w || (vec_ok && gx0 + 8 <= W))
 					{
 						if (N == 3)
 						{
@@ -393,6 +424,7 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 					}
 					else
 					{
+						const int count = min(8, W - gx0);
 #pragma unroll
 						for (int p = 0; p < 8; ++p)
 							if (p < count)

@@ -27,32 +27,28 @@
 __device__ __forceinline__ void idct_1d(int s0, int s1, int s2, int s3, int s4, int s5, int s6, int s7, int bias,
 													 int (&o)[8])
 {
-	/* even part */
-	int z = (s2 + s6) * 2217;
-	int e2 = z + s6 * -7567;
-	int e3 = z + s2 * 3135;
-	int a0 = (s0 + s4) * 4096 + bias;
-	int a1 = (s0 - s4) * 4096 + bias;
-	int x0 = a0 + e3, x3 = a0 - e3, x1 = a1 + e2, x2 = a1 - e2;
-	/* odd part */
-	int q3 = s7 + s3, q4 = s5 + s1, q1 = s7 + s1, q2 = s5 + s3;
-	int q5 = (q3 + q4) * 4816;
-	int A = q5 + q1 * -3685;
-	int B = q5 + q2 * -10497;
-	int C = q3 * -8034;
-	int D = q4 * -1597;
-	int d3 = s1 * 6149 + A + D;
-	int d2 = s3 * 12586 + B + C;
-	int d1 = s5 * 8410 + B + D;
-	int d0 = s7 * 1223 + A + C;
-	o[0] = x0 + d3;
-	o[7] = x0 - d3;
-	o[1] = x1 + d2;
-	o[6] = x1 - d2;
-	o[2] = x2 + d1;
-	o[5] = x2 - d1;
-	o[3] = x3 + d0;
-	o[4] = x3 - d0;
+	/* even part (jpeg.c:580-591): p1 = (s2+s6)*f2f(0.5411961); t2 = p1 - s6*f2f(1.847759065); t3 = p1 + s2*f2f(0.765366865) */
+	const int z = (s2 + s6) * 2217;
+	const int e2 = z + s6 * -7567;
+	const int e3 = z + s2 * 3135;
+	const int a0 = (s0 + s4) * 4096 + bias;
+	const int a1 = (s0 - s4) * 4096 + bias;
+	/* odd part (jpeg.c:592-612) multiplied out: in the ring Z/2^32 the reference's factored butterfly
+	   (p5 = (p3+p4)*f2f(1.175875602), t0..t3 *= ..., t3 += p1+p4, ...) equals this 4x4 integer matrix,
+	   e.g. d3 = s1*(6149+4816-3685-1597) + s3*4816 + s5*(4816-1597) + s7*(4816-3685); 16 multiply-adds, no adds */
+	const int d3 = s1 * 5683 + s3 * 4816 + s5 * 3219 + s7 * 1131;
+	const int d2 = s1 * 4816 + s3 * -1129 + s5 * -5681 + s7 * -3218;
+	const int d1 = s1 * 3219 + s3 * -5681 + s5 * 1132 + s7 * 4816;
+	const int d0 = s1 * 1131 + s3 * -3218 + s5 * 4816 + s7 * -5680;
+	/* outputs as three-input sums (IADD3): x0 = a0+e3, x3 = a0-e3, x1 = a1+e2, x2 = a1-e2 are never materialised */
+	o[0] = (a0 + d3) + e3;
+	o[7] = (a0 - d3) + e3;
+	o[1] = (a1 + d2) + e2;
+	o[6] = (a1 - d2) + e2;
+	o[2] = (a1 + d1) - e2;
+	o[5] = (a1 - d1) - e2;
+	o[3] = (a0 + d0) - e3;
+	o[4] = (a0 - d0) - e3;
 }
 
 __device__ __forceinline__ int clamp_u8(int v) { return min(max(v, 0), 255); }

@@ -181,7 +181,7 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 		for (int i = 0; i < b->n_images; ++i)
 			if (imgs[i].ok && !c->force_generic && imgs[i].path == JCU_PATH_FUSED_420)
 				strip_rows += (long long)((imgs[i].mcu_x + S420_MS - 1) / S420_MS) * imgs[i].mcu_y;
-		long long rb = strip_rows / (148 * 2 * 8);
+		long long rb = strip_rows / (148 * (512 / S420_THREADS) * 8);
 		c->rows_per_band = (int)std::min<long long>(std::max<long long>(rb, 2), 24);
 		const char *ov = getenv("IMAGE_CODECS_B200_ROWS_PER_BAND"); /* test hook: force the band height */
 		if (ov && atoi(ov) > 0)

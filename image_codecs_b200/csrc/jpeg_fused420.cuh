@@ -39,12 +39,14 @@
 #include "jpeg_coef_layout.cuh"
 #include "jpeg_output.cuh"
 
-#define S420_THREADS 256
-#define S420_MS 40									  /* MCUs per strip (640 px) */
+#ifndef S420_THREADS
+#define S420_THREADS 128
+#endif
+#define S420_MS (5 * S420_THREADS / 32)									  /* MCUs per strip (640 px) */
 #define S420_MC (S420_MS + 2)						  /* chroma block positions incl. one halo each side */
 #define S420_SLOTS (4 * S420_MS + 2 * S420_MC) /* staged coefficient blocks per iteration (244) */
 #define S420_YW (S420_MS * 16)					  /* luma sample row, bytes */
-#define S420_CW 340									  /* chroma ring row stride in words (>= 8 * S420_MC, == 20 mod 32) */
+#define S420_CW (8 * S420_MC + 4)								  /* chroma ring row stride in words (>= 8 * S420_MC, == 20 mod 32) */
 #define S420_OFF_Y (S420_SLOTS * 128)
 #define S420_OFF_C (S420_OFF_Y + 16 * S420_YW)
 #define S420_OFF_P (S420_OFF_C + 2 * 8 * S420_CW * 4)
@@ -194,7 +196,7 @@ __device__ __forceinline__ void s420_colour(uint32_t c16, uint32_t yw, int &r, i
  * otherwise the entropy stage already stored (short)(c*q) as the reference does for baseline.
  */
 template <int N, bool DEQ>
-__global__ void __launch_bounds__(S420_THREADS, 2)
+__global__ void __launch_bounds__(S420_THREADS, 512 / S420_THREADS)
 k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__ images, const int16_t *__restrict__ coef,
 					  uint8_t *__restrict__ out, int rows_per_band)
 {

@@ -83,6 +83,9 @@ struct stbi_jpeg_batch
 	int need_clear;
 
 	stbi_jpeg_batch_timings tm;
+
+	struct stbi_jpeg_batch *pipe; /* second object (own stream, staging and device buffers) so that the host-buffer
+												call can parse / upload chunk k+1 while chunk k computes and downloads */
 };
 
 static int online_cpus(void)
@@ -133,6 +136,8 @@ API void stbi_jpeg_batch_destroy(stbi_jpeg_batch *b)
 {
 	if (!b)
 		return;
+	if (b->pipe)
+		stbi_jpeg_batch_destroy(b->pipe);
 	batch_release_results(b);
 	jcu_ctx_destroy(b->ctx);
 	jcu_host_free(b->slab);
@@ -578,39 +583,70 @@ API int stbi_jpeg_decode_batch(stbi_jpeg_batch *b, const stbi_uc *const *bufs, c
 			nok += b->res[done].ok;
 		return nok;
 	}
-	chunk = b->params.chunk_images > 0 ? b->params.chunk_images : 64;
-	while (done < count)
+	chunk = b->params.chunk_images > 0 ? b->params.chunk_images : 256;
+	if (count > chunk && !b->pipe)
 	{
-		int n = count - done < chunk ? count - done : chunk, i;
-		if (stbi_jpeg_batch_prepare(b, bufs + done, lens + done, n, req_comp, NULL, NULL, NULL, NULL) < 0)
-			return -1;
-		if (!stbi_jpeg_batch_run(b))
-			return -1;
-		for (i = 0; i < n; ++i)
-			if (b->res[i].ok)
-				batch_enqueue_fetch(b, i, outs[done + i], out_caps[done + i]);
-		if (!stbi_jpeg_batch_sync(b))
-			return -1;
-		batch_report(b, xs ? xs + done : NULL, ys ? ys + done : NULL, comps ? comps + done : NULL,
-						 status ? status + done : NULL);
-		for (i = 0; i < n; ++i)
-			if (stbi_jpeg_batch_status(b, i) == STBI_JPEG_OK)
+		stbi_jpeg_batch_params pp = b->params;
+		b->pipe = stbi_jpeg_batch_create(&pp);
+	}
+	{
+		/* two-deep software pipeline over chunks: object k&1 parses + uploads + launches + enqueues the
+		   download of chunk k on its own stream, then the host moves on to chunk k+1 on the other object and
+		   only waits for chunk k when that object is needed again.  Host parse, H2D, kernels and D2H of
+		   neighbouring chunks overlap; D2H (3 B/px over PCIe) is the floor. */
+		stbi_jpeg_batch *obj[2];
+		int pend_first[2] = {-1, -1}, pend_n[2] = {0, 0}, k = 0;
+		obj[0] = b;
+		obj[1] = b->pipe ? b->pipe : b;
+		while (done < count || pend_first[0] >= 0 || pend_first[1] >= 0)
+		{
+			const int slot = b->pipe ? (k & 1) : 0;
+			stbi_jpeg_batch *s = obj[slot];
+			int i;
+			if (pend_first[slot] >= 0)
 			{
-				if (g_flip_on_load)
-					flip_rows(outs[done + i], b->images[i].width, b->images[i].height, b->images[i].n_out);
-				++nok;
+				const int first = pend_first[slot], n = pend_n[slot];
+				if (!stbi_jpeg_batch_sync(s))
+					return -1;
+				batch_report(s, xs ? xs + first : NULL, ys ? ys + first : NULL, comps ? comps + first : NULL,
+								 status ? status + first : NULL);
+				for (i = 0; i < n; ++i)
+					if (stbi_jpeg_batch_status(s, i) == STBI_JPEG_OK)
+					{
+						if (g_flip_on_load)
+							flip_rows(outs[first + i], s->images[i].width, s->images[i].height, s->images[i].n_out);
+						++nok;
+					}
+				acc.parse_ms += s->tm.parse_ms;
+				acc.h2d_ms += s->tm.h2d_ms;
+				acc.entropy_ms += s->tm.entropy_ms;
+				acc.idct_ms += s->tm.idct_ms;
+				acc.d2h_ms += s->tm.d2h_ms;
+				acc.total_ms += s->tm.total_ms;
+				acc.entropy_bits += s->tm.entropy_bits;
+				acc.coef_bytes += s->tm.coef_bytes;
+				acc.out_bytes += s->tm.out_bytes;
+				acc.launches += s->tm.launches;
+				pend_first[slot] = -1;
 			}
-		acc.parse_ms += b->tm.parse_ms;
-		acc.h2d_ms += b->tm.h2d_ms;
-		acc.entropy_ms += b->tm.entropy_ms;
-		acc.idct_ms += b->tm.idct_ms;
-		acc.d2h_ms += b->tm.d2h_ms;
-		acc.total_ms += b->tm.total_ms;
-		acc.entropy_bits += b->tm.entropy_bits;
-		acc.coef_bytes += b->tm.coef_bytes;
-		acc.out_bytes += b->tm.out_bytes;
-		acc.launches += b->tm.launches;
-		done += n;
+			if (done < count)
+			{
+				/* ramp the first chunks (16, 32, 64, ...) so the first download starts early */
+				const int want = (k < 4 && (16 << k) < chunk) ? (16 << k) : chunk;
+				const int n = count - done < want ? count - done : want;
+				if (stbi_jpeg_batch_prepare(s, bufs + done, lens + done, n, req_comp, NULL, NULL, NULL, NULL) < 0)
+					return -1;
+				if (!stbi_jpeg_batch_run(s))
+					return -1;
+				for (i = 0; i < n; ++i)
+					if (s->res[i].ok)
+						batch_enqueue_fetch(s, i, outs[done + i], out_caps[done + i]);
+				pend_first[slot] = done;
+				pend_n[slot] = n;
+				done += n;
+			}
+			++k;
+		}
 	}
 	b->tm = acc;
 	return nok;

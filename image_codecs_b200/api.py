@@ -30,7 +30,7 @@ class Timings(C.Structure):
     _fields_ = [("parse_ms", C.c_float), ("h2d_ms", C.c_float), ("entropy_ms", C.c_float), ("idct_ms", C.c_float),
                 ("d2h_ms", C.c_float), ("total_ms", C.c_float), ("entropy_bits", C.c_double),
                 ("coef_bytes", C.c_double), ("out_bytes", C.c_double), ("launches", C.c_int),
-                ("reserved", C.c_int * 5)]
+                ("selfsync_scans", C.c_int), ("selfsync_rounds", C.c_int), ("reserved", C.c_int * 3)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}

@@ -453,6 +453,8 @@ API int stbi_jpeg_batch_sync(stbi_jpeg_batch *b)
 		b->tm.d2h_ms = t.d2h_ms;
 		b->tm.total_ms = t.total_ms;
 		b->tm.launches = t.launches;
+		b->tm.selfsync_scans = t.ss_scans;
+		b->tm.selfsync_rounds = t.ss_rounds;
 	}
 	return 1;
 }
@@ -627,6 +629,9 @@ API int stbi_jpeg_decode_batch(stbi_jpeg_batch *b, const stbi_uc *const *bufs, c
 				acc.coef_bytes += s->tm.coef_bytes;
 				acc.out_bytes += s->tm.out_bytes;
 				acc.launches += s->tm.launches;
+				acc.selfsync_scans += s->tm.selfsync_scans;
+				if (s->tm.selfsync_rounds > acc.selfsync_rounds)
+					acc.selfsync_rounds = s->tm.selfsync_rounds;
 				pend_first[slot] = -1;
 			}
 			if (done < count)

@@ -15,6 +15,7 @@
 #include "../../include/jpeg_cuda_abi.h"
 #include "jpeg_entropy.cuh"
 #include "jpeg_entropy_baseline.cuh"
+#include "jpeg_selfsync.cuh"
 #include "jpeg_output.cuh"
 #include "jpeg_fused.cuh"
 #include "jpeg_fused420.cuh"
@@ -35,6 +36,11 @@ struct jcu_ctx
 					ev_d2h1 = nullptr;
 	bool d2h_open = false;
 	DevBuf bits, images, scans, segs, huff, work, coef, planes, out, err, lists;
+	DevBuf ss_work, ss_scans, ss_exit_a, ss_exit_b, ss_entry, ss_nblk, ss_first, ss_changed;
+	std::vector<SsWork> ss_work_h; /* self-synchronising decode: CTA work items over all waves */
+	std::vector<SsScan> ss_scan_h;
+	uint32_t ss_nsub_total = 0, ss_max_nsub = 0;
+	int ss_rounds = 0; /* refine rounds the last run needed */
 	/* batch metadata kept on the host */
 	int n_images = 0, n_waves = 0;
 	size_t coef_elems = 0, out_bytes = 0;
@@ -127,7 +133,8 @@ extern "C" void jcu_ctx_destroy(jcu_ctx *c)
 		return;
 	cudaSetDevice(c->device);
 	cudaStreamSynchronize(c->stream);
-	DevBuf *bufs[] = {&c->bits, &c->images, &c->scans, &c->segs, &c->huff, &c->work, &c->coef, &c->planes, &c->out, &c->err, &c->lists};
+	DevBuf *bufs[] = {&c->bits, &c->images, &c->scans, &c->segs, &c->huff, &c->work, &c->coef, &c->planes, &c->out, &c->err, &c->lists,
+							&c->ss_work, &c->ss_scans, &c->ss_exit_a, &c->ss_exit_b, &c->ss_entry, &c->ss_nblk, &c->ss_first, &c->ss_changed};
 	for (auto b : bufs)
 		if (b->p)
 			cudaFree(b->p);
@@ -230,6 +237,45 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 
 	/* ---- CTA work items per wave: ENT_THREADS segments of one scan each ---- */
 	c->work_h.clear();
+	c->ss_work_h.clear();
+	c->ss_scan_h.clear();
+	c->ss_nsub_total = 0;
+	c->ss_max_nsub = 0;
+	std::vector<char> is_ss((size_t)std::max(1, b->n_scans), 0);
+	for (int s = 0; s < b->n_scans; ++s)
+	{
+		/* baseline scans without restart markers: one serial segment per scan, unless it is long enough
+		   (or entropy_mode == 2) for the self-synchronising decoder; entropy_mode == 1 forces the serial path */
+		const jcu_scan &sc = b->scans[s];
+		if (!imgs[sc.image].ok || sc.kind != JCU_SCAN_BASELINE || sc.restart_interval != 0 || sc.nseg != 1 || c->entropy_mode == 1)
+			continue;
+		const uint32_t start = b->seg_start[sc.seg_first];
+		const uint32_t bytes = sc.data_end > start ? sc.data_end - start : 0u;
+		if (bytes < (c->entropy_mode == 2 ? 1u : 4u * SS_SUB_BYTES))
+			continue;
+		SsScan e;
+		e.scan = s;
+		e.base = c->ss_nsub_total;
+		e.nsub = (bytes + SS_SUB_BYTES - 1) / SS_SUB_BYTES;
+		e.pad = 0;
+		c->ss_scan_h.push_back(e);
+		for (uint32_t f = 0; f < e.nsub; f += SS_THREADS)
+		{
+			SsWork wk;
+			wk.scan = s;
+			wk.first = f;
+			wk.count = std::min<uint32_t>(SS_THREADS, e.nsub - f);
+			wk.scan_base = e.base;
+			wk.scan_nsub = e.nsub;
+			wk.pad = 0;
+			c->ss_work_h.push_back(wk);
+		}
+		c->ss_nsub_total += e.nsub;
+		c->ss_max_nsub = std::max(c->ss_max_nsub, e.nsub);
+		is_ss[s] = 1;
+	}
+	if (!c->ss_scan_h.empty())
+		c->need_clear = true; /* phase 4 writes single coefficients into zeroed blocks */
 	c->wave_off.assign((size_t)b->n_waves + 1, 0);
 	c->wave_nbase.assign((size_t)b->n_waves, 0);
 	for (int w = 0; w < b->n_waves; ++w)
@@ -240,7 +286,7 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 			for (int s = 0; s < b->n_scans; ++s)
 			{
 				const jcu_scan &sc = b->scans[s];
-				if (sc.wave != w || !imgs[sc.image].ok || (sc.kind == JCU_SCAN_BASELINE) != (pass == 0))
+				if (sc.wave != w || !imgs[sc.image].ok || is_ss[s] || (sc.kind == JCU_SCAN_BASELINE) != (pass == 0))
 					continue;
 				for (uint32_t f = 0; f < sc.nseg; f += ENT_THREADS)
 				{
@@ -269,6 +315,18 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 	CK(ensure(c->out, b->out_bytes + 256));
 	CK(ensure(c->err, sizeof(int32_t) * std::max(1, b->n_images)));
 	CK(ensure(c->lists, sizeof(int32_t) * std::max<size_t>(1, c->list_h.size())));
+	if (!c->ss_scan_h.empty())
+	{
+		const size_t n = c->ss_nsub_total;
+		CK(ensure(c->ss_work, sizeof(SsWork) * c->ss_work_h.size()));
+		CK(ensure(c->ss_scans, sizeof(SsScan) * c->ss_scan_h.size()));
+		CK(ensure(c->ss_exit_a, sizeof(SsState) * n));
+		CK(ensure(c->ss_exit_b, sizeof(SsState) * n));
+		CK(ensure(c->ss_entry, sizeof(SsState) * n));
+		CK(ensure(c->ss_nblk, sizeof(uint32_t) * n));
+		CK(ensure(c->ss_first, sizeof(uint32_t) * n));
+		CK(ensure(c->ss_changed, 256));
+	}
 
 	if (c->profile)
 		CK(cudaEventRecord(c->ev_h2d0, c->stream));
@@ -284,6 +342,11 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 		CK(cudaMemcpyAsync(c->huff.p, b->huff, sizeof(jcu_huff_spec) * b->n_huff, cudaMemcpyHostToDevice, c->stream));
 	if (!c->work_h.empty())
 		CK(cudaMemcpyAsync(c->work.p, c->work_h.data(), sizeof(EntWork) * c->work_h.size(), cudaMemcpyHostToDevice, c->stream));
+	if (!c->ss_scan_h.empty())
+	{
+		CK(cudaMemcpyAsync(c->ss_work.p, c->ss_work_h.data(), sizeof(SsWork) * c->ss_work_h.size(), cudaMemcpyHostToDevice, c->stream));
+		CK(cudaMemcpyAsync(c->ss_scans.p, c->ss_scan_h.data(), sizeof(SsScan) * c->ss_scan_h.size(), cudaMemcpyHostToDevice, c->stream));
+	}
 	if (!c->list_h.empty())
 		CK(cudaMemcpyAsync(c->lists.p, c->list_h.data(), sizeof(int32_t) * c->list_h.size(), cudaMemcpyHostToDevice, c->stream));
 	if (c->profile)
@@ -323,6 +386,43 @@ extern "C" int jcu_run(jcu_ctx *c)
 																				(const uint8_t *)c->bits.p, (int16_t *)c->coef.p, (int32_t *)c->err.p);
 			c->launches++;
 		}
+	}
+	if (!c->ss_scan_h.empty())
+	{
+		/* self-synchronising decode of the restart-less baseline scans (jpeg_selfsync.cuh) */
+		SsBuffers sb;
+		sb.exit_a = (SsState *)c->ss_exit_a.p;
+		sb.exit_b = (SsState *)c->ss_exit_b.p;
+		sb.entry_used = (SsState *)c->ss_entry.p;
+		sb.nblk = (uint32_t *)c->ss_nblk.p;
+		sb.first_blk = (uint32_t *)c->ss_first.p;
+		sb.changed = (int32_t *)c->ss_changed.p;
+		const unsigned nw = (unsigned)c->ss_work_h.size(), ns = (unsigned)c->ss_scan_h.size();
+		const SsWork *wk = (const SsWork *)c->ss_work.p;
+#define SS_ARGS wk, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p, (const jcu_huff_spec *)c->huff.p, \
+					 (const uint8_t *)c->bits.p, (int16_t *)c->coef.p, (int32_t *)c->err.p, sb
+		k_ss_decode<SS_GUESS><<<nw, SS_THREADS, 0, st>>>(SS_ARGS, 0);
+		c->launches++;
+		int parity = 0;
+		c->ss_rounds = 0;
+		for (uint32_t round = 0; round < c->ss_max_nsub + 2; ++round)
+		{
+			int32_t changed = 0;
+			CK(cudaMemsetAsync(sb.changed, 0, sizeof(int32_t), st));
+			k_ss_decode<SS_REFINE><<<nw, SS_THREADS, 0, st>>>(SS_ARGS, parity);
+			c->launches++;
+			parity ^= 1;
+			c->ss_rounds++;
+			CK(cudaMemcpyAsync(&changed, sb.changed, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+			CK(cudaStreamSynchronize(st)); /* the round count is data dependent */
+			if (!changed)
+				break;
+		}
+		k_ss_scan<<<ns, 256, 0, st>>>((const SsScan *)c->ss_scans.p, sb.nblk, sb.first_blk);
+		k_ss_decode<SS_WRITE><<<nw, SS_THREADS, 0, st>>>(SS_ARGS, parity);
+		k_ss_dc<<<dim3(ns, 4), 256, 0, st>>>((const SsScan *)c->ss_scans.p, (const jcu_scan *)c->scans.p, d_img, (int16_t *)c->coef.p);
+		c->launches += 3;
+#undef SS_ARGS
 	}
 	CK(cudaGetLastError());
 	if (c->profile)
@@ -395,6 +495,8 @@ extern "C" int jcu_get_timings(jcu_ctx *c, jcu_timings *t)
 {
 	memset(t, 0, sizeof(*t));
 	t->launches = c->launches;
+	t->ss_scans = (int32_t)c->ss_scan_h.size();
+	t->ss_rounds = c->ss_rounds;
 	if (!c->profile)
 		return 0;
 	CK(cudaSetDevice(c->device));

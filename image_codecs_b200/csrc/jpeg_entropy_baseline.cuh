@@ -60,6 +60,8 @@ struct EntbShared
 											 positions 64..127 alias natural 63 like the reference's padded table (jpeg.c:303) */
 	uint32_t blk[ENTB_MAX_MCU_BLOCKS]; /* per block of an MCU: slot | dx << 4 | dy << 8 | dc lut << 12 | ac lut << 16 */
 	int nblk;
+	unsigned long long coff[4]; /* per slot: first coefficient of the component in the slab */
+	int bw[4], hn[4], vn[4];	 /* per slot: blocks per plane row; blocks per MCU across / down (1 x 1 in single-component scans) */
 };
 
 /* entry for symbol `sym` of code length l (l <= 9) */
@@ -235,28 +237,11 @@ __device__ __forceinline__ bool entb_symbol(const uint8_t *__restrict__ base, EB
 	return true;
 }
 
-/*
- * grid = CTA work items (EntWork) of one wave restricted to baseline scans; thread t decodes restart
- * segment (work.seg_first + t) of the CTA's scan.
- */
-__global__ void __launch_bounds__(ENTB_THREADS)
-k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans,
-						 const jcu_image *__restrict__ images, const uint32_t *__restrict__ seg_start,
-						 const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ bitstream,
-						 int16_t *__restrict__ coef, int32_t *__restrict__ img_err)
+/* per-scan tables, built once per CTA by all its threads (slots sharing a DHT table share one lookup) */
+__device__ __forceinline__ void entb_setup(EntbShared &sh, const jcu_scan *sc, const jcu_image *im,
+														 const jcu_huff_spec *__restrict__ huff, int tid, int nthreads)
 {
-	__shared__ EntbShared sh;
-	__shared__ unsigned long long s_coff[4];
-	__shared__ int s_bw[4], s_hn[4], s_vn[4];
-	__shared__ __align__(16) uint32_t s_slots[ENTB_THREADS * ENTB_SLOT_WORDS];
-
-	const int tid = threadIdx.x;
-	const EntWork w = work[blockIdx.x];
-	const jcu_scan *sc = &scans[w.scan];
-	const jcu_image *im = &images[sc->image];
 	const int ncs = sc->ncomp;
-
-	/* ---- per-scan tables, once per CTA (slots sharing a DHT table share one lookup) ---- */
 	int lut_dc[4], lut_ac[4]; /* indices resolved after unrolling: no dynamic indexing */
 #pragma unroll
 	for (int i = 0; i < 4; ++i)
@@ -275,12 +260,12 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 						lut_ac[i] = lut_ac[j];
 				}
 			if (lut_dc[i] == i && sc->dc_spec[i] >= 0)
-				entb_lut_build(&sh.dc[i], &huff[sc->dc_spec[i]], true, tid, ENTB_THREADS);
+				entb_lut_build(&sh.dc[i], &huff[sc->dc_spec[i]], true, tid, nthreads);
 			if (lut_ac[i] == i && sc->ac_spec[i] >= 0)
-				entb_lut_build(&sh.ac[i], &huff[sc->ac_spec[i]], false, tid, ENTB_THREADS);
+				entb_lut_build(&sh.ac[i], &huff[sc->ac_spec[i]], false, tid, nthreads);
 		}
 	}
-	for (int i = tid; i < ncs * 128; i += ENTB_THREADS)
+	for (int i = tid; i < ncs * 128; i += nthreads)
 	{
 		const int s = i >> 7, z = i & 127;
 		const int nat = c_natural[z < 79 ? z : 79];
@@ -295,10 +280,10 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 			{
 				const jcu_comp *cp = &im->comp[sc->comp[i]];
 				const int hn = ncs == 1 ? 1 : cp->h, vn = ncs == 1 ? 1 : cp->v;
-				s_coff[i] = cp->coef_off;
-				s_bw[i] = cp->bw;
-				s_hn[i] = hn;
-				s_vn[i] = vn;
+				sh.coff[i] = cp->coef_off;
+				sh.bw[i] = cp->bw;
+				sh.hn[i] = hn;
+				sh.vn[i] = vn;
 				for (int y = 0; y < vn; ++y)
 					for (int x = 0; x < hn; ++x)
 						if (n < ENTB_MAX_MCU_BLOCKS)
@@ -308,6 +293,26 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 		sh.nblk = n;
 	}
 	__syncthreads();
+}
+
+/*
+ * grid = CTA work items (EntWork) of one wave restricted to baseline scans; thread t decodes restart
+ * segment (work.seg_first + t) of the CTA's scan.
+ */
+__global__ void __launch_bounds__(ENTB_THREADS)
+k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans,
+						 const jcu_image *__restrict__ images, const uint32_t *__restrict__ seg_start,
+						 const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ bitstream,
+						 int16_t *__restrict__ coef, int32_t *__restrict__ img_err)
+{
+	__shared__ EntbShared sh;
+	__shared__ __align__(16) uint32_t s_slots[ENTB_THREADS * ENTB_SLOT_WORDS];
+
+	const int tid = threadIdx.x;
+	const EntWork w = work[blockIdx.x];
+	const jcu_scan *sc = &scans[w.scan];
+	const jcu_image *im = &images[sc->image];
+	entb_setup(sh, sc, im, huff, tid, ENTB_THREADS);
 
 	/* ---- this thread's segment ---- */
 	const bool active = (uint32_t)tid < w.nseg;
@@ -380,8 +385,8 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 			__syncwarp();
 			if (live)
 			{
-				const int bx = ux * s_hn[s] + (int)((ent >> 4) & 15u), by = uy * s_vn[s] + (int)((ent >> 8) & 15u);
-				uint4 *d4 = reinterpret_cast<uint4 *>(coef + s_coff[s] + ((size_t)by * s_bw[s] + bx) * 64);
+				const int bx = ux * sh.hn[s] + (int)((ent >> 4) & 15u), by = uy * sh.vn[s] + (int)((ent >> 8) & 15u);
+				uint4 *d4 = reinterpret_cast<uint4 *>(coef + sh.coff[s] + ((size_t)by * sh.bw[s] + bx) * 64);
 				uint4 *s4 = reinterpret_cast<uint4 *>(slot_w);
 				const unsigned key = coef_key(d4);
 #pragma unroll

@@ -115,7 +115,9 @@ typedef struct
 	double coef_bytes;	/* algorithmic bytes read by the fused kernel: 128 B x coefficient blocks */
 	double out_bytes;		/* algorithmic bytes written: n x width x height summed */
 	int launches;			/* kernels launched by the last run */
-	int reserved[5];
+	int selfsync_scans;	/* scans decoded by the self-synchronising path (streams without restart markers) */
+	int selfsync_rounds; /* refine rounds that path needed to converge */
+	int reserved[3];
 } stbi_jpeg_batch_timings;
 
 STBIDEF stbi_jpeg_batch *stbi_jpeg_batch_create(const stbi_jpeg_batch_params *params);

@@ -137,6 +137,8 @@ typedef struct
 {
 	float h2d_ms, entropy_ms, idct_ms, d2h_ms, total_ms;
 	int32_t launches;
+	int32_t ss_scans;	 /* scans decoded by the self-synchronising path in the last run */
+	int32_t ss_rounds; /* refine rounds it needed */
 } jcu_timings;
 
 typedef struct jcu_ctx jcu_ctx;

@@ -138,3 +138,39 @@ def test_full_size_1080p_420_rst16(oracle, decoder):
     outs = decoder.decode(datas, 3)
     for i, (data, got) in enumerate(zip(datas, outs)):
         _check(oracle, got, data, 3, f"1080p #{i}")
+
+
+@pytest.mark.parametrize("entropy_mode", [1, 2])
+def test_restartless_streams_serial_and_selfsync(oracle, entropy_mode):
+    """Baseline scans without restart markers: entropy_mode 1 = one thread per scan (serial, as the reference),
+    2 = self-synchronising speculative decoder forced even for tiny scans.  Both must be bit-exact."""
+    cases = [c for c in S.small_matrix()
+             if c[0] in ("420", "444", "gray", "420_opt", "422", "440", "411", "420_nonint", "cmyk", "ycck", "420_q100",
+                         "420_q10_dqt16", "rgb", "ycc_nojfif", "410", "441")]
+    datas = [S.stream(f, w, h, k) for f, w, h, k in cases]
+    d = ic.BatchDecoder(device=0, entropy_mode=entropy_mode)
+    for rc in (0, 3):
+        outs = d.decode(datas, rc)
+        for (f, w, h, k), data, got in zip(cases, datas, outs):
+            _check(oracle, got, data, rc, f"mode{entropy_mode} {f} {w}x{h} kind{k} req{rc}")
+        tm = d.timings()
+        assert (tm["selfsync_scans"] > 0) == (entropy_mode == 2), tm
+    d.close()
+
+
+def test_selfsync_full_size_444_and_gray(oracle, decoder):
+    """BASELINE.json configs[2]: 1080p 4:4:4 colour and 8-bit grayscale without restart markers (auto mode picks
+    the self-synchronising path for scans this long), plus 4:2:0 and a dense-noise image."""
+    from tools import testenc as te
+
+    datas = []
+    datas += te.encode_many(2, 1920, 1080, kind=-1, base_seed=77, quality=90, subsampling="444")
+    datas += te.encode_many(2, 1920, 1080, kind=-1, base_seed=78, quality=90, colorspace=te.CS_GRAY)
+    datas += te.encode_many(2, 1920, 1080, kind=-1, base_seed=79, quality=90, subsampling="420")
+    datas += te.encode_many(1, 1000, 700, kind=-1, base_seed=80, quality=100, subsampling="420", optimize=True)
+    outs = decoder.decode(datas, 3)
+    for i, (data, got) in enumerate(zip(datas, outs)):
+        _check(oracle, got, data, 3, f"selfsync 1080p #{i}")
+    tm = decoder.timings()
+    assert tm["selfsync_scans"] >= 7 and 1 <= tm["selfsync_rounds"] <= 2000, tm  # dense q100 noise re-syncs slowly
+    print("self-sync:", tm["selfsync_scans"], "scans,", tm["selfsync_rounds"], "refine rounds")

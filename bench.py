@@ -37,7 +37,7 @@ UNIT = "MP/s"
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--images", type=int, default=1024, help="images per GPU per step")
@@ -251,6 +251,13 @@ def main():
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6.65 TB/s"
     algo_bytes = tm["coef_bytes"] + tm["out_bytes"]
+    traffic = None
+    try:  # dram__bytes_read+write of one ncu --set full capture (profiles/), scaled per image to this launch
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic_fused420.json")))
+        if args.subsampling == "420" and not args.gray and (args.width, args.height) == (1920, 1080):
+            traffic = tj["dram_bytes_per_image"] * args.images
+    except Exception:
+        pass
     idct_step_ms = idct_ms / args.steps
     achieved = algo_bytes / 1e9 / (idct_step_ms / 1e3) if idct_step_ms > 0 else 0.0
     ent_step_ms = ent_ms / args.steps
@@ -317,13 +324,16 @@ def main():
             "clocks": clocks,
             "e2e": e2e,
             "gpu_launches": launches,
-            "roofline": {"bound": "hbm", "kernel": "k_fused_420<3>", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak if peak else None, "traffic": None,
+            "roofline": {"bound": "hbm", "kernel": "k_fused420_strip<3,false>" if args.subsampling == "420" and not args.gray
+                         else "k_fused_444/gray", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak if peak else None, "traffic": traffic,
+                         "traffic_source": "ncu dram__bytes_read+write per image (profiles/traffic_fused420.json) x images",
                          "peak_source": peak_src, "algorithmic_bytes_per_launch": algo_bytes,
                          "ms_per_launch": idct_step_ms},
             "cpu_baseline": cpu,
             "stages": {"entropy_ms": ent_step_ms, "idct_color_ms": idct_step_ms,
                        "entropy_bits_per_s_per_sm": bits_per_s_sm, "entropy_gbit_per_s": bits_per_s_sm * sms / 1e9,
+                       "selfsync_scans": tm.get("selfsync_scans"), "selfsync_rounds": tm.get("selfsync_rounds"),
                        "wall_ms_per_step": wall_ms / args.steps},
         }
         print(json.dumps(line), flush=True)

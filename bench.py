@@ -287,7 +287,8 @@ def main():
             outs[i] = pin_out.ptr + i * per
             caps[i] = per
         st = (C.c_int * n_e)()
-        e_dec = ic.BatchDecoder(device=local_rank, profile=False, chunk_images=int(os.environ.get("BENCH_CHUNK", "0")))
+        e_dec = ic.BatchDecoder(device=local_rank, profile=False, chunk_images=int(os.environ.get("BENCH_CHUNK", "0")),
+                                host_threads=max(2, ncores // world))  # ranks share the host cores
         e_dec.decode_into(bufs, lens, n_e, 3, outs, caps, None, None, None, st)  # warm-up (allocations)
         barrier()
         t0 = time.perf_counter()

@@ -18,7 +18,8 @@ class LibraryMissing(RuntimeError):
 
 
 def lib_path() -> str:
-    return os.path.join(HERE, _LIB_NAME)
+    # IMAGE_CODECS_B200_LIB: an alternative build of the same library (kernel tuning experiments, tools/build_variant.sh)
+    return os.environ.get("IMAGE_CODECS_B200_LIB") or os.path.join(HERE, _LIB_NAME)
 
 
 class Params(C.Structure):

@@ -37,6 +37,7 @@ struct jcu_ctx
 	bool d2h_open = false;
 	DevBuf bits, images, scans, segs, huff, work, coef, planes, out, err, lists;
 	DevBuf ss_work, ss_scans, ss_exit_a, ss_exit_b, ss_entry, ss_nblk, ss_first, ss_changed;
+	DevBuf uslab, useg_len; /* unstuffed copy of the baseline segments (jpeg_entropy_baseline.cuh) */
 	std::vector<SsWork> ss_work_h; /* self-synchronising decode: CTA work items over all waves */
 	std::vector<SsScan> ss_scan_h;
 	uint32_t ss_nsub_total = 0, ss_max_nsub = 0;
@@ -48,6 +49,7 @@ struct jcu_ctx
 	std::vector<EntWork> work_h;
 	std::vector<int> wave_off; /* n_waves + 1 offsets into work_h */
 	std::vector<int> wave_nbase; /* per wave: leading work items that are baseline scans */
+	std::vector<char> wave_two;	  /* per wave: every baseline scan uses <= 2 distinct DC and <= 2 distinct AC tables */
 	std::vector<int32_t> list_h; /* image lists per path, concatenated */
 	int list_off[4] = {0, 0, 0, 0}, list_n[4] = {0, 0, 0, 0};
 	int tiles[4] = {0, 0, 0, 0};
@@ -123,6 +125,9 @@ extern "C" int jcu_ctx_create(int device, int profile, int entropy_mode, jcu_ctx
 	cudaEvent_t *evs[] = {&c->ev_h2d0, &c->ev_h2d1, &c->ev_run0, &c->ev_ent1, &c->ev_out1, &c->ev_d2h0, &c->ev_d2h1};
 	for (auto ev : evs)
 		cudaEventCreate(ev);
+	/* tables (static) + slots and rings (dynamic) exceed the 48 KB default */
+	cudaFuncSetAttribute(k_entropy_baseline<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ENTB_DYN_SMEM);
+	cudaFuncSetAttribute(k_entropy_baseline<4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ENTB_DYN_SMEM);
 	*out = c;
 	return 0;
 }
@@ -134,7 +139,7 @@ extern "C" void jcu_ctx_destroy(jcu_ctx *c)
 	cudaSetDevice(c->device);
 	cudaStreamSynchronize(c->stream);
 	DevBuf *bufs[] = {&c->bits, &c->images, &c->scans, &c->segs, &c->huff, &c->work, &c->coef, &c->planes, &c->out, &c->err, &c->lists,
-							&c->ss_work, &c->ss_scans, &c->ss_exit_a, &c->ss_exit_b, &c->ss_entry, &c->ss_nblk, &c->ss_first, &c->ss_changed};
+							&c->ss_work, &c->ss_scans, &c->ss_exit_a, &c->ss_exit_b, &c->ss_entry, &c->ss_nblk, &c->ss_first, &c->ss_changed, &c->uslab, &c->useg_len};
 	for (auto b : bufs)
 		if (b->p)
 			cudaFree(b->p);
@@ -278,6 +283,7 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 		c->need_clear = true; /* phase 4 writes single coefficients into zeroed blocks */
 	c->wave_off.assign((size_t)b->n_waves + 1, 0);
 	c->wave_nbase.assign((size_t)b->n_waves, 0);
+	c->wave_two.assign((size_t)b->n_waves, 1);
 	for (int w = 0; w < b->n_waves; ++w)
 	{
 		c->wave_off[w] = (int)c->work_h.size();
@@ -288,12 +294,30 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 				const jcu_scan &sc = b->scans[s];
 				if (sc.wave != w || !imgs[sc.image].ok || is_ss[s] || (sc.kind == JCU_SCAN_BASELINE) != (pass == 0))
 					continue;
-				for (uint32_t f = 0; f < sc.nseg; f += ENT_THREADS)
+				if (pass == 0)
+				{
+					int nd = 0, na = 0;
+					for (int i = 0; i < sc.ncomp; ++i)
+					{
+						bool newd = true, newa = true;
+						for (int j = 0; j < i; ++j)
+						{
+							newd = newd && sc.dc_spec[j] != sc.dc_spec[i];
+							newa = newa && sc.ac_spec[j] != sc.ac_spec[i];
+						}
+						nd += newd;
+						na += newa;
+					}
+					if (nd > 2 || na > 2)
+						c->wave_two[w] = 0;
+				}
+				const uint32_t per_cta = pass == 0 ? ENTB_THREADS : ENT_THREADS;
+				for (uint32_t f = 0; f < sc.nseg; f += per_cta)
 				{
 					EntWork wk;
 					wk.scan = s;
 					wk.seg_first = f;
-					wk.nseg = std::min<uint32_t>(ENT_THREADS, sc.nseg - f);
+					wk.nseg = std::min<uint32_t>(per_cta, sc.nseg - f);
 					c->work_h.push_back(wk);
 				}
 			}
@@ -305,6 +329,16 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 
 	/* ---- device buffers ---- */
 	CK(ensure(c->bits, b->bitstream_bytes + 64));
+	{
+		bool any_base = false;
+		for (int w = 0; w < b->n_waves; ++w)
+			any_base = any_base || c->wave_nbase[w] > 0;
+		if (any_base)
+		{
+			CK(ensure(c->uslab, b->bitstream_bytes + 32 * ((size_t)b->n_segs + 4)));
+			CK(ensure(c->useg_len, sizeof(uint32_t) * std::max<size_t>(1, b->n_segs)));
+		}
+	}
 	CK(ensure(c->images, sizeof(jcu_image) * std::max(1, b->n_images)));
 	CK(ensure(c->scans, sizeof(jcu_scan) * std::max(1, b->n_scans)));
 	CK(ensure(c->segs, sizeof(uint32_t) * std::max<size_t>(1, b->n_segs)));
@@ -374,9 +408,17 @@ extern "C" int jcu_run(jcu_ctx *c)
 		const EntWork *wk = (const EntWork *)c->work.p + c->wave_off[w];
 		if (nb > 0)
 		{
-			k_entropy_baseline<<<nb, ENTB_THREADS, 0, st>>>(wk, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p,
-																			(const jcu_huff_spec *)c->huff.p, (const uint8_t *)c->bits.p,
-																			(int16_t *)c->coef.p, (int32_t *)c->err.p);
+			k_unstuff<<<nb, ENTB_THREADS, 0, st>>>(wk, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p,
+																(const uint8_t *)c->bits.p, (uint8_t *)c->uslab.p, (uint32_t *)c->useg_len.p);
+			c->launches++;
+			if (c->wave_two[w])
+				k_entropy_baseline<2, 2><<<nb, ENTB_THREADS, ENTB_DYN_SMEM, st>>>(
+					wk, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p, (const jcu_huff_spec *)c->huff.p,
+					(const uint8_t *)c->uslab.p, (const uint32_t *)c->useg_len.p, (int16_t *)c->coef.p, (int32_t *)c->err.p);
+			else
+				k_entropy_baseline<4, 4><<<nb, ENTB_THREADS, ENTB_DYN_SMEM, st>>>(
+					wk, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p, (const jcu_huff_spec *)c->huff.p,
+					(const uint8_t *)c->uslab.p, (const uint32_t *)c->useg_len.p, (int16_t *)c->coef.p, (int32_t *)c->err.p);
 			c->launches++;
 		}
 		if (n - nb > 0)

@@ -2,26 +2,39 @@
  * jpeg_entropy_baseline.cuh -- baseline (SOF0/1) Huffman entropy decode, lock-step edition (sm_100a).
  *
  * Replaces stbi__jpeg_decode_block (jpeg.c:308-370) driven by stbi__parse_entropy_coded_data
- * (jpeg.c:1155-1234) for every baseline scan of a batch in one launch.  The progressive block
- * decoders stay in jpeg_entropy.cuh.
+ * (jpeg.c:1155-1234) for every baseline scan of a batch.  The progressive block decoders stay in
+ * jpeg_entropy.cuh.  Two kernels per wave:
  *
- * Decomposition: one thread = one restart segment (stbi__jpeg_reset, jpeg.c:1142, clears every
- * carried state at a restart marker), ENTB_THREADS segments of ONE scan per CTA so the scan's
- * tables are built once in shared memory.  All lanes of a warp walk the same (MCU, block) position
- * of their own segment, so the per-block control flow is warp-uniform; the only divergent loop is
- * the AC symbol loop, whose body is a single straight-line path:
+ *   k_unstuff           one thread per restart segment copies the segment's entropy-coded bytes into a
+ *                       second slab with the byte stuffing of stbi__grow_buffer_unsafe (jpeg.c:167-187)
+ *                       already resolved: FF 00 -> FF, fill bytes dropped, everything from the first
+ *                       marker on cut off; output as big-endian 32-bit words, zero padded to 16 bytes.
+ *   k_entropy_baseline  one thread = one restart segment (stbi__jpeg_reset, jpeg.c:1142, clears every
+ *                       carried state at a restart marker), ENTB_THREADS segments of ONE scan per CTA so
+ *                       the scan's tables are built once in shared memory.  All lanes of a warp walk the
+ *                       same (MCU, block) position of their own segment, so the per-block control flow is
+ *                       warp-uniform; the only divergent loop is the AC symbol loop.
  *
- *   entry  = lut[top 9 bits]            one 32-bit entry: code length | magnitude bits | k advance
+ * With stuffing out of the way the bit reader is stateless: a lane keeps only its bit position `bp`; the
+ * next 32 stream bits are funnelshift(ring[bp/32], ring[bp/32 + 1], bp % 32), read from a per-lane ring of
+ * 32 words in shared memory ([word][lane] layout: conflict-free) that cp.async tops up at warp-uniform
+ * checkpoints (block start and every ENTB_CHECK_EVERY-th AC symbol).  A checkpoint waits only for the
+ * copies of the checkpoint before the previous one, so a copy has two intervals to land and the symbol loop
+ * never touches global memory.  No underflow is possible: a symbol is at most 16 + 15 bits, an interval at
+ * most ENTB_CHECK_EVERY symbols, and the ring runs >= 105 bytes ahead of what three intervals can consume
+ * (see ebr_checkpoint).  Past the end of a segment the ring is zero filled, which is what the reference
+ * feeds after a marker or the end of the file (jpeg.c:176-184, common.c:39).
+ *
+ * One AC symbol is a single straight-line path:
+ *
+ *   entry  = lut[top 11 bits]           one 16-bit entry: k advance | magnitude bits | code length
  *   value  = extend(next `size` bits)   branch-free form of stbi__extend_receive (jpeg.c:250)
  *   slot[natural(k + run)] = (short)(value * q)      dequantised at decode time like jpeg.c:325,345,365
  *   k     += run + 1   (EOB: += 64, ZRL: += 16)
  *
  * EOB/ZRL need no branch: they carry size 0, so they store a zero at a position that has not been
- * written yet (coefficients are produced in increasing zig-zag order).  Codes longer than 9 bits
- * take a canonical search (same result as jpeg.c:217-241).  The bit buffer holds >= 32 valid bits
- * at every symbol start (a code is <= 16 bits and its magnitude <= 15), so one symbol works on
- * the top 32-bit word only.  Refill is word-at-a-time with the next word already in a register;
- * a word containing 0xFF (stuffing, fill bytes, markers: jpeg.c:167-187) drops to a byte loop.
+ * written yet (coefficients are produced in increasing zig-zag order).  Codes longer than the table's
+ * prefix take a canonical search (same result as jpeg.c:217-241).
  *
  * Output: int16 coefficients, natural order, 128-byte blocks, written once per block from a
  * zeroed shared-memory slot (the memset of jpeg.c:320).
@@ -33,14 +46,19 @@
 #include "../../include/jpeg_cuda_abi.h"
 #include "jpeg_entropy.cuh"
 
-#define ENTB_THREADS 128
-#define ENTB_SLOT_WORDS 36 /* 64 int16 + 4 pad words (bank spread of the 16-byte flush reads) */
+#ifndef ENTB_THREADS
+#define ENTB_THREADS 256 /* restart segments per CTA: the tables are shared by more lanes, more warps fit an SM */
+#endif
+#define ENTB_SLOT_WORDS 32 /* 64 int16; byte o of lane l's block sits at o ^ entb_slot_key(l) */
 #define ENTB_MAX_MCU_BLOCKS 64
 
 #define ENTB_DC_BITS 9
 #define ENTB_AC_BITS 11
 
-/* 16-bit lookup entry: len (5) | size (4) << 5 | kadv (7) << 9 ; 0 = code longer than the table's prefix */
+/* 16-bit lookup entry: kadv (7) | size (4) << 7 | len (5) << 11 ; 0 = code longer than the table's prefix */
+#define ENTB_E_KADV(e) ((e) & 127u)
+#define ENTB_E_SIZE(e) (((e) >> 7) & 15u)
+#define ENTB_E_LEN(e) ((e) >> 11)
 template <int BITS>
 struct EntbLutT
 {
@@ -52,17 +70,20 @@ struct EntbLutT
 typedef EntbLutT<ENTB_DC_BITS> EntbDc;
 typedef EntbLutT<ENTB_AC_BITS> EntbAc;
 
-struct EntbShared
+template <int ND, int NA>
+struct EntbSharedT
 {
-	EntbDc dc[4];					 /* per scan-component slot */
-	EntbAc ac[4];
-	uint32_t zq[4][128];			 /* per slot: natural index | quantiser << 16, indexed by zig-zag position;
+	EntbDc dc[ND];					 /* distinct DC tables of the scan, compact ids */
+	EntbAc ac[NA];
+	uint32_t zq[4][128];			 /* per slot: 2 * natural index | quantiser << 16, indexed by zig-zag position;
 											 positions 64..127 alias natural 63 like the reference's padded table (jpeg.c:303) */
 	uint32_t blk[ENTB_MAX_MCU_BLOCKS]; /* per block of an MCU: slot | dx << 4 | dy << 8 | dc lut << 12 | ac lut << 16 */
 	int nblk;
 	unsigned long long coff[4]; /* per slot: first coefficient of the component in the slab */
 	int bw[4], hn[4], vn[4];	 /* per slot: blocks per plane row; blocks per MCU across / down (1 x 1 in single-component scans) */
 };
+typedef EntbSharedT<4, 4> EntbShared;
+#define ENTB_ZQ_NAT(e) (((e) & 0xffffu) >> 1)
 
 /* entry for symbol `sym` of code length l (l <= 9) */
 __device__ __forceinline__ uint32_t entb_entry(int sym, int l, bool is_dc)
@@ -79,7 +100,7 @@ __device__ __forceinline__ uint32_t entb_entry(int sym, int l, bool is_dc)
 		const int run = sym >> 4;
 		kadv = size ? run + 1 : (sym == 0xF0 ? 16 : 64); /* s == 0: ZRL or end of block (jpeg.c:352-355) */
 	}
-	return (uint32_t)l | ((uint32_t)size << 5) | ((uint32_t)kadv << 9);
+	return (uint32_t)kadv | ((uint32_t)size << 7) | ((uint32_t)l << 11);
 }
 
 template <int BITS>
@@ -129,147 +150,54 @@ __device__ __forceinline__ void entb_lut_build(EntbLutT<BITS> *L, const jcu_huff
 }
 
 
-/* ---- bit reader: 64-bit MSB-aligned buffer over one file (base pointer is CTA-uniform),
- *      next aligned word already in a register ---- */
-struct EBR
-{
-	uint32_t pos, len; /* byte offset in the file; file length */
-	uint64_t buf;
-	int nbits;
-	uint32_t w; /* word at pos if pos is 4-aligned and pos + 4 <= len, else 0xffffffff (forces the byte path) */
-};
-
-__device__ __forceinline__ uint32_t ebr_prefetch(const uint8_t *__restrict__ base, uint32_t pos, uint32_t len)
-{
-	return (((pos & 3u) == 0u) && pos + 4u <= len) ? __ldg(reinterpret_cast<const uint32_t *>(base + pos)) : 0xffffffffu;
-}
-
-/* byte path with the stuffing rules of stbi__grow_buffer_unsafe (jpeg.c:167-187): FF 00 -> FF, FF FF.. fill,
-   FF xx -> marker: stop consuming (pos = len) and feed zero bits; past the end of the file reads 0 (common.c:39).
-   Loops until at least 32 bits are valid and the reader is back on an aligned word (or out of data). */
-__device__ __forceinline__ void ebr_slow(const uint8_t *__restrict__ base, EBR &br)
-{
-	do
-	{
-		uint32_t b = 0;
-		if (br.pos < br.len)
-		{
-			b = base[br.pos++];
-			if (b == 0xff)
-			{
-				uint32_t q = br.pos;
-				uint32_t c = q < br.len ? base[q] : 0u;
-				while (c == 0xff)
-				{
-					++q;
-					c = q < br.len ? base[q] : 0u;
-				}
-				if (c == 0)
-					br.pos = q < br.len ? q + 1 : br.len;
-				else
-				{
-					br.pos = br.len;
-					b = 0;
-				}
-			}
-		}
-		br.buf |= (uint64_t)b << (56 - br.nbits);
-		br.nbits += 8;
-	} while (br.nbits <= 56 && (br.nbits < 32 || br.pos >= br.len || (br.pos & 3u) != 0u));
-	br.w = ebr_prefetch(base, br.pos, br.len);
-}
-
-__device__ __forceinline__ uint32_t shr_clamp(uint32_t x, uint32_t n) /* n >= 32 gives 0 (PTX shr semantics) */
-{
-	uint32_t d;
-	asm("shr.u32 %0, %1, %2;" : "=r"(d) : "r"(x), "r"(n));
-	return d;
-}
-
-/*
- * One Huffman symbol plus its magnitude bits.  Returns false for "bad huffman code" (jpeg.c:317,351).
- * value = extended magnitude (0 when the symbol carries no bits); kadv = k advance (AC tables).
- * The refill is predicated, not branched: nearly every lock-step iteration has SOME lane short of
- * bits, so a branch would serialise a 3-lane refill against the rest of the warp every time.
- */
-template <int BITS, bool IS_DC>
-__device__ __forceinline__ bool entb_symbol(const uint8_t *__restrict__ base, EBR &br, const EntbLutT<BITS> *__restrict__ L,
-														  int &value, int &kadv)
-{
-	{
-		const bool need = br.nbits < 32;
-		const uint32_t w = br.w;
-		const uint32_t ff = ((w & 0x7f7f7f7fu) + 0x01010101u) & w & 0x80808080u;
-		if (need && ff)
-			ebr_slow(base, br); /* leaves >= 32 bits */
-		else
-		{
-			const uint64_t ins = (uint64_t)__byte_perm(w, 0, 0x0123) << ((32 - br.nbits) & 63);
-			br.buf |= need ? ins : 0ull;
-			br.nbits += need ? 32 : 0;
-			br.pos += need ? 4u : 0u;
-			if (need)
-				br.w = ebr_prefetch(base, br.pos, br.len);
-		}
-	}
-	const uint32_t top = (uint32_t)(br.buf >> 32);
-	uint32_t e = L->fast[top >> (32 - BITS)];
-	if (e == 0)
-	{
-		const uint32_t t16 = top >> 16;
-		int l = BITS + 1;
-		while (t16 >= L->limit[l])
-			++l;
-		if (l > 16)
-			return false;
-		e = entb_entry(L->vals[(L->base[l] + (int)(t16 >> (16 - l))) & 255], l, IS_DC);
-	}
-	const int len = (int)(e & 31u), size = (int)((e >> 5) & 15u);
-	kadv = (int)(e >> 9);
-	const uint32_t after = top << len;
-	const uint32_t s32 = 32u - (uint32_t)size;
-	const uint32_t v = shr_clamp(after, s32), mask = shr_clamp(0xffffffffu, s32);
-	const int t = (int)after >> 31;
-	value = (int)v - (int)(mask & ~(uint32_t)t);
-	const int total = len + size;
-	br.buf <<= total;
-	br.nbits -= total;
-	return true;
-}
-
 /* per-scan tables, built once per CTA by all its threads (slots sharing a DHT table share one lookup) */
-__device__ __forceinline__ void entb_setup(EntbShared &sh, const jcu_scan *sc, const jcu_image *im,
+template <int ND, int NA>
+__device__ __forceinline__ void entb_setup(EntbSharedT<ND, NA> &sh, const jcu_scan *sc, const jcu_image *im,
 														 const jcu_huff_spec *__restrict__ huff, int tid, int nthreads)
 {
 	const int ncs = sc->ncomp;
-	int lut_dc[4], lut_ac[4]; /* indices resolved after unrolling: no dynamic indexing */
+	int lut_dc[4], lut_ac[4]; /* compact table ids per slot; resolved after unrolling: no dynamic indexing */
+	int nd = 0, na = 0;
 #pragma unroll
 	for (int i = 0; i < 4; ++i)
 	{
-		lut_dc[i] = i;
-		lut_ac[i] = i;
+		lut_dc[i] = 0;
+		lut_ac[i] = 0;
 		if (i < ncs)
 		{
+			int ad = -1, aa = -1;
 #pragma unroll
 			for (int j = 0; j < 4; ++j)
 				if (j < i)
 				{
-					if (sc->dc_spec[j] == sc->dc_spec[i] && lut_dc[i] == i)
-						lut_dc[i] = lut_dc[j];
-					if (sc->ac_spec[j] == sc->ac_spec[i] && lut_ac[i] == i)
-						lut_ac[i] = lut_ac[j];
+					if (sc->dc_spec[j] == sc->dc_spec[i] && ad < 0)
+						ad = lut_dc[j];
+					if (sc->ac_spec[j] == sc->ac_spec[i] && aa < 0)
+						aa = lut_ac[j];
 				}
-			if (lut_dc[i] == i && sc->dc_spec[i] >= 0)
-				entb_lut_build(&sh.dc[i], &huff[sc->dc_spec[i]], true, tid, nthreads);
-			if (lut_ac[i] == i && sc->ac_spec[i] >= 0)
-				entb_lut_build(&sh.ac[i], &huff[sc->ac_spec[i]], false, tid, nthreads);
+			if (ad < 0)
+			{
+				ad = min(nd, ND - 1); /* the host picks ND/NA >= distinct tables of every scan in the launch */
+				++nd;
+				if (sc->dc_spec[i] >= 0)
+					entb_lut_build(&sh.dc[ad], &huff[sc->dc_spec[i]], true, tid, nthreads);
+			}
+			if (aa < 0)
+			{
+				aa = min(na, NA - 1);
+				++na;
+				if (sc->ac_spec[i] >= 0)
+					entb_lut_build(&sh.ac[aa], &huff[sc->ac_spec[i]], false, tid, nthreads);
+			}
+			lut_dc[i] = ad;
+			lut_ac[i] = aa;
 		}
 	}
 	for (int i = tid; i < ncs * 128; i += nthreads)
 	{
 		const int s = i >> 7, z = i & 127;
 		const int nat = c_natural[z < 79 ? z : 79];
-		sh.zq[s][z] = (uint32_t)nat | ((uint32_t)im->qt[sc->comp[s]][nat] << 16);
+		sh.zq[s][z] = (uint32_t)(2 * nat) | ((uint32_t)im->qt[sc->comp[s]][nat] << 16);
 	}
 	if (tid == 0)
 	{
@@ -295,18 +223,312 @@ __device__ __forceinline__ void entb_setup(EntbShared &sh, const jcu_scan *sc, c
 	__syncthreads();
 }
 
+/* ------------------------------------------------------------------------------------------------------
+ * Unstuffed slab.  Segment g (global index into the segment table) of a file at slab offset data_off whose
+ * raw bytes start at file offset s is written at  data_off + align16(s) + 32 * g , zero padded to 16 bytes and
+ * followed by one all-zero 16-byte unit (the source of every fetch past the end).  Raw segments are at least
+ * 2 bytes apart (the RSTn marker) and never grow, so in 16-byte units the area of segment g holds
+ * ceil(s'/16) - ceil(s/16) + 2 >= ceil(raw/16) + 1 units: the areas cannot overlap; the slab needs
+ * bitstream_bytes + 32 * (n_segs + 2) bytes.  useg_len[g] = bytes produced, rounded up to 16.
+ * ------------------------------------------------------------------------------------------------------ */
+__device__ __forceinline__ size_t entb_useg_off(uint64_t data_off, uint32_t seg_start, uint32_t g)
+{
+	return (size_t)data_off + (((size_t)seg_start + 15u) & ~(size_t)15u) + 32u * (size_t)g;
+}
+
+struct UnstuffOut
+{
+	uint32_t *wp;	 /* next output word */
+	uint32_t pend;	 /* pending bytes, left aligned */
+	uint32_t nacc;	 /* 0..3 */
+	uint32_t words; /* words written */
+};
+__device__ __forceinline__ void unstuff_emit(UnstuffOut &o, uint32_t b)
+{
+	o.pend |= b << (24u - 8u * o.nacc);
+	if (++o.nacc == 4u)
+	{
+		*o.wp++ = o.pend;
+		++o.words;
+		o.pend = 0u;
+		o.nacc = 0u;
+	}
+}
+/* one byte with the rules of stbi__grow_buffer_unsafe (jpeg.c:167-187); false = marker or end of file */
+__device__ __forceinline__ bool unstuff_byte(const uint8_t *__restrict__ base, uint32_t &pos, uint32_t len, UnstuffOut &o)
+{
+	if (pos >= len)
+		return false;
+	const uint32_t b = base[pos++];
+	if (b == 0xffu)
+	{
+		uint32_t q = pos;
+		uint32_t c = q < len ? base[q] : 0u;
+		while (c == 0xffu)
+		{
+			++q;
+			c = q < len ? base[q] : 0u;
+		}
+		if (c != 0u)
+		{
+			pos = len;
+			return false; /* marker: nothing more from this segment */
+		}
+		pos = q < len ? q + 1u : len;
+	}
+	unstuff_emit(o, b);
+	return true;
+}
+
+/* one aligned raw word at `pos`: no 0xFF -> four output bytes at once; else the byte rules until the
+   reader is word aligned again (that may swallow following words: FF at the end, 00 at the start of the next) */
+__device__ __forceinline__ bool unstuff_word(const uint8_t *__restrict__ base, uint32_t wd, uint32_t &pos, uint32_t len, UnstuffOut &o)
+{
+	const uint32_t ff = ((wd & 0x7f7f7f7fu) + 0x01010101u) & wd & 0x80808080u;
+	if (ff == 0u)
+	{
+		const uint32_t be = __byte_perm(wd, 0, 0x0123);
+		const uint32_t sh = 8u * o.nacc;
+		*o.wp++ = o.pend | (be >> sh);
+		++o.words;
+		uint32_t np;
+		asm("shl.b32 %0, %1, %2;" : "=r"(np) : "r"(be), "r"(32u - sh)); /* shift 32 gives 0 */
+		o.pend = np;
+		pos += 4u;
+		return true;
+	}
+	bool more;
+	do
+		more = unstuff_byte(base, pos, len, o);
+	while (more && (pos & 3u) != 0u);
+	return more;
+}
+
+/*
+ * One thread per restart segment.  Raw bytes are read as aligned 16-byte units, the next unit requested
+ * before the current one is processed (the loop is a serial dependency chain per lane, so only a prefetch
+ * hides the memory latency).
+ */
+__global__ void __launch_bounds__(ENTB_THREADS)
+k_unstuff(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans, const jcu_image *__restrict__ images,
+			 const uint32_t *__restrict__ seg_start, const uint8_t *__restrict__ bitstream, uint8_t *__restrict__ uslab,
+			 uint32_t *__restrict__ useg_len)
+{
+	const EntWork w = work[blockIdx.x];
+	if (threadIdx.x >= w.nseg)
+		return;
+	const jcu_scan *sc = &scans[w.scan];
+	const jcu_image *im = &images[sc->image];
+	const uint32_t g = (uint32_t)sc->seg_first + w.seg_first + threadIdx.x;
+	const uint8_t *__restrict__ base = bitstream + im->data_off; /* 16-byte aligned */
+	const uint32_t len = im->data_len;
+	uint32_t pos = seg_start[g];
+	/* The host walks the scan with the same byte rules (jpeg_parse.c walk_entropy_segments), so the first
+	   marker after `pos` is the one that ends this segment: the loop below stops at least 2 raw bytes before
+	   the next segment's start and the output area (sized by the raw distance) cannot overflow. */
+	UnstuffOut o;
+	o.wp = reinterpret_cast<uint32_t *>(uslab + entb_useg_off(im->data_off, pos, g));
+	o.pend = 0u;
+	o.nacc = 0u;
+	o.words = 0u;
+	bool more = true;
+	while (more && (pos & 3u) != 0u)
+		more = unstuff_byte(base, pos, len, o);
+	/* the slab is padded (jpeg_cuda.cu: + 64 bytes), so a whole unit may be read whenever it starts inside the file */
+	uint32_t ub = pos & ~15u;
+	uint4 nextu = make_uint4(0u, 0u, 0u, 0u);
+	if (more && ub < len)
+		nextu = __ldg(reinterpret_cast<const uint4 *>(base + ub));
+	while (more)
+	{
+		const uint4 u = nextu;
+		const uint32_t nb = ub + 16u;
+		if (nb < len)
+			nextu = __ldg(reinterpret_cast<const uint4 *>(base + nb));
+		const uint32_t wv[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+		for (int k = 0; k < 4; ++k)
+		{
+			const uint32_t wpos = ub + 4u * (uint32_t)k;
+			if (more && pos == wpos)
+			{
+				if (wpos + 4u <= len)
+					more = unstuff_word(base, wv[k], pos, len, o);
+				else
+				{
+					do
+						more = unstuff_byte(base, pos, len, o);
+					while (more);
+				}
+			}
+		}
+		if (more)
+		{
+			const uint32_t want = pos & ~15u; /* a fill run may have jumped over whole units */
+			if (want != nb)
+				nextu = want < len ? __ldg(reinterpret_cast<const uint4 *>(base + want)) : make_uint4(0u, 0u, 0u, 0u);
+			ub = want;
+		}
+	}
+	if (o.nacc)
+	{
+		*o.wp++ = o.pend;
+		++o.words;
+	}
+	while (o.words & 3u)
+	{
+		*o.wp++ = 0u;
+		++o.words;
+	}
+	*reinterpret_cast<uint4 *>(o.wp) = make_uint4(0u, 0u, 0u, 0u);
+	useg_len[g] = o.words * 4u;
+}
+
+/* ------------------------------------------------------------------------------------------------------
+ * Bit reader over the unstuffed slab.  A lane keeps its bit position `bp` and the three stream words at
+ * bp/32, +1, +2 in registers (cur, nxt, nx2); the next 32 stream bits are funnelshift(cur:nxt, bp % 32).
+ * When a symbol crosses a word boundary the window slides and nx2 is re-read from the lane's ring of
+ * ENTB_RING_WORDS words in shared memory (row u of the ring = 16-byte unit (index % 4 == u) of every lane,
+ * filled by one 16-byte cp.async: the L1 pipe pays per distinct line touched, so 4-byte copies cost 4x).
+ * That read is consumed at the next crossing at the earliest, so the only shared-memory latency on the
+ * symbol-to-symbol dependency chain is the table lookup.
+ * ------------------------------------------------------------------------------------------------------ */
+#define ENTB_RING_WORDS 16
+#define ENTB_RING_ROW (ENTB_THREADS * 16) /* one 16-byte unit of every lane */
+#define ENTB_RING_BYTES (ENTB_RING_WORDS / 4 * ENTB_RING_ROW)
+#define ENTB_CHECK_EVERY 2 /* symbols between ring checkpoints */
+#define ENTB_DYN_SMEM (ENTB_THREADS * ENTB_SLOT_WORDS * 4 + ENTB_RING_BYTES + ENTB_THREADS * 8)
+
+struct EBR
+{
+	uint32_t bp;			 /* bit position in the segment's unstuffed stream */
+	uint32_t cur, nxt, nx2; /* words bp/32, bp/32 + 1, bp/32 + 2 */
+	uint32_t fw;			 /* next word to fetch (multiple of 4) */
+	uint32_t nwords;		 /* words the segment holds (multiple of 4); the 4 words behind them are zero */
+	const uint32_t *src; /* the segment in the unstuffed slab (16-byte aligned) */
+};
+
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a)
+{
+	uint32_t v;
+	asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+	return v;
+}
+__device__ __forceinline__ uint32_t lds_u32_m4(uint32_t a)
+{
+	uint32_t v;
+	asm volatile("ld.shared.u32 %0, [%1+-4];" : "=r"(v) : "r"(a));
+	return v;
+}
+__device__ __forceinline__ uint32_t lds_u16(uint32_t a)
+{
+	uint32_t v;
+	asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a));
+	return v;
+}
+__device__ __forceinline__ void sts_u16(uint32_t a, uint32_t v)
+{
+	asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ebr_ring_addr(uint32_t ring_lane, uint32_t word)
+{
+	return ring_lane + ((word >> 2) & (ENTB_RING_WORDS / 4 - 1u)) * ENTB_RING_ROW + ((word & 3u) << 2);
+}
+
+/*
+ * Warp-uniform checkpoint.  Each checkpoint commits one cp.async group and (WAIT) waits for all but the two
+ * newest: a copy has three intervals to land.  After a checkpoint that found room, fw >= (unit of bp) + 16
+ * words.  Between checkpoints j+2 and j+3 the reader touches at most word
+ * (bp_j + 4 intervals * ENTB_CHECK_EVERY symbols * 31 bits) / 32 + 2, i.e. less than 44 bytes past bp_j,
+ * which is below (unit of bp_j) + 64 bytes: issued at or before checkpoint j, landed.  One unit per
+ * checkpoint keeps up because an interval consumes < 128 bits.
+ */
+template <int MAX_UNITS, bool WAIT>
+__device__ __forceinline__ void ebr_checkpoint(uint32_t ring_lane, EBR &br)
+{
+	if (WAIT)
+		asm volatile("cp.async.wait_group 2;" ::: "memory");
+#pragma unroll
+	for (int u = 0; u < MAX_UNITS; ++u)
+	{
+		/* the slot still holds words fw-16..fw-13: they must lie below the unit bp is in */
+		if (br.fw + 4u <= ((br.bp >> 5) & ~3u) + ENTB_RING_WORDS)
+		{
+			const uint32_t *g = br.src + min(br.fw, br.nwords); /* past the end: the segment's zero unit */
+			const uint32_t d = ebr_ring_addr(ring_lane, br.fw);
+			asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(d), "l"(g) : "memory");
+			br.fw += 4u;
+		}
+	}
+	asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
+__device__ __forceinline__ uint32_t shr_clamp(uint32_t x, uint32_t n) /* n >= 32 gives 0 (PTX shr semantics) */
+{
+	uint32_t d;
+	asm("shr.u32 %0, %1, %2;" : "=r"(d) : "r"(x), "r"(n));
+	return d;
+}
+
+/*
+ * One Huffman symbol plus its magnitude bits.  Returns false for "bad huffman code" (jpeg.c:317,351).
+ * value = extended magnitude (0 when the symbol carries no bits); e = the symbol's table entry.
+ * `between` runs after the table lookup has been issued and before its result is needed.
+ */
+template <int BITS, bool IS_DC, typename F>
+__device__ __forceinline__ bool entb_symbol(uint32_t ring_lane, EBR &br, uint32_t fast_addr, const EntbLutT<BITS> *__restrict__ L,
+														  int &value, uint32_t &e, F between)
+{
+	const uint32_t top = __funnelshift_l(br.nxt, br.cur, br.bp);
+	e = lds_u16(fast_addr + ((top >> (32 - BITS)) << 1));
+	between();
+	if (e == 0u)
+	{
+		const uint32_t t16 = top >> 16;
+		int l = BITS + 1;
+		while (t16 >= L->limit[l])
+			++l;
+		if (l > 16)
+			return false;
+		e = entb_entry(L->vals[(L->base[l] + (int)(t16 >> (16 - l))) & 255], l, IS_DC);
+	}
+	const uint32_t len = ENTB_E_LEN(e), size = ENTB_E_SIZE(e);
+	const uint32_t after = top << len;
+	const uint32_t s32 = 32u - size;
+	const uint32_t v = shr_clamp(after, s32), mask = shr_clamp(0xffffffffu, s32);
+	const int t = (int)after >> 31;
+	value = (int)v - (int)(mask & ~(uint32_t)t);
+	const uint32_t nbp = br.bp + len + size;
+	/* a symbol is < 32 bits: at most one word boundary.  Predicated in place: no temporary whose copy would
+	   wait for the read that was just issued. */
+	asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %3, 0;\n\t@p mov.u32 %0, %1;\n\t@p mov.u32 %1, %2;\n\t"
+					 "@p ld.shared.u32 %2, [%4];\n\t}"
+					 : "+r"(br.cur), "+r"(br.nxt), "+r"(br.nx2)
+					 : "r"((nbp ^ br.bp) & 32u), "r"(ebr_ring_addr(ring_lane, (nbp >> 5) + 2u)));
+	br.bp = nbp;
+	return true;
+}
+
 /*
  * grid = CTA work items (EntWork) of one wave restricted to baseline scans; thread t decodes restart
- * segment (work.seg_first + t) of the CTA's scan.
+ * segment (work.seg_first + t) of the CTA's scan from the unstuffed slab.  <ND, NA> = distinct DC / AC
+ * tables the CTA can hold: the host launches <2, 2> when no scan of the wave needs more (the usual luma +
+ * chroma pair), which fits one more CTA per SM.  Dynamic shared memory (ENTB_DYN_SMEM): slots, then rings.
+ *
+ * The warp issues in order, so every shared-memory round trip that is consumed right away stalls all of
+ * it.  The symbol loop therefore has exactly one exposed round trip (the table lookup): the dequantiser
+ * entry of symbol i is requested as soon as its position is known and the coefficient is stored during
+ * the lookup of symbol i+1.
  */
+template <int ND, int NA>
 __global__ void __launch_bounds__(ENTB_THREADS)
 k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 						 const jcu_image *__restrict__ images, const uint32_t *__restrict__ seg_start,
-						 const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ bitstream,
-						 int16_t *__restrict__ coef, int32_t *__restrict__ img_err)
+						 const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ uslab,
+						 const uint32_t *__restrict__ useg_len, int16_t *__restrict__ coef, int32_t *__restrict__ img_err)
 {
-	__shared__ EntbShared sh;
-	__shared__ __align__(16) uint32_t s_slots[ENTB_THREADS * ENTB_SLOT_WORDS];
+	__shared__ EntbSharedT<ND, NA> sh;
+	extern __shared__ __align__(16) uint32_t s_dyn[];
 
 	const int tid = threadIdx.x;
 	const EntWork w = work[blockIdx.x];
@@ -322,19 +544,35 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 	const int u0 = ri ? (int)seg * ri : 0;
 	const int u1 = ri ? min(u0 + ri, total) : total;
 	const int nblk = sh.nblk;
-	const uint8_t *__restrict__ base = bitstream + im->data_off;
+	const uint32_t ring_lane = (uint32_t)__cvta_generic_to_shared(s_dyn + ENTB_THREADS * ENTB_SLOT_WORDS) + (uint32_t)tid * 16u;
 
 	EBR br;
-	br.len = im->data_len;
-	br.pos = active ? seg_start[sc->seg_first + seg] : br.len;
-	br.buf = 0;
-	br.nbits = 0;
-	br.w = ebr_prefetch(base, br.pos, br.len);
+	br.bp = 0u;
+	br.fw = 0u;
+	br.nwords = 0u;
+	br.src = reinterpret_cast<const uint32_t *>(uslab);
+	if (active)
+	{
+		const uint32_t g = (uint32_t)sc->seg_first + seg;
+		br.nwords = useg_len[g] >> 2;
+		br.src = reinterpret_cast<const uint32_t *>(uslab + entb_useg_off(im->data_off, seg_start[g], g));
+	}
+	ebr_checkpoint<ENTB_RING_WORDS / 4, false>(ring_lane, br);
+	asm volatile("cp.async.wait_all;" ::: "memory");
+	br.cur = lds_u32(ebr_ring_addr(ring_lane, 0u));
+	br.nxt = lds_u32(ebr_ring_addr(ring_lane, 1u));
+	br.nx2 = lds_u32(ebr_ring_addr(ring_lane, 2u));
 	int dc0 = 0, dc1 = 0, dc2 = 0, dc3 = 0;
 	bool failed = false;
 
-	uint32_t *slot_w = &s_slots[tid * ENTB_SLOT_WORDS];
-	int16_t *slot = reinterpret_cast<int16_t *>(slot_w);
+	uint32_t *slot_w = &s_dyn[tid * ENTB_SLOT_WORDS];
+	const uint32_t slot_addr = (uint32_t)__cvta_generic_to_shared(slot_w);
+	const uint32_t lane = (uint32_t)tid & 31u;
+	/* byte offset o of the lane's block sits at o ^ slot_key: chunk index ^ (lane & 7), word in chunk ^ (lane >> 3),
+	   so the 32 lanes of a warp storing the same coefficient position hit 32 different banks */
+	const uint32_t slot_key = ((lane & 7u) << 4) | ((lane >> 3) << 2);
+	unsigned long long *s_ptr = reinterpret_cast<unsigned long long *>(s_dyn + ENTB_THREADS * ENTB_SLOT_WORDS + ENTB_RING_BYTES / 4);
+	const int wbase = tid & ~31;
 #pragma unroll
 	for (int i = 0; i < 32; ++i)
 		slot_w[i] = 0u;
@@ -348,15 +586,20 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 		{
 			const uint32_t ent = sh.blk[b];
 			const int s = (int)(ent & 15u);
-			const EntbDc *Ldc = &sh.dc[(ent >> 12) & 3u];
-			const EntbAc *Lac = &sh.ac[(ent >> 16) & 3u];
-			const uint32_t *zq = sh.zq[s];
+			const EntbDc *Ldc = &sh.dc[(ent >> 12) & (ND - 1)];
+			const EntbAc *Lac = &sh.ac[(ent >> 16) & (NA - 1)];
+			const uint32_t dc_fast = (uint32_t)__cvta_generic_to_shared(Ldc->fast);
+			const uint32_t ac_fast = (uint32_t)__cvta_generic_to_shared(Lac->fast);
+			const uint32_t zq_addr = (uint32_t)__cvta_generic_to_shared(sh.zq[s]);
 			const bool live = live_u && !failed;
 			bool ok = false;
 			if (live)
 			{
-				int diff, kadv;
-				ok = entb_symbol<ENTB_DC_BITS, true>(base, br, Ldc, diff, kadv);
+				int diff;
+				uint32_t e;
+				ebr_checkpoint<1, true>(ring_lane, br);
+				uint32_t zqp = lds_u32(zq_addr); /* pending store: dequantiser entry and value of the previous symbol */
+				ok = entb_symbol<ENTB_DC_BITS, true>(ring_lane, br, dc_fast, Ldc, diff, e, [] {});
 				if (ok)
 				{
 					int dcp = s == 0 ? dc0 : s == 1 ? dc1 : s == 2 ? dc2 : dc3;
@@ -365,39 +608,59 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 					else if (s == 1) dc1 = dcp;
 					else if (s == 2) dc2 = dcp;
 					else dc3 = dcp;
-					slot[0] = (int16_t)(dcp * (int)(zq[0] >> 16));
-					int k = 1;
+					int valp = dcp;
+					/* kp walks the zig-zag table: kp = &zq[k]; the entry of the coefficient is the one before it */
+					uint32_t kp = zq_addr + 4u;
+					const uint32_t kend = zq_addr + 256u;
+					int it = 1;
 					do
 					{
 						int val;
-						if (!entb_symbol<ENTB_AC_BITS, false>(base, br, Lac, val, kadv))
+						if (++it > ENTB_CHECK_EVERY)
+						{
+							it = 1;
+							ebr_checkpoint<1, true>(ring_lane, br);
+						}
+						if (!entb_symbol<ENTB_AC_BITS, false>(ring_lane, br, ac_fast, Lac, val, e, [&] {
+								 sts_u16(slot_addr + ((zqp & 0xffffu) ^ slot_key), (uint32_t)(valp * (int)(zqp >> 16)));
+							 }))
 						{
 							ok = false;
 							break;
 						}
-						const uint32_t e = zq[k + kadv - 1];
-						k += kadv;
-						slot[e & 0xffffu] = (int16_t)(val * (int)(e >> 16));
-					} while (k < 64);
+						kp += ENTB_E_KADV(e) << 2;
+						zqp = lds_u32_m4(kp);
+						valp = val;
+					} while (kp < kend);
+					sts_u16(slot_addr + ((zqp & 0xffffu) ^ slot_key), (uint32_t)(valp * (int)(zqp >> 16)));
 				}
 				failed = !ok;
 			}
-			__syncwarp();
-			if (live)
+			/* ---- flush: the warp writes its 32 blocks as whole 128-byte lines (8 lanes per block), which costs the
+			   L1 pipe one line per 8 lanes instead of one per lane; the owner publishes its destination first ---- */
 			{
 				const int bx = ux * sh.hn[s] + (int)((ent >> 4) & 15u), by = uy * sh.vn[s] + (int)((ent >> 8) & 15u);
-				uint4 *d4 = reinterpret_cast<uint4 *>(coef + sh.coff[s] + ((size_t)by * sh.bw[s] + bx) * 64);
-				uint4 *s4 = reinterpret_cast<uint4 *>(slot_w);
-				const unsigned key = coef_key(d4);
-#pragma unroll
-				for (int q = 0; q < 8; ++q)
-				{
-					const uint4 v = s4[q];
-					if (ok)
-						d4[q ^ key] = v; /* slab chunk permutation (jpeg_coef_layout.cuh) */
-					s4[q] = make_uint4(0u, 0u, 0u, 0u);
-				}
+				const unsigned long long dst =
+					(live && ok) ? (unsigned long long)(coef + sh.coff[s] + ((size_t)by * sh.bw[s] + bx) * 64) : 0ull;
+				s_ptr[tid] = dst;
 			}
+			__syncwarp();
+#pragma unroll
+			for (int i = 0; i < 8; ++i)
+			{
+				const int o = 4 * i + (int)(lane >> 3); /* owner lane of the block this lane helps to write */
+				const uint32_t c = lane & 7u;			  /* natural chunk of that block */
+				uint4 *d4 = reinterpret_cast<uint4 *>(s_ptr[wbase + o]);
+				uint4 *src = reinterpret_cast<uint4 *>(&s_dyn[(wbase + o) * ENTB_SLOT_WORDS]) + (c ^ (uint32_t)(o & 7));
+				const uint4 v = *src;
+				*src = make_uint4(0u, 0u, 0u, 0u);
+				/* words of the chunk are permuted by (owner lane >> 3) == (i >> 1): a compile-time renaming */
+				const uint32_t wv[4] = {v.x, v.y, v.z, v.w};
+				const int r = (i >> 1) & 3;
+				if (d4)
+					d4[c ^ coef_key(d4)] = make_uint4(wv[0 ^ r], wv[1 ^ r], wv[2 ^ r], wv[3 ^ r]); /* slab chunk permutation */
+			}
+			__syncwarp();
 		}
 		if (++ux == upr)
 		{
@@ -405,6 +668,7 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 			++uy;
 		}
 	}
+	asm volatile("cp.async.wait_all;" ::: "memory"); /* no copy may land after the CTA's shared memory is reassigned */
 	if (failed)
 		atomicOr(&img_err[sc->image], 1);
 }

@@ -126,8 +126,8 @@ __device__ __forceinline__ bool ss_symbol(SBR &br, const EntbLutT<BITS> *__restr
 		}
 		e = entb_entry(L->vals[(L->base[l] + (int)(t16 >> (16 - l))) & 255], l, IS_DC);
 	}
-	const int len = (int)(e & 31u), size = (int)((e >> 5) & 15u);
-	kadv = (int)(e >> 9);
+	const int len = (int)ENTB_E_LEN(e), size = (int)ENTB_E_SIZE(e);
+	kadv = (int)ENTB_E_KADV(e);
 	const uint32_t after = top << len;
 	const uint32_t s32 = 32u - (uint32_t)size;
 	const uint32_t v = shr_clamp(after, s32), mask = shr_clamp(0xffffffffu, s32);
@@ -274,7 +274,7 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 			{
 				failed |= !ok;
 				if (ok && val)
-					blk[coef_pos((int)(e & 0xffffu), key)] = (int16_t)(val * (int)(e >> 16));
+					blk[coef_pos((int)ENTB_ZQ_NAT(e), key)] = (int16_t)(val * (int)(e >> 16));
 			}
 		}
 		if (k >= 64)

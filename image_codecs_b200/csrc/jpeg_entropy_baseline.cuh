@@ -45,6 +45,7 @@
 
 #include "../../include/jpeg_cuda_abi.h"
 #include "jpeg_entropy.cuh"
+#include "jpeg_unstuff.h"
 
 #ifndef ENTB_THREADS
 #define ENTB_THREADS 256 /* restart segments per CTA: the tables are shared by more lanes, more warps fit an SM */
@@ -236,78 +237,13 @@ __device__ __forceinline__ size_t entb_useg_off(uint64_t data_off, uint32_t seg_
 	return (size_t)data_off + (((size_t)seg_start + 15u) & ~(size_t)15u) + 32u * (size_t)g;
 }
 
-struct UnstuffOut
-{
-	uint32_t *wp;	 /* next output word */
-	uint32_t pend;	 /* pending bytes, left aligned */
-	uint32_t nacc;	 /* 0..3 */
-	uint32_t words; /* words written */
-};
-__device__ __forceinline__ void unstuff_emit(UnstuffOut &o, uint32_t b)
-{
-	o.pend |= b << (24u - 8u * o.nacc);
-	if (++o.nacc == 4u)
-	{
-		*o.wp++ = o.pend;
-		++o.words;
-		o.pend = 0u;
-		o.nacc = 0u;
-	}
-}
-/* one byte with the rules of stbi__grow_buffer_unsafe (jpeg.c:167-187); false = marker or end of file */
-__device__ __forceinline__ bool unstuff_byte(const uint8_t *__restrict__ base, uint32_t &pos, uint32_t len, UnstuffOut &o)
-{
-	if (pos >= len)
-		return false;
-	const uint32_t b = base[pos++];
-	if (b == 0xffu)
-	{
-		uint32_t q = pos;
-		uint32_t c = q < len ? base[q] : 0u;
-		while (c == 0xffu)
-		{
-			++q;
-			c = q < len ? base[q] : 0u;
-		}
-		if (c != 0u)
-		{
-			pos = len;
-			return false; /* marker: nothing more from this segment */
-		}
-		pos = q < len ? q + 1u : len;
-	}
-	unstuff_emit(o, b);
-	return true;
-}
-
-/* one aligned raw word at `pos`: no 0xFF -> four output bytes at once; else the byte rules until the
-   reader is word aligned again (that may swallow following words: FF at the end, 00 at the start of the next) */
-__device__ __forceinline__ bool unstuff_word(const uint8_t *__restrict__ base, uint32_t wd, uint32_t &pos, uint32_t len, UnstuffOut &o)
-{
-	const uint32_t ff = ((wd & 0x7f7f7f7fu) + 0x01010101u) & wd & 0x80808080u;
-	if (ff == 0u)
-	{
-		const uint32_t be = __byte_perm(wd, 0, 0x0123);
-		const uint32_t sh = 8u * o.nacc;
-		*o.wp++ = o.pend | (be >> sh);
-		++o.words;
-		uint32_t np;
-		asm("shl.b32 %0, %1, %2;" : "=r"(np) : "r"(be), "r"(32u - sh)); /* shift 32 gives 0 */
-		o.pend = np;
-		pos += 4u;
-		return true;
-	}
-	bool more;
-	do
-		more = unstuff_byte(base, pos, len, o);
-	while (more && (pos & 3u) != 0u);
-	return more;
-}
-
 /*
- * One thread per restart segment.  Raw bytes are read as aligned 16-byte units, the next unit requested
- * before the current one is processed (the loop is a serial dependency chain per lane, so only a prefetch
- * hides the memory latency).
+ * One thread per restart segment; all lanes of a warp step through aligned raw words of their own segment
+ * together.  A word without 0xFF is four output bytes; a word whose 0xFF bytes are all followed by 0x00 is
+ * compacted branch-free (zero-byte mask & shifted FF mask -> 4-bit drop mask -> PRMT selector); only an
+ * 0xFF followed by something else (a marker: the end of the segment, or fill bytes) takes the byte loop
+ * with the exact rules of the reference.  Raw bytes are read as aligned 16-byte units, the next unit
+ * requested before the current one is processed.
  */
 __global__ void __launch_bounds__(ENTB_THREADS)
 k_unstuff(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans, const jcu_image *__restrict__ images,
@@ -315,71 +251,84 @@ k_unstuff(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans, 
 			 uint32_t *__restrict__ useg_len)
 {
 	const EntWork w = work[blockIdx.x];
-	if (threadIdx.x >= w.nseg)
-		return;
 	const jcu_scan *sc = &scans[w.scan];
 	const jcu_image *im = &images[sc->image];
-	const uint32_t g = (uint32_t)sc->seg_first + w.seg_first + threadIdx.x;
+	const bool active = threadIdx.x < w.nseg;
+	const uint32_t g = (uint32_t)sc->seg_first + w.seg_first + (active ? threadIdx.x : 0u);
 	const uint8_t *__restrict__ base = bitstream + im->data_off; /* 16-byte aligned */
 	const uint32_t len = im->data_len;
 	uint32_t pos = seg_start[g];
 	/* The host walks the scan with the same byte rules (jpeg_parse.c walk_entropy_segments), so the first
 	   marker after `pos` is the one that ends this segment: the loop below stops at least 2 raw bytes before
 	   the next segment's start and the output area (sized by the raw distance) cannot overflow. */
+	__shared__ uint32_t s_stage[4 * ENTB_THREADS];
 	UnstuffOut o;
 	o.wp = reinterpret_cast<uint32_t *>(uslab + entb_useg_off(im->data_off, pos, g));
 	o.pend = 0u;
 	o.nacc = 0u;
 	o.words = 0u;
-	bool more = true;
-	while (more && (pos & 3u) != 0u)
-		more = unstuff_byte(base, pos, len, o);
-	/* the slab is padded (jpeg_cuda.cu: + 64 bytes), so a whole unit may be read whenever it starts inside the file */
-	uint32_t ub = pos & ~15u;
-	uint4 nextu = make_uint4(0u, 0u, 0u, 0u);
-	if (more && ub < len)
-		nextu = __ldg(reinterpret_cast<const uint4 *>(base + ub));
-	while (more)
+	o.stage = (uint32_t)__cvta_generic_to_shared(s_stage) + threadIdx.x * 4u;
+	o.stride = ENTB_THREADS * 4u;
+	bool more = active && pos < len;
+	/* Raw bytes are read as aligned 32-byte sectors (two 16-byte loads), the next sector requested before the
+	   current one is processed: the L1 is too small to keep a half-used sector per lane until the lane comes
+	   back for the other half.  The slab is padded (jpeg_cuda.cu: + 64 bytes), so a whole sector may be read
+	   whenever it starts inside the file. */
+	uint32_t ub = pos & ~31u;
+	uint4 na = make_uint4(0u, 0u, 0u, 0u), nb4 = na;
+	if (more)
 	{
-		const uint4 u = nextu;
-		const uint32_t nb = ub + 16u;
-		if (nb < len)
-			nextu = __ldg(reinterpret_cast<const uint4 *>(base + nb));
-		const uint32_t wv[4] = {u.x, u.y, u.z, u.w};
+		na = __ldg(reinterpret_cast<const uint4 *>(base + ub));
+		nb4 = __ldg(reinterpret_cast<const uint4 *>(base + ub + 16u));
+	}
+	while (__any_sync(0xffffffffu, more))
+	{
+		const uint4 u0 = na, u1 = nb4;
+		const uint32_t nb = ub + 32u;
+		if (more && nb < len)
+		{
+			na = __ldg(reinterpret_cast<const uint4 *>(base + nb));
+			nb4 = __ldg(reinterpret_cast<const uint4 *>(base + nb + 16u));
+		}
+		const uint32_t wv[9] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w, na.x};
 #pragma unroll
-		for (int k = 0; k < 4; ++k)
+		for (int k = 0; k < 8; ++k)
 		{
 			const uint32_t wpos = ub + 4u * (uint32_t)k;
-			if (more && pos == wpos)
+			const uint32_t d = pos - wpos; /* leading bytes of this word that are not ours (or already consumed) */
+			const bool mine = more && d < 4u;
+			const uint32_t wd = wv[k];
+			const uint32_t ffq = ((wd & 0x7f7f7f7fu) + 0x01010101u) & wd & 0x80808080u;
+			const bool fast = !mine || (d == 0u && wpos + 4u <= len && ffq == 0u);
+			if (__all_sync(0xffffffffu, fast))
 			{
-				if (wpos + 4u <= len)
-					more = unstuff_word(base, wv[k], pos, len, o);
-				else
+				if (mine)
 				{
-					do
-						more = unstuff_byte(base, pos, len, o);
-					while (more);
+					unstuff_append(o, __byte_perm(wd, 0, 0x0123), 4u);
+					pos = wpos + 4u;
 				}
+				continue;
 			}
+			if (mine)
+				more = unstuff_word(base, len, wpos, wd, wv[k + 1], pos, o);
 		}
 		if (more)
 		{
-			const uint32_t want = pos & ~15u; /* a fill run may have jumped over whole units */
+			const uint32_t want = pos & ~31u; /* a fill run may have jumped over whole sectors */
 			if (want != nb)
-				nextu = want < len ? __ldg(reinterpret_cast<const uint4 *>(base + want)) : make_uint4(0u, 0u, 0u, 0u);
+			{
+				na = want < len ? __ldg(reinterpret_cast<const uint4 *>(base + want)) : make_uint4(0u, 0u, 0u, 0u);
+				nb4 = want < len ? __ldg(reinterpret_cast<const uint4 *>(base + want + 16u)) : make_uint4(0u, 0u, 0u, 0u);
+			}
 			ub = want;
 		}
 	}
+	if (!active)
+		return;
 	if (o.nacc)
-	{
-		*o.wp++ = o.pend;
-		++o.words;
-	}
+		unstuff_put(o, o.pend);
 	while (o.words & 3u)
-	{
-		*o.wp++ = 0u;
-		++o.words;
-	}
+		unstuff_put(o, 0u);
 	*reinterpret_cast<uint4 *>(o.wp) = make_uint4(0u, 0u, 0u, 0u);
 	useg_len[g] = o.words * 4u;
 }

@@ -345,12 +345,15 @@ k_unstuff(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans, 
 #define ENTB_RING_WORDS 16
 #define ENTB_RING_ROW (ENTB_THREADS * 16) /* one 16-byte unit of every lane */
 #define ENTB_RING_BYTES (ENTB_RING_WORDS / 4 * ENTB_RING_ROW)
+/* bits 7..8 of a bit position select the unit: shift them to the unit stride (ENTB_THREADS is a power of two) */
+#define ENTB_RING_UNIT_SHIFT (ENTB_THREADS == 128 ? 4 : ENTB_THREADS == 256 ? 5 : 6)
+static_assert(ENTB_THREADS == 128 || ENTB_THREADS == 256 || ENTB_THREADS == 512, "ENTB_THREADS: 128, 256 or 512");
 #define ENTB_CHECK_EVERY 2 /* symbols between ring checkpoints */
 #define ENTB_DYN_SMEM (ENTB_THREADS * ENTB_SLOT_WORDS * 4 + ENTB_RING_BYTES + ENTB_THREADS * 8)
 
 struct EBR
 {
-	uint32_t bp;			 /* bit position in the segment's unstuffed stream */
+	uint32_t bp;			 /* bit position in the segment's unstuffed stream + 64, so that bp / 32 is the index of nx2 */
 	uint32_t cur, nxt, nx2; /* words bp/32, bp/32 + 1, bp/32 + 2 */
 	uint32_t fw;			 /* next word to fetch (multiple of 4) */
 	uint32_t nwords;		 /* words the segment holds (multiple of 4); the 4 words behind them are zero */
@@ -401,7 +404,7 @@ __device__ __forceinline__ void ebr_checkpoint(uint32_t ring_lane, EBR &br)
 	for (int u = 0; u < MAX_UNITS; ++u)
 	{
 		/* the slot still holds words fw-16..fw-13: they must lie below the unit bp is in */
-		if (br.fw + 4u <= ((br.bp >> 5) & ~3u) + ENTB_RING_WORDS)
+		if (br.fw + 4u <= (((br.bp >> 5) - 2u) & ~3u) + ENTB_RING_WORDS)
 		{
 			const uint32_t *g = br.src + min(br.fw, br.nwords); /* past the end: the segment's zero unit */
 			const uint32_t d = ebr_ring_addr(ring_lane, br.fw);
@@ -450,10 +453,14 @@ __device__ __forceinline__ bool entb_symbol(uint32_t ring_lane, EBR &br, uint32_
 	const uint32_t nbp = br.bp + len + size;
 	/* a symbol is < 32 bits: at most one word boundary.  Predicated in place: no temporary whose copy would
 	   wait for the read that was just issued. */
+	/* ring address of word nbp / 32 (the new nx2): unit (w / 4) % 4 at ENTB_RING_ROW strides, word w % 4 inside it;
+	   both fields come from bits 5..8 of nbp */
+	const uint32_t m = nbp & 0x1e0u;
+	const uint32_t ra = ring_lane + (((m >> 3) | (m << ENTB_RING_UNIT_SHIFT)) & (0xcu | (3u * ENTB_RING_ROW)));
 	asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %3, 0;\n\t@p mov.u32 %0, %1;\n\t@p mov.u32 %1, %2;\n\t"
 					 "@p ld.shared.u32 %2, [%4];\n\t}"
 					 : "+r"(br.cur), "+r"(br.nxt), "+r"(br.nx2)
-					 : "r"((nbp ^ br.bp) & 32u), "r"(ebr_ring_addr(ring_lane, (nbp >> 5) + 2u)));
+					 : "r"((nbp ^ br.bp) & 32u), "r"(ra));
 	br.bp = nbp;
 	return true;
 }
@@ -496,7 +503,7 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 	const uint32_t ring_lane = (uint32_t)__cvta_generic_to_shared(s_dyn + ENTB_THREADS * ENTB_SLOT_WORDS) + (uint32_t)tid * 16u;
 
 	EBR br;
-	br.bp = 0u;
+	br.bp = 64u;
 	br.fw = 0u;
 	br.nwords = 0u;
 	br.src = reinterpret_cast<const uint32_t *>(uslab);
@@ -561,15 +568,12 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 					/* kp walks the zig-zag table: kp = &zq[k]; the entry of the coefficient is the one before it */
 					uint32_t kp = zq_addr + 4u;
 					const uint32_t kend = zq_addr + 256u;
-					int it = 1;
-					do
+					/* two symbols per ring checkpoint (ENTB_CHECK_EVERY), written out so that no counter is needed */
+					static_assert(ENTB_CHECK_EVERY == 2, "the loop below is unrolled for two symbols per checkpoint");
+					for (;;)
 					{
 						int val;
-						if (++it > ENTB_CHECK_EVERY)
-						{
-							it = 1;
-							ebr_checkpoint<1, true>(ring_lane, br);
-						}
+						ebr_checkpoint<1, true>(ring_lane, br);
 						if (!entb_symbol<ENTB_AC_BITS, false>(ring_lane, br, ac_fast, Lac, val, e, [&] {
 								 sts_u16(slot_addr + ((zqp & 0xffffu) ^ slot_key), (uint32_t)(valp * (int)(zqp >> 16)));
 							 }))
@@ -580,7 +584,22 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 						kp += ENTB_E_KADV(e) << 2;
 						zqp = lds_u32_m4(kp);
 						valp = val;
-					} while (kp < kend);
+						if (kp >= kend)
+							break;
+						if (!entb_symbol<ENTB_AC_BITS, false>(ring_lane, br, ac_fast, Lac, val, e, [&] {
+								 sts_u16(slot_addr + ((zqp & 0xffffu) ^ slot_key), (uint32_t)(valp * (int)(zqp >> 16)));
+							 }))
+						{
+							ok = false;
+							break;
+						}
+						kp += ENTB_E_KADV(e) << 2;
+						zqp = lds_u32_m4(kp);
+						valp = val;
+						if (kp >= kend)
+							break;
+					}
+					if (ok)
 					sts_u16(slot_addr + ((zqp & 0xffffu) ^ slot_key), (uint32_t)(valp * (int)(zqp >> 16)));
 				}
 				failed = !ok;

@@ -15,15 +15,13 @@
  *                       same (MCU, block) position of their own segment, so the per-block control flow is
  *                       warp-uniform; the only divergent loop is the AC symbol loop.
  *
- * With stuffing out of the way the bit reader is stateless: a lane keeps only its bit position `bp`; the
- * next 32 stream bits are funnelshift(ring[bp/32], ring[bp/32 + 1], bp % 32), read from a per-lane ring of
- * 32 words in shared memory ([word][lane] layout: conflict-free) that cp.async tops up at warp-uniform
- * checkpoints (block start and every ENTB_CHECK_EVERY-th AC symbol).  A checkpoint waits only for the
- * copies of the checkpoint before the previous one, so a copy has two intervals to land and the symbol loop
- * never touches global memory.  No underflow is possible: a symbol is at most 16 + 15 bits, an interval at
- * most ENTB_CHECK_EVERY symbols, and the ring runs >= 105 bytes ahead of what three intervals can consume
- * (see ebr_checkpoint).  Past the end of a segment the ring is zero filled, which is what the reference
- * feeds after a marker or the end of the file (jpeg.c:176-184, common.c:39).
+ * With stuffing out of the way the bit reader is stateless: a lane keeps its bit position and the three
+ * stream words around it in registers (next 32 bits = one funnel shift); crossing a word boundary slides the
+ * window and re-reads the third word from a per-lane 64-byte ring in shared memory that 16-byte cp.async
+ * copies top up at warp-uniform checkpoints (every ENTB_CHECK_EVERY symbols).  A checkpoint waits only for
+ * the copies of three checkpoints ago, so the symbol loop never touches global memory, and the ring
+ * provably never underflows (see ebr_checkpoint).  Past the end of a segment the ring is zero filled, which
+ * is what the reference feeds after a marker or the end of the file (jpeg.c:176-184, common.c:39).
  *
  * One AC symbol is a single straight-line path:
  *

@@ -63,6 +63,8 @@ def lib() -> C.CDLL:
     L.stbi_set_flip_vertically_on_load.argtypes = [C.c_int]
     L.stbi_jpeg_inspect.restype = C.c_int
     L.stbi_jpeg_inspect.argtypes = [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_longlong)]
+    L.stbi_jpeg_inspect_scans.restype = C.c_int
+    L.stbi_jpeg_inspect_scans.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_int), C.c_int]
     L.stbi_jpeg_cuda_device_count.restype = C.c_int
     L.stbi_jpeg_batch_create.restype = C.c_void_p
     L.stbi_jpeg_batch_create.argtypes = [C.POINTER(Params)]
@@ -160,6 +162,14 @@ def inspect(data: bytes, req_comp: int = 0) -> Optional[dict]:
     if not lib().stbi_jpeg_inspect(data, len(data), req_comp, info):
         return None
     return dict(zip(_INSPECT_KEYS, list(info)))
+
+
+def inspect_scans(data: bytes) -> List[int]:
+    """Dependency level ("wave") of every scan of the stream (host only); [] if it does not parse."""
+    cap = 256
+    waves = (C.c_int * cap)()
+    n = lib().stbi_jpeg_inspect_scans(data, len(data), waves, cap)
+    return list(waves[:min(n, cap)])
 
 
 class PinnedBuffer:

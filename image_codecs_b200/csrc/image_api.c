@@ -347,7 +347,8 @@ static int batch_parse(stbi_jpeg_batch *b, const stbi_uc *const *bufs, const int
 			ng += (size_t)r->nsegs;
 			memcpy(b->huff + nh, r->huff, sizeof(jcu_huff_spec) * (size_t)r->nhuff);
 			nh += (size_t)r->nhuff;
-			if (r->nscans > waves) waves = r->nscans;
+			for (s = 0; s < r->nscans; ++s)
+				if (r->scans[s].wave + 1 > waves) waves = r->scans[s].wave + 1;
 			if (im->progressive) clear = 1;
 			bits += r->entropy_bytes * 8.0;
 			cbytes += 128.0 * (double)r->coef_blocks;
@@ -863,6 +864,23 @@ API int stbi_is_16_bit_from_memory(stbi_uc const *buffer, int len)
 	(void)buffer;
 	(void)len;
 	return 0;
+}
+
+API int stbi_jpeg_inspect_scans(stbi_uc const *buffer, int len, int *waves, int cap)
+{
+	jp_result r;
+	size_t n = len > 0 ? (size_t)len : 0;
+	int i, ns = 0;
+	if (jp_parse(buffer, n, 0, JP_MODE_LOAD, &r))
+	{
+		ns = r.nscans;
+		for (i = 0; i < ns && i < cap; ++i)
+			waves[i] = r.scans[i].wave;
+	}
+	else
+		err_zero(r.reason);
+	jp_result_free(&r);
+	return ns;
 }
 
 API int stbi_jpeg_inspect(stbi_uc const *buffer, int len, int req_comp, long long info[16])

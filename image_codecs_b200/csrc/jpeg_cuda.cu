@@ -50,6 +50,7 @@ struct jcu_ctx
 	std::vector<int> wave_off; /* n_waves + 1 offsets into work_h */
 	std::vector<int> wave_nbase; /* per wave: leading work items that are baseline scans */
 	std::vector<char> wave_two;	  /* per wave: every baseline scan uses <= 2 distinct DC and <= 2 distinct AC tables */
+	std::vector<int> wave_nsmall;	  /* per wave: work items after the baseline ones that are progressive scans of <= 32 segments */
 	std::vector<int32_t> list_h; /* image lists per path, concatenated */
 	int list_off[4] = {0, 0, 0, 0}, list_n[4] = {0, 0, 0, 0};
 	int tiles[4] = {0, 0, 0, 0};
@@ -284,15 +285,21 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 	c->wave_off.assign((size_t)b->n_waves + 1, 0);
 	c->wave_nbase.assign((size_t)b->n_waves, 0);
 	c->wave_two.assign((size_t)b->n_waves, 1);
+	c->wave_nsmall.assign((size_t)b->n_waves, 0);
 	for (int w = 0; w < b->n_waves; ++w)
 	{
 		c->wave_off[w] = (int)c->work_h.size();
-		for (int pass = 0; pass < 2; ++pass) /* baseline scans first (k_entropy_baseline), then the rest */
+		/* three groups per wave, one launch each: baseline scans (k_entropy_baseline), progressive scans of at
+		   most ENT_SMALL_THREADS segments (32-thread CTAs), the other progressive scans */
+		for (int pass = 0; pass < 3; ++pass)
 		{
 			for (int s = 0; s < b->n_scans; ++s)
 			{
 				const jcu_scan &sc = b->scans[s];
-				if (sc.wave != w || !imgs[sc.image].ok || is_ss[s] || (sc.kind == JCU_SCAN_BASELINE) != (pass == 0))
+				if (sc.wave != w || !imgs[sc.image].ok || is_ss[s])
+					continue;
+				const int group = sc.kind == JCU_SCAN_BASELINE ? 0 : sc.nseg <= ENT_SMALL_THREADS ? 1 : 2;
+				if (group != pass)
 					continue;
 				if (pass == 0)
 				{
@@ -311,7 +318,7 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 					if (nd > 2 || na > 2)
 						c->wave_two[w] = 0;
 				}
-				const uint32_t per_cta = pass == 0 ? ENTB_THREADS : ENT_THREADS;
+				const uint32_t per_cta = pass == 0 ? ENTB_THREADS : pass == 1 ? ENT_SMALL_THREADS : ENT_THREADS;
 				for (uint32_t f = 0; f < sc.nseg; f += per_cta)
 				{
 					EntWork wk;
@@ -323,6 +330,8 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 			}
 			if (pass == 0)
 				c->wave_nbase[w] = (int)c->work_h.size() - c->wave_off[w];
+			if (pass == 1)
+				c->wave_nsmall[w] = (int)c->work_h.size() - c->wave_off[w] - c->wave_nbase[w];
 		}
 	}
 	c->wave_off[b->n_waves] = (int)c->work_h.size();
@@ -421,11 +430,19 @@ extern "C" int jcu_run(jcu_ctx *c)
 					(const uint8_t *)c->uslab.p, (const uint32_t *)c->useg_len.p, (int16_t *)c->coef.p, (int32_t *)c->err.p);
 			c->launches++;
 		}
-		if (n - nb > 0)
+		const int nsm = c->wave_nsmall[w];
+		if (nsm > 0)
 		{
-			k_entropy_segments<<<n - nb, ENT_THREADS, 0, st>>>(wk + nb, (const jcu_scan *)c->scans.p, d_img,
-																				(const uint32_t *)c->segs.p, (const jcu_huff_spec *)c->huff.p,
-																				(const uint8_t *)c->bits.p, (int16_t *)c->coef.p, (int32_t *)c->err.p);
+			k_entropy_segments<ENT_SMALL_THREADS><<<nsm, ENT_SMALL_THREADS, 0, st>>>(
+				wk + nb, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p, (const jcu_huff_spec *)c->huff.p,
+				(const uint8_t *)c->bits.p, (int16_t *)c->coef.p, (int32_t *)c->err.p);
+			c->launches++;
+		}
+		if (n - nb - nsm > 0)
+		{
+			k_entropy_segments<ENT_THREADS><<<n - nb - nsm, ENT_THREADS, 0, st>>>(
+				wk + nb + nsm, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p, (const jcu_huff_spec *)c->huff.p,
+				(const uint8_t *)c->bits.p, (int16_t *)c->coef.p, (int32_t *)c->err.p);
 			c->launches++;
 		}
 	}

@@ -35,6 +35,7 @@
 #include "jpeg_coef_layout.cuh"
 
 #define ENT_THREADS 128
+#define ENT_SMALL_THREADS 32 /* CTA size for scans of few segments (no restart markers: one) */
 #define ENT_LUT_BITS 9
 #define ENT_SLOT_WORDS 36 /* 64 int16 = 32 words, +4 pad words: 16B chunks of the 8 lanes of a phase hit distinct banks */
 
@@ -260,10 +261,9 @@ __device__ __forceinline__ int receive_extend(BitReader &br, int n)
 
 struct ScanShared
 {
-	HuffLut lut[8];	/* [0..3] DC per scan-component slot, [4..7] AC */
+	HuffLut lut[4];	/* per scan-component slot: a progressive scan uses DC tables or AC tables, never both */
 	int lut_of_dc[4]; /* slot -> lut index (slots sharing a spec share a table) */
 	int lut_of_ac[4];
-	uint16_t q[4][64]; /* quant table per scan-component slot, natural order (baseline) */
 	uint8_t zz[80];
 };
 
@@ -383,105 +383,22 @@ __device__ __forceinline__ int prog_ac_refine(BitReader &br, const HuffLut *L, c
 	return 1;
 }
 
-/* baseline block into a zeroed shared-memory slot: natural order, dequantised, truncated to
-   16 bits like the reference's (short) casts (jpeg.c:325,345,365) */
-__device__ __forceinline__ int baseline_block(BitReader &br, const HuffLut *Ldc, const HuffLut *Lac,
-															 const uint16_t *__restrict__ q, const uint8_t *__restrict__ zz, int16_t *slot,
-															 int &dc_pred)
-{
-	/* DC */
-	{
-		if (br.nbits <= 32)
-			br_refill(br);
-		const uint32_t e = Ldc->fast[br_peek(br, ENT_LUT_BITS)];
-		int diff;
-		if ((e & 31u) == 0)
-		{
-			int t = huff_decode_long(br, Ldc);
-			if (t < 0)
-				return 0;
-			diff = receive_extend(br, t > 15 ? 0 : t);
-		}
-		else
-		{
-			br_skip(br, (int)(e & 31u));
-			if (e & LUT_RESOLVED)
-				diff = (int)e >> 16;
-			else
-			{
-				const int s = (int)((e >> 9) & 15u);
-				diff = 0;
-				if (s)
-				{
-					diff = (int)br_peek(br, s);
-					br_skip(br, s);
-					if (diff < (1 << (s - 1)))
-						diff += (int)(0xffffffffu << s) + 1;
-				}
-			}
-		}
-		dc_pred += diff;
-		slot[0] = (int16_t)(dc_pred * (int)q[0]);
-	}
-	/* AC */
-	int k = 1;
-	do
-	{
-		if (br.nbits <= 32)
-			br_refill(br); /* > 32 bits: a 16-bit code plus 15 magnitude bits never needs a second refill */
-		uint32_t e = Lac->fast[br_peek(br, ENT_LUT_BITS)];
-		int r, s, val;
-		if ((e & 31u) == 0)
-		{
-			int rs = huff_decode_long(br, Lac);
-			if (rs < 0)
-				return 0;
-			r = rs >> 4;
-			s = rs & 15;
-			e = 0;
-		}
-		else
-		{
-			br_skip(br, (int)(e & 31u));
-			r = (int)((e >> 5) & 15u);
-			s = (int)((e >> 9) & 15u);
-		}
-		if (e & LUT_RESOLVED)
-			val = (int)e >> 16;
-		else
-		{
-			if (s == 0)
-			{
-				if (r != 15)
-					break; /* EOB */
-				k += 16;	 /* ZRL */
-				continue;
-			}
-			val = (int)br_peek(br, s);
-			br_skip(br, s);
-			if (val < (1 << (s - 1)))
-				val += (int)(0xffffffffu << s) + 1;
-		}
-		k += r;
-		const int zig = zz[k];
-		++k;
-		slot[zig] = (int16_t)(val * (int)q[zig]);
-	} while (k < 64);
-	return 1;
-}
-
 /*
- * Entropy-decode kernel: grid = CTA work items of one wave (one scan ordinal across the batch).
- * Thread t of a CTA decodes restart segment (work.seg_first + t) of the CTA's scan.
+ * Progressive entropy decode (the three decoders of jpeg.c:372-558), in place on the coefficient slab:
+ * grid = CTA work items of one wave (scans of one dependency level across the batch).  Thread t of a CTA
+ * decodes restart segment (work.seg_first + t) of the CTA's scan.  T = segments per CTA: scans without
+ * restart markers are one segment each, so they get 32-thread CTAs (a decoder is a serial, latency-bound
+ * thread: what counts is how many scans are resident, and a CTA slot per scan is the limit).
+ * Baseline scans never come here (jpeg_entropy_baseline.cuh, jpeg_selfsync.cuh).
  */
-__global__ void __launch_bounds__(ENT_THREADS)
+template <int T>
+__global__ void __launch_bounds__(T)
 k_entropy_segments(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 						 const jcu_image *__restrict__ images, const uint32_t *__restrict__ seg_start,
 						 const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ bitstream,
 						 int16_t *__restrict__ coef, int32_t *__restrict__ img_err)
 {
 	__shared__ ScanShared sh;
-	__shared__ __align__(16) uint32_t s_slots[ENT_THREADS * ENT_SLOT_WORDS];
 
 	const int tid = threadIdx.x;
 	const EntWork w = work[blockIdx.x];
@@ -490,10 +407,8 @@ k_entropy_segments(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 	const int kind = sc->kind, ncs = sc->ncomp;
 
 	/* ---- lookup tables, once per CTA ---- */
-	if (tid < 80)
-		sh.zz[tid] = c_natural[tid];
-	for (int i = tid; i < ncs * 64; i += ENT_THREADS)
-		sh.q[i >> 6][i & 63] = im->qt[sc->comp[i >> 6]][i & 63];
+	for (int i = tid; i < 80; i += T)
+		sh.zz[i] = c_natural[i];
 	for (int i = 0; i < ncs; ++i)
 	{
 		if (sc->dc_spec[i] >= 0)
@@ -504,7 +419,7 @@ k_entropy_segments(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 					alias = sh.lut_of_dc[j];
 			if (alias < 0)
 			{
-				hufflut_build(&sh.lut[i], &huff[sc->dc_spec[i]], true, tid, ENT_THREADS);
+				hufflut_build(&sh.lut[i], &huff[sc->dc_spec[i]], true, tid, T);
 				alias = i;
 			}
 			if (tid == 0)
@@ -518,8 +433,8 @@ k_entropy_segments(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 					alias = sh.lut_of_ac[j];
 			if (alias < 0)
 			{
-				hufflut_build(&sh.lut[4 + i], &huff[sc->ac_spec[i]], false, tid, ENT_THREADS);
-				alias = 4 + i;
+				hufflut_build(&sh.lut[i], &huff[sc->ac_spec[i]], false, tid, T);
+				alias = i;
 			}
 			if (tid == 0)
 				sh.lut_of_ac[i] = alias;
@@ -545,15 +460,6 @@ k_entropy_segments(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 	int eob_run = 0;
 	bool failed = false;
 
-	uint32_t *slot_w = &s_slots[tid * ENT_SLOT_WORDS];
-	int16_t *slot = reinterpret_cast<int16_t *>(slot_w);
-	if (kind == JCU_SCAN_BASELINE)
-	{
-#pragma unroll
-		for (int i = 0; i < 32; ++i)
-			slot_w[i] = 0u;
-	}
-
 	const int ss = sc->ss, se = sc->se, al = sc->al;
 
 	for (int uu = 0; uu < n_units; ++uu)
@@ -566,39 +472,15 @@ k_entropy_segments(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 		{
 			const jcu_comp *cp = &im->comp[sc->comp[i]];
 			const int bh_n = ncs == 1 ? 1 : cp->v, bw_n = ncs == 1 ? 1 : cp->h;
-			const HuffLut *Ldc = &sh.lut[sh.lut_of_dc[i] & 7];
-			const HuffLut *Lac = &sh.lut[sh.lut_of_ac[i] & 7];
+			const HuffLut *Ldc = &sh.lut[sh.lut_of_dc[i] & 3];
+			const HuffLut *Lac = &sh.lut[sh.lut_of_ac[i] & 3];
 			int dcp = dc_pred[i];
 			for (int y = 0; y < bh_n; ++y)
 				for (int x = 0; x < bw_n; ++x)
 				{
 					const int bx = ux * bw_n + x, by = uy * bh_n + y;
 					int16_t *blk = coef + cp->coef_off + ((size_t)by * cp->bw + bx) * 64;
-					if (kind == JCU_SCAN_BASELINE)
-					{
-						bool ok = false;
-						if (live && !failed)
-						{
-							ok = baseline_block(br, Ldc, Lac, sh.q[i], sh.zz, slot, dcp) != 0;
-							if (!ok)
-								failed = true;
-						}
-						__syncwarp();
-						if (live)
-						{
-							const uint4 *s4 = reinterpret_cast<const uint4 *>(slot_w);
-							uint4 *d4 = reinterpret_cast<uint4 *>(blk);
-#pragma unroll
-							for (int q = 0; q < 8; ++q)
-							{
-								uint4 v = s4[q];
-								if (ok)
-									d4[q ^ coef_key(blk)] = v;
-								reinterpret_cast<uint4 *>(slot_w)[q] = make_uint4(0u, 0u, 0u, 0u);
-							}
-						}
-					}
-					else if (live && !failed)
+					if (live && !failed)
 					{
 						int ok = 1;
 						if (kind == JCU_SCAN_PROG_DC_FIRST)

@@ -39,6 +39,9 @@
 #include "jpeg_coef_layout.cuh"
 #include "jpeg_output.cuh"
 
+#ifndef S420_MIN_CTAS
+#define S420_MIN_CTAS (512 / S420_THREADS) /* resident CTAs per SM asked of the register allocator (5 and 6 measured: +1 %) */
+#endif
 #ifndef S420_THREADS
 #define S420_THREADS 128
 #endif
@@ -196,7 +199,7 @@ __device__ __forceinline__ void s420_colour(uint32_t c16, uint32_t yw, int &r, i
  * otherwise the entropy stage already stored (short)(c*q) as the reference does for baseline.
  */
 template <int N, bool DEQ>
-__global__ void __launch_bounds__(S420_THREADS, 512 / S420_THREADS)
+__global__ void __launch_bounds__(S420_THREADS, S420_MIN_CTAS)
 k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__ images, const int16_t *__restrict__ coef,
 					  uint8_t *__restrict__ out, int rows_per_band)
 {

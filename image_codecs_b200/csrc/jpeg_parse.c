@@ -516,7 +516,28 @@ static int one_scan(parser *p)
 		sc.units_per_row = im->mcu_x;
 		sc.total_units = im->mcu_x * im->mcu_y;
 	}
-	sc.wave = r->nscans;
+	/* Wave = dependency level: a scan must follow every earlier scan of the image that touches one of its
+	   components in an overlapping coefficient band (the reference runs scans strictly in file order,
+	   jpeg.c:1716; scans on disjoint data commute).  Baseline and first DC scans own the whole block (the
+	   latter clears it, jpeg.c:380). */
+	{
+		const int lo = (sc.kind == JCU_SCAN_BASELINE || sc.kind == JCU_SCAN_PROG_DC_FIRST) ? 0 : sc.ss;
+		const int hi = (sc.kind == JCU_SCAN_BASELINE || sc.kind == JCU_SCAN_PROG_DC_FIRST) ? 63 : sc.se;
+		int j, a, b, level = 0;
+		for (j = 0; j < r->nscans; ++j)
+		{
+			const jcu_scan *o = &r->scans[j];
+			const int olo = (o->kind == JCU_SCAN_BASELINE || o->kind == JCU_SCAN_PROG_DC_FIRST) ? 0 : o->ss;
+			const int ohi = (o->kind == JCU_SCAN_BASELINE || o->kind == JCU_SCAN_PROG_DC_FIRST) ? 63 : o->se;
+			int shared = 0;
+			for (a = 0; a < sc.ncomp; ++a)
+				for (b = 0; b < o->ncomp; ++b)
+					shared |= sc.comp[a] == o->comp[b];
+			if (shared && lo <= ohi && olo <= hi && o->wave + 1 > level)
+				level = o->wave + 1;
+		}
+		sc.wave = level;
+	}
 	/* baseline dequantises at decode time with the table in force at this scan (jpeg.c:1176) */
 	if (!p->progressive)
 		for (i = 0; i < sc.ncomp; ++i)

@@ -167,6 +167,14 @@ STBIDEF int stbi_jpeg_batch_timings_get(stbi_jpeg_batch *b, stbi_jpeg_batch_timi
  */
 STBIDEF int stbi_jpeg_inspect(stbi_uc const *buffer, int len, int req_comp, long long info[16]);
 
+/*
+ * Host-only: the decode schedule of one stream.  Fills waves[i] (i < cap) with the dependency level of scan
+ * i -- scans of one level touch disjoint (component, coefficient band) sets and are entropy decoded by the
+ * same launch; the reference runs them one after the other in file order (jpeg.c:1716).  Returns the number
+ * of scans, 0 if the stream does not parse.
+ */
+STBIDEF int stbi_jpeg_inspect_scans(stbi_uc const *buffer, int len, int *waves, int cap);
+
 /* number of CUDA devices visible (0 when there is none); never falls back to a CPU decode */
 STBIDEF int stbi_jpeg_cuda_device_count(void);
 

@@ -19,6 +19,7 @@
 #include "jpeg_output.cuh"
 #include "jpeg_fused.cuh"
 #include "jpeg_fused420.cuh"
+#include "jpeg_fused1x1.cuh"
 
 struct DevBuf
 {
@@ -227,6 +228,12 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 			{
 				im.tiles_x = (im.mcu_x + S420_MS - 1) / S420_MS;						/* strips */
 				im.tiles_y = (im.mcu_y + c->rows_per_band - 1) / c->rows_per_band; /* bands */
+			}
+			else
+			{
+				const int bs = p == JCU_PATH_FUSED_444 ? F1_BS(3) : F1_BS(1);
+				im.tiles_x = (im.comp[0].bw + bs - 1) / bs;											 /* strips */
+				im.tiles_y = ((im.height + 7) / 8 + F1_ROWS_PER_BAND - 1) / F1_ROWS_PER_BAND; /* bands */
 			}
 			im.tile_first = c->tiles[p];
 			c->tiles[p] += im.tiles_x * im.tiles_y;
@@ -505,8 +512,11 @@ extern "C" int jcu_run(jcu_ctx *c)
 			cudaError_t e = p == JCU_PATH_FUSED_420
 									  ? fused420_launch(c->path_maxtiles[p], lst, c->list_n[p], d_img, d_coef, (uint8_t *)c->out.p, st,
 															  c->path_n[p], c->path_deq[p], c->rows_per_band)
-									  : fused_launch(p, c->path_maxtiles[p], lst, c->list_n[p], d_img, d_coef, (uint8_t *)c->out.p, st,
-														  c->path_n[p], c->path_deq[p]);
+								  : p == JCU_PATH_FUSED_444
+									  ? fused1x1_launch<3>(c->path_maxtiles[p], lst, c->list_n[p], d_img, d_coef, (uint8_t *)c->out.p, st,
+																  c->path_n[p], c->path_deq[p])
+									  : fused1x1_launch<1>(c->path_maxtiles[p], lst, c->list_n[p], d_img, d_coef, (uint8_t *)c->out.p, st,
+																  c->path_n[p], c->path_deq[p]);
 			if (e != cudaSuccess)
 				return set_err(c, e, "fused_launch");
 			c->launches++;

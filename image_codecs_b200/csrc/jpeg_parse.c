@@ -582,8 +582,8 @@ static void choose_output(parser *p, int req_comp)
 	im->color_mode = mode;
 
 	im->path = JCU_PATH_GENERIC;
-	if (mode == JCU_CM_Y)
-		im->path = JCU_PATH_FUSED_GRAY;
+	if (mode == JCU_CM_Y && im->comp[0].h == im->hmax && im->comp[0].v == im->vmax)
+		im->path = JCU_PATH_FUSED_GRAY; /* component 0 is at full resolution: resample_row_1 (jpeg.c:2270) */
 	else if (mode == JCU_CM_YCBCR && im->ncomp == 3)
 	{
 		const jcu_comp *c = im->comp;

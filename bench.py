@@ -314,6 +314,7 @@ def main():
             cpu = {"value": None, "unit": UNIT, "cores": ncores, "kind": "unavailable", "sample": str(e)}
 
     if rank == 0:
+        deq = "true" if args.progressive else "false"
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
@@ -325,8 +326,9 @@ def main():
             "clocks": clocks,
             "e2e": e2e,
             "gpu_launches": launches,
-            "roofline": {"bound": "hbm", "kernel": "k_fused420_strip<3,false>" if args.subsampling == "420" and not args.gray
-                         else "k_fused_444/gray", "achieved": achieved, "peak": peak,
+            "roofline": {"bound": "hbm", "kernel": ("k_fused1x1_strip<3,1,%s>" % deq) if args.gray
+                         else ("k_fused420_strip<3,%s>" % deq) if args.subsampling == "420"
+                         else ("k_fused1x1_strip<3,3,%s>" % deq) if args.subsampling == "444" else "k_generic_idct + k_generic_color", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak if peak else None, "traffic": traffic,
                          "traffic_source": "ncu dram__bytes_read+write per image (profiles/traffic_fused420.json) x images",
                          "peak_source": peak_src, "algorithmic_bytes_per_launch": algo_bytes,

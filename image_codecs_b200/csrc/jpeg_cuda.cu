@@ -17,7 +17,6 @@
 #include "jpeg_entropy_baseline.cuh"
 #include "jpeg_selfsync.cuh"
 #include "jpeg_output.cuh"
-#include "jpeg_fused.cuh"
 #include "jpeg_fused420.cuh"
 #include "jpeg_fused1x1.cuh"
 
@@ -220,10 +219,6 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 		}
 		else
 		{
-			int tw, th;
-			fused_tile_dims(p, &tw, &th);
-			im.tiles_x = (im.width + tw - 1) / tw;
-			im.tiles_y = (im.height + th - 1) / th;
 			if (p == JCU_PATH_FUSED_420)
 			{
 				im.tiles_x = (im.mcu_x + S420_MS - 1) / S420_MS;						/* strips */

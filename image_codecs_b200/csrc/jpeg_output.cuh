@@ -10,8 +10,8 @@
  * The generic C kernels are canonical, not the SSE2/NEON variants.
  *
  * This header holds the shared device arithmetic and the GENERIC two-pass path (any H,V in
- * 1..4, any colour mode).  The fused single-pass tile kernels for the headline formats are in
- * jpeg_fused.cuh and use the same arithmetic.
+ * 1..4, any colour mode).  The fused single-pass strip kernels for the headline formats are in
+ * jpeg_fused420.cuh (4:2:0) and jpeg_fused1x1.cuh (4:4:4, single component) and use the same arithmetic.
  */
 #pragma once
 #include <cuda_runtime.h>

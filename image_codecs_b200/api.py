@@ -89,6 +89,8 @@ def lib() -> C.CDLL:
     L.stbi_jpeg_batch_status.argtypes = [C.c_void_p, C.c_int]
     L.stbi_jpeg_batch_reason.restype = C.c_char_p
     L.stbi_jpeg_batch_reason.argtypes = [C.c_void_p, C.c_int]
+    L.stbi_jpeg_batch_debug_guards.restype = C.c_int
+    L.stbi_jpeg_batch_debug_guards.argtypes = [C.c_void_p]
     L.stbi_jpeg_batch_timings_get.restype = C.c_int
     L.stbi_jpeg_batch_timings_get.argtypes = [C.c_void_p, C.POINTER(Timings)]
     # thin CUDA ABI (stage-level tests, pinned memory)
@@ -282,6 +284,10 @@ class BatchDecoder:
         nb = C.c_size_t(0)
         p = lib().stbi_jpeg_batch_device_pixels(self._h, i, C.byref(nb))
         return (p or 0), nb.value
+
+    def guards_ok(self) -> int:
+        """Test hook (IMAGE_CODECS_B200_GUARD=1): 1 = no kernel wrote past the end of a device buffer, 0 = one did."""
+        return lib().stbi_jpeg_batch_debug_guards(self._h)
 
     def timings(self) -> dict:
         t = Timings()

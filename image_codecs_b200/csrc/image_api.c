@@ -556,6 +556,17 @@ API int stbi_jpeg_batch_fetch_all(stbi_jpeg_batch *b, stbi_uc *const *outs, cons
 	return n;
 }
 
+API int stbi_jpeg_batch_debug_guards(stbi_jpeg_batch *b)
+{
+	int r;
+	if (!b)
+		return -1;
+	r = jcu_debug_guards_ok(b->ctx);
+	if (r == 1 && b->pipe)
+		r = jcu_debug_guards_ok(b->pipe->ctx);
+	return r;
+}
+
 API int stbi_jpeg_batch_timings_get(stbi_jpeg_batch *b, stbi_jpeg_batch_timings *t)
 {
 	if (!b || !t)

@@ -24,7 +24,12 @@ struct DevBuf
 {
 	void *p = nullptr;
 	size_t cap = 0;
+	size_t guard_at = 0; /* guard mode: offset of the JCU_GUARD_BYTES canary behind the logical size */
 };
+#define JCU_GUARD_BYTES 4096
+/* IMAGE_CODECS_B200_GUARD=1 (test hook; compute-sanitizer is not available on every box): every device buffer
+   is allocated at exactly the size asked for plus a canary that jcu_debug_guards_ok() verifies */
+static bool g_guard_mode = false;
 
 struct jcu_ctx
 {
@@ -81,6 +86,20 @@ static int set_err(jcu_ctx *c, cudaError_t e, const char *where)
 
 static cudaError_t ensure(DevBuf &b, size_t bytes)
 {
+	if (g_guard_mode)
+	{
+		if (b.p)
+			cudaFree(b.p);
+		b.p = nullptr;
+		b.cap = 0;
+		const size_t at = (bytes + 15) & ~(size_t)15;
+		cudaError_t e = cudaMalloc(&b.p, at + JCU_GUARD_BYTES);
+		if (e != cudaSuccess)
+			return e;
+		b.cap = bytes;
+		b.guard_at = at;
+		return cudaMemset((char *)b.p + at, 0xA5, JCU_GUARD_BYTES);
+	}
 	if (bytes <= b.cap)
 		return cudaSuccess;
 	if (b.p)
@@ -115,6 +134,8 @@ extern "C" int jcu_ctx_create(int device, int profile, int entropy_mode, jcu_ctx
 	c->device = device;
 	c->profile = profile;
 	c->entropy_mode = entropy_mode;
+	const char *gm = getenv("IMAGE_CODECS_B200_GUARD");
+	g_guard_mode = gm && gm[0] == '1';
 	const char *fg = getenv("IMAGE_CODECS_B200_FORCE_GENERIC");
 	c->force_generic = fg && fg[0] == '1';
 	e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
@@ -150,6 +171,35 @@ extern "C" void jcu_ctx_destroy(jcu_ctx *c)
 			cudaEventDestroy(ev);
 	cudaStreamDestroy(c->stream);
 	delete c;
+}
+
+extern "C" int jcu_debug_guards_ok(jcu_ctx *c)
+{
+	if (!c || !g_guard_mode)
+		return -1;
+	cudaSetDevice(c->device);
+	if (cudaStreamSynchronize(c->stream) != cudaSuccess)
+		return 0;
+	DevBuf *bufs[] = {&c->bits, &c->images, &c->scans, &c->segs, &c->huff, &c->work, &c->coef, &c->planes, &c->out, &c->err, &c->lists,
+							&c->ss_work, &c->ss_scans, &c->ss_exit_a, &c->ss_exit_b, &c->ss_entry, &c->ss_nblk, &c->ss_first, &c->ss_changed,
+							&c->uslab, &c->useg_len};
+	std::vector<unsigned char> h(JCU_GUARD_BYTES);
+	int which = 0;
+	for (auto b : bufs)
+	{
+		++which;
+		if (!b->p)
+			continue;
+		if (cudaMemcpy(h.data(), (char *)b->p + b->guard_at, JCU_GUARD_BYTES, cudaMemcpyDeviceToHost) != cudaSuccess)
+			return 0;
+		for (size_t i = 0; i < JCU_GUARD_BYTES; ++i)
+			if (h[i] != 0xA5)
+			{
+				snprintf(c->errstr, sizeof(c->errstr), "guard of device buffer #%d overwritten at +%zu", which, i);
+				return 0;
+			}
+	}
+	return 1;
 }
 
 extern "C" const char *jcu_error_string(jcu_ctx *c) { return c ? c->errstr : "no context"; }

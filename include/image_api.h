@@ -157,6 +157,9 @@ STBIDEF void *stbi_jpeg_batch_device_pixels(stbi_jpeg_batch *b, int image, size_
 STBIDEF int stbi_jpeg_batch_status(stbi_jpeg_batch *b, int image);
 STBIDEF const char *stbi_jpeg_batch_reason(stbi_jpeg_batch *b, int image);
 STBIDEF int stbi_jpeg_batch_timings_get(stbi_jpeg_batch *b, stbi_jpeg_batch_timings *t);
+/* test hook: with IMAGE_CODECS_B200_GUARD=1 set before stbi_jpeg_batch_create, every device buffer carries a
+   canary behind its logical size; 1 = all intact, 0 = one was overwritten, -1 = guard mode off */
+STBIDEF int stbi_jpeg_batch_debug_guards(stbi_jpeg_batch *b);
 
 /*
  * Host-only full marker parse of one stream (no GPU): what the batch loader would hand to the

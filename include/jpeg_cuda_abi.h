@@ -166,6 +166,10 @@ JCU_API int jcu_get_timings(jcu_ctx *c, jcu_timings *t);
 
 /* stage-level entry points for the parity tests (host pointers in, host pointers out) */
 JCU_API int jcu_test_idct_blocks(jcu_ctx *c, const int16_t *coef, const uint16_t *qt, int nblocks, uint8_t *out64);
+/* test hook: with IMAGE_CODECS_B200_GUARD=1 in the environment every device buffer carries a 4 KB canary behind
+   its logical size; returns 1 if all canaries are intact, 0 if one was overwritten (jcu_error_string says
+   which), -1 if guard mode is off */
+JCU_API int jcu_debug_guards_ok(jcu_ctx *c);
 JCU_API int jcu_test_ycbcr(jcu_ctx *c, const uint8_t *y, const uint8_t *cb, const uint8_t *cr, int n, int step, uint8_t *out);
 JCU_API int jcu_read_coefs(jcu_ctx *c, size_t elem_off, size_t elems, int16_t *dst); /* coefficient slab after run */
 

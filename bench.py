@@ -253,9 +253,10 @@ def main():
     algo_bytes = tm["coef_bytes"] + tm["out_bytes"]
     traffic = None
     try:  # dram__bytes_read+write of one ncu --set full capture (profiles/), scaled per image to this launch
-        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic_fused420.json")))
-        if args.subsampling == "420" and not args.gray and (args.width, args.height) == (1920, 1080):
-            traffic = tj["dram_bytes_per_image"] * args.images
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        fmt = "gray" if args.gray else args.subsampling
+        if fmt in tj and not args.progressive and (args.width, args.height) == (1920, 1080):
+            traffic = tj[fmt]["dram_bytes_per_image"] * args.images
     except Exception:
         pass
     idct_step_ms = idct_ms / args.steps
@@ -330,7 +331,7 @@ def main():
                          else ("k_fused420_strip<3,%s>" % deq) if args.subsampling == "420"
                          else ("k_fused1x1_strip<3,3,%s>" % deq) if args.subsampling == "444" else "k_generic_idct + k_generic_color", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak if peak else None, "traffic": traffic,
-                         "traffic_source": "ncu dram__bytes_read+write per image (profiles/traffic_fused420.json) x images",
+                         "traffic_source": "ncu dram__bytes_read+write per image (profiles/traffic.json) x images",
                          "peak_source": peak_src, "algorithmic_bytes_per_launch": algo_bytes,
                          "ms_per_launch": idct_step_ms},
             "cpu_baseline": cpu,

@@ -288,7 +288,9 @@ def main():
             outs[i] = pin_out.ptr + i * per
             caps[i] = per
         st = (C.c_int * n_e)()
-        e_dec = ic.BatchDecoder(device=local_rank, profile=False, chunk_images=int(os.environ.get("BENCH_CHUNK", "0")),
+        # chunk size of the library's host pipeline (a public tuning parameter): about 3 GB of pixels per chunk
+        e2e_chunk = int(min(1024, max(64, 2 ** round(np.log2(3.2e9 / (args.width * args.height * 3))))))
+        e_dec = ic.BatchDecoder(device=local_rank, profile=False, chunk_images=int(os.environ.get("BENCH_CHUNK", "0")) or e2e_chunk,
                                 host_threads=max(2, ncores // world))  # ranks share the host cores
         e_dec.decode_into(bufs, lens, n_e, 3, outs, caps, None, None, None, st)  # warm-up (allocations)
         barrier()

@@ -84,7 +84,8 @@ struct stbi_jpeg_batch
 
 	stbi_jpeg_batch_timings tm;
 
-	struct stbi_jpeg_batch *pipe; /* second object (own stream, staging and device buffers) so that the host-buffer
+#define STBI_JPEG_PIPE_MAX 4
+	struct stbi_jpeg_batch *pipe[STBI_JPEG_PIPE_MAX - 1]; /* further objects (own stream, staging and device buffers) so that the host-buffer
 												call can parse / upload chunk k+1 while chunk k computes and downloads */
 };
 
@@ -136,8 +137,12 @@ API void stbi_jpeg_batch_destroy(stbi_jpeg_batch *b)
 {
 	if (!b)
 		return;
-	if (b->pipe)
-		stbi_jpeg_batch_destroy(b->pipe);
+	{
+		int pi;
+		for (pi = 0; pi < STBI_JPEG_PIPE_MAX - 1; ++pi)
+			if (b->pipe[pi])
+				stbi_jpeg_batch_destroy(b->pipe[pi]);
+	}
 	batch_release_results(b);
 	jcu_ctx_destroy(b->ctx);
 	jcu_host_free(b->slab);
@@ -521,6 +526,44 @@ static void flip_rows(stbi_uc *px, int w, int h, int n)
 	free(tmp);
 }
 
+/* enqueue the downloads of images [0, n) of the batch into outs[0..n): neighbours that are contiguous both in
+   the device pixel slab and in host memory travel as one copy (up to 64 MB), which takes the per-copy launch
+   gaps off the PCIe link (one 6 MB copy per 1080p image otherwise) */
+static void batch_enqueue_fetch_all(stbi_jpeg_batch *b, int n, stbi_uc *const *outs, const size_t *out_caps)
+{
+	size_t run_src = 0, run_bytes = 0;
+	stbi_uc *run_dst = NULL;
+	int i;
+	const char *mg = getenv("IMAGE_CODECS_B200_DL_MERGE"); /* tuning hook */
+	const int merge = !(mg && mg[0] == '0');
+	for (i = 0; i < n; ++i)
+	{
+		const jcu_image *im = &b->images[i];
+		const size_t bytes = (size_t)im->n_out * (size_t)im->width * (size_t)im->height;
+		if (!b->res[i].ok)
+			continue;
+		if (bytes > out_caps[i])
+		{
+			b->res[i].ok = 0;
+			b->res[i].reason = "output too small";
+			continue;
+		}
+		if (merge && run_bytes && im->out_off == run_src + run_bytes && outs[i] == run_dst + run_bytes &&
+			 run_bytes < ((size_t)64 << 20))
+		{
+			run_bytes += bytes;
+			continue;
+		}
+		if (run_bytes)
+			jcu_download(b->ctx, run_src, run_bytes, run_dst);
+		run_src = im->out_off;
+		run_dst = outs[i];
+		run_bytes = bytes;
+	}
+	if (run_bytes)
+		jcu_download(b->ctx, run_src, run_bytes, run_dst);
+}
+
 API int stbi_jpeg_batch_fetch(stbi_jpeg_batch *b, int image, stbi_uc *out, size_t out_cap)
 {
 	if (!b || image < 0 || image >= b->count)
@@ -541,9 +584,7 @@ API int stbi_jpeg_batch_fetch_all(stbi_jpeg_batch *b, stbi_uc *const *outs, cons
 	int i, n = 0;
 	if (!b)
 		return -1;
-	for (i = 0; i < b->count; ++i)
-		if (b->res[i].ok)
-			batch_enqueue_fetch(b, i, outs[i], out_caps[i]);
+	batch_enqueue_fetch_all(b, b->count, outs, out_caps);
 	if (!stbi_jpeg_batch_sync(b))
 		return -1;
 	for (i = 0; i < b->count; ++i)
@@ -562,8 +603,12 @@ API int stbi_jpeg_batch_debug_guards(stbi_jpeg_batch *b)
 	if (!b)
 		return -1;
 	r = jcu_debug_guards_ok(b->ctx);
-	if (r == 1 && b->pipe)
-		r = jcu_debug_guards_ok(b->pipe->ctx);
+	{
+		int pi;
+		for (pi = 0; pi < STBI_JPEG_PIPE_MAX - 1; ++pi)
+			if (r == 1 && b->pipe[pi])
+				r = jcu_debug_guards_ok(b->pipe[pi]->ctx);
+	}
 	return r;
 }
 
@@ -582,7 +627,7 @@ API int stbi_jpeg_decode_batch(stbi_jpeg_batch *b, const stbi_uc *const *bufs, c
 										 int req_comp, stbi_uc *const *outs, const size_t *out_caps, int *xs, int *ys,
 										 int *comps, int *status)
 {
-	int done = 0, nok = 0, chunk;
+	int done = 0, nok = 0, chunk, depth, k0;
 	stbi_jpeg_batch_timings acc;
 	if (!b || count < 0)
 		return -1;
@@ -598,30 +643,53 @@ API int stbi_jpeg_decode_batch(stbi_jpeg_batch *b, const stbi_uc *const *bufs, c
 		return nok;
 	}
 	chunk = b->params.chunk_images > 0 ? b->params.chunk_images : 256;
-	if (count > chunk && !b->pipe)
+	/* Software pipeline over chunks, `depth` objects deep (each with its own stream, staging and device
+	   buffers): object k % depth parses + uploads + launches + enqueues the download of chunk k on its own
+	   stream, then the host moves on to chunk k+1 on the next object and only waits for chunk k when that
+	   object is needed again.  Host parse, H2D, kernels and D2H of neighbouring chunks overlap; D2H (3 B/px over
+	   PCIe) is the floor.  Three deep, not two: with two, both downloads in flight finish together and the link
+	   idles while the host prepares the next chunk (measured: 11 ms of 155 per 1024 x 1080p).  Each object
+	   downloads on its own stream: one shared FIFO download stream measured 10-20 % slower. */
+	depth = 1;
+	if (count > chunk)
 	{
-		stbi_jpeg_batch_params pp = b->params;
-		b->pipe = stbi_jpeg_batch_create(&pp);
+		const char *dv = getenv("IMAGE_CODECS_B200_PIPE_DEPTH"); /* tuning hook */
+		depth = dv ? atoi(dv) : 3;
+		if (depth < 1) depth = 1;
+		if (depth > STBI_JPEG_PIPE_MAX) depth = STBI_JPEG_PIPE_MAX;
+		for (k0 = 0; k0 < depth - 1; ++k0)
+			if (!b->pipe[k0])
+			{
+				stbi_jpeg_batch_params pp = b->params;
+				b->pipe[k0] = stbi_jpeg_batch_create(&pp);
+				if (!b->pipe[k0])
+				{
+					depth = k0 + 1;
+					break;
+				}
+			}
 	}
 	{
-		/* two-deep software pipeline over chunks: object k&1 parses + uploads + launches + enqueues the
-		   download of chunk k on its own stream, then the host moves on to chunk k+1 on the other object and
-		   only waits for chunk k when that object is needed again.  Host parse, H2D, kernels and D2H of
-		   neighbouring chunks overlap; D2H (3 B/px over PCIe) is the floor. */
-		stbi_jpeg_batch *obj[2];
-		int pend_first[2] = {-1, -1}, pend_n[2] = {0, 0}, k = 0;
+		stbi_jpeg_batch *obj[STBI_JPEG_PIPE_MAX];
+		int pend_first[STBI_JPEG_PIPE_MAX] = {-1, -1, -1, -1}, pend_n[STBI_JPEG_PIPE_MAX] = {0, 0, 0, 0}, k = 0, pending = 0;
+		const int trace = getenv("IMAGE_CODECS_B200_TRACE") != NULL; /* diagnostic: host timeline of the chunk pipeline on stderr */
+		const double tr0 = now_ms();
+		double tr_wait0 = 0, tr_wait1 = 0, tr_prep = 0, tr_run = 0;
 		obj[0] = b;
-		obj[1] = b->pipe ? b->pipe : b;
-		while (done < count || pend_first[0] >= 0 || pend_first[1] >= 0)
+		for (k0 = 1; k0 < depth; ++k0)
+			obj[k0] = b->pipe[k0 - 1];
+		while (done < count || pending > 0)
 		{
-			const int slot = b->pipe ? (k & 1) : 0;
+			const int slot = k % depth;
 			stbi_jpeg_batch *s = obj[slot];
 			int i;
 			if (pend_first[slot] >= 0)
 			{
 				const int first = pend_first[slot], n = pend_n[slot];
+				tr_wait0 = now_ms() - tr0;
 				if (!stbi_jpeg_batch_sync(s))
 					return -1;
+				tr_wait1 = now_ms() - tr0;
 				batch_report(s, xs ? xs + first : NULL, ys ? ys + first : NULL, comps ? comps + first : NULL,
 								 status ? status + first : NULL);
 				for (i = 0; i < n; ++i)
@@ -645,6 +713,7 @@ API int stbi_jpeg_decode_batch(stbi_jpeg_batch *b, const stbi_uc *const *bufs, c
 				if (s->tm.selfsync_rounds > acc.selfsync_rounds)
 					acc.selfsync_rounds = s->tm.selfsync_rounds;
 				pend_first[slot] = -1;
+				--pending;
 			}
 			if (done < count)
 			{
@@ -653,13 +722,17 @@ API int stbi_jpeg_decode_batch(stbi_jpeg_batch *b, const stbi_uc *const *bufs, c
 				const int n = count - done < want ? count - done : want;
 				if (stbi_jpeg_batch_prepare(s, bufs + done, lens + done, n, req_comp, NULL, NULL, NULL, NULL) < 0)
 					return -1;
+				tr_prep = now_ms() - tr0;
 				if (!stbi_jpeg_batch_run(s))
 					return -1;
-				for (i = 0; i < n; ++i)
-					if (s->res[i].ok)
-						batch_enqueue_fetch(s, i, outs[done + i], out_caps[done + i]);
+				tr_run = now_ms() - tr0;
+				batch_enqueue_fetch_all(s, n, outs + done, out_caps + done);
+				if (trace)
+					fprintf(stderr, "chunk %d slot %d n %d: wait %.2f..%.2f prepared %.2f launched %.2f downloads enqueued %.2f\n", k, slot,
+							  n, tr_wait0, tr_wait1, tr_prep, tr_run, now_ms() - tr0);
 				pend_first[slot] = done;
 				pend_n[slot] = n;
+				++pending;
 				done += n;
 			}
 			++k;

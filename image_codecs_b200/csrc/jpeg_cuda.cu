@@ -37,6 +37,10 @@ struct jcu_ctx
 	int profile = 0;
 	int entropy_mode = 0;
 	cudaStream_t stream = nullptr;
+	/* downloads run on their own stream, behind an event of the compute stream */
+	cudaStream_t dl_own = nullptr, dl_use = nullptr;
+	cudaEvent_t ev_ready = nullptr, ev_dl = nullptr;
+	bool dl_open = false;
 	cudaEvent_t ev_h2d0 = nullptr, ev_h2d1 = nullptr, ev_run0 = nullptr, ev_ent1 = nullptr, ev_out1 = nullptr, ev_d2h0 = nullptr,
 					ev_d2h1 = nullptr;
 	bool d2h_open = false;
@@ -144,6 +148,16 @@ extern "C" int jcu_ctx_create(int device, int profile, int entropy_mode, jcu_ctx
 		delete c;
 		return (int)e;
 	}
+	e = cudaStreamCreateWithFlags(&c->dl_own, cudaStreamNonBlocking);
+	if (e != cudaSuccess)
+	{
+		cudaStreamDestroy(c->stream);
+		delete c;
+		return (int)e;
+	}
+	c->dl_use = c->dl_own;
+	cudaEventCreateWithFlags(&c->ev_ready, cudaEventDisableTiming);
+	cudaEventCreateWithFlags(&c->ev_dl, cudaEventDisableTiming);
 	cudaEvent_t *evs[] = {&c->ev_h2d0, &c->ev_h2d1, &c->ev_run0, &c->ev_ent1, &c->ev_out1, &c->ev_d2h0, &c->ev_d2h1};
 	for (auto ev : evs)
 		cudaEventCreate(ev);
@@ -169,9 +183,14 @@ extern "C" void jcu_ctx_destroy(jcu_ctx *c)
 	for (auto ev : evs)
 		if (ev)
 			cudaEventDestroy(ev);
+	cudaStreamSynchronize(c->dl_use);
+	cudaEventDestroy(c->ev_ready);
+	cudaEventDestroy(c->ev_dl);
+	cudaStreamDestroy(c->dl_own);
 	cudaStreamDestroy(c->stream);
 	delete c;
 }
+
 
 extern "C" int jcu_debug_guards_ok(jcu_ctx *c)
 {
@@ -575,23 +594,35 @@ extern "C" int jcu_run(jcu_ctx *c)
 extern "C" int jcu_sync(jcu_ctx *c)
 {
 	CK(cudaSetDevice(c->device));
-	if (c->profile && c->d2h_open)
+	if (c->dl_open)
 	{
-		CK(cudaEventRecord(c->ev_d2h1, c->stream));
+		if (c->profile)
+			CK(cudaEventRecord(c->ev_d2h1, c->dl_use));
+		CK(cudaEventRecord(c->ev_dl, c->dl_use));
 	}
 	CK(cudaStreamSynchronize(c->stream));
+	if (c->dl_open)
+	{
+		CK(cudaEventSynchronize(c->ev_dl));
+		c->dl_open = false;
+	}
 	return 0;
 }
 
 extern "C" int jcu_download(jcu_ctx *c, size_t off, size_t bytes, void *dst)
 {
 	CK(cudaSetDevice(c->device));
-	if (c->profile && !c->d2h_open)
+	if (!c->dl_open)
 	{
-		CK(cudaEventRecord(c->ev_d2h0, c->stream));
+		/* first download after a run: the download stream waits for the kernels */
+		CK(cudaEventRecord(c->ev_ready, c->stream));
+		CK(cudaStreamWaitEvent(c->dl_use, c->ev_ready, 0));
+		if (c->profile)
+			CK(cudaEventRecord(c->ev_d2h0, c->dl_use));
+		c->dl_open = true;
 		c->d2h_open = true;
 	}
-	CK(cudaMemcpyAsync(dst, (const uint8_t *)c->out.p + off, bytes, cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaMemcpyAsync(dst, (const uint8_t *)c->out.p + off, bytes, cudaMemcpyDeviceToHost, c->dl_use));
 	return 0;
 }
 

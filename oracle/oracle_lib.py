@@ -64,14 +64,16 @@ class Oracle:
         lib.oracle_idct_block.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         lib.oracle_ycbcr_row.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
         lib.oracle_resample_row.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
-        lib.oracle_plane_geometry.restype = C.c_int
-        lib.oracle_plane_geometry.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int),
-                                              C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
-                                              C.POINTER(C.c_int)]
-        lib.oracle_decode_capture.restype = C.c_void_p
-        lib.oracle_decode_capture.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int),
-                                              C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p),
-                                              C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        self.has_capture = hasattr(lib, "oracle_decode_capture")  # the reference builds only (intermediate planes)
+        if self.has_capture:
+            lib.oracle_plane_geometry.restype = C.c_int
+            lib.oracle_plane_geometry.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                                  C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                                  C.POINTER(C.c_int)]
+            lib.oracle_decode_capture.restype = C.c_void_p
+            lib.oracle_decode_capture.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                                  C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p),
+                                                  C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
         lib.oracle_time_decode.restype = C.c_double
         lib.oracle_time_decode.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_int), C.c_int, C.c_int, C.c_int,
                                            C.c_int, C.POINTER(C.c_longlong), C.POINTER(C.c_int)]

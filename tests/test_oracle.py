@@ -96,3 +96,41 @@ def test_reference_build_agrees_with_its_sse2_build():
     for fmt, w, h in [("420", 233, 177), ("444", 64, 48), ("gray", 129, 65), ("420_prog", 64, 48)]:
         d = S.stream(fmt, w, h, 1)
         assert np.array_equal(a.load_from_memory(d, 3)[0], b.load_from_memory(d, 3)[0])
+
+
+# ---- the plain-C restatement (oracle/jpeg_port.c) is pinned the same way, and against the reference build ----
+@pytest.fixture(scope="module")
+def port():
+    from oracle import oracle_lib
+
+    try:
+        return oracle_lib.load("port")
+    except Exception as e:  # not built
+        pytest.skip(f"oracle port not built: {e}")
+
+
+def test_port_matches_golden_fixtures(port, golden):
+    """oracle/jpeg_port.c against every committed fixture: the decoded-stream hashes of the whole format matrix,
+    the stored pixel vectors, the kernel-level vectors and the jpeg_write.c probe stream."""
+    test_oracle_matches_golden_matrix(port, golden)
+    test_oracle_matches_golden_vectors(port)
+    test_oracle_kernels_match_golden(port)
+    test_probe_stream_decodes_to_golden_hash(port, golden)
+
+
+def test_port_equals_reference_build(port):
+    """Where the compiled reference is present (oracle/_ref), the port must agree with it byte for byte on the
+    whole matrix, every req_comp, and on header queries."""
+    from oracle import oracle_lib
+
+    try:
+        ref = oracle_lib.load("reference")
+    except Exception:
+        pytest.skip("oracle/_ref not present")
+    for f, w, h, k in S.small_matrix():
+        data = S.stream(f, w, h, k)
+        assert ref.info_from_memory(data) == port.info_from_memory(data), (f, w, h)
+        for rc in (0, 1, 2, 3, 4):
+            a, b = ref.load_from_memory(data, rc), port.load_from_memory(data, rc)
+            assert a[1:] == b[1:], (f, w, h, rc)
+            assert np.array_equal(a[0], b[0]), (f, w, h, k, rc)

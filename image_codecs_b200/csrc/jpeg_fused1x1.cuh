@@ -42,13 +42,15 @@ __device__ __forceinline__ void f1_colour(uint32_t yw, uint32_t cbw, uint32_t cr
 	const int y = s420_byte<0x4440 + SEL>(yw);
 	const int cb = s420_byte<0x4440 + SEL>(cbw);
 	const int cr = s420_byte<0x4440 + SEL>(crw);
-	const int yfr = s420_mad(y, 4096, 2048 - 128 * 5743);
-	const int yfb = s420_mad(y, 4096, 2048 - 128 * 7258);
-	const int yfg = s420_mad(y, 4096, 2048 + 128 * 2925);
-	r = s420_mad(cr, 5743, yfr) >> 12;
-	b = s420_mad(cb, 7258, yfb) >> 12;
-	const int m = s420_mad(cb, -1410, 128 * 1410) & ~255;
-	g = (s420_mad(cr, -2925, yfg) + m) >> 12;
+	/* y + (t >> 12) is one LEA.HI.SX32; the -128 of both chroma samples lives in the constants */
+	r = y + (s420_mad(cr, 5743, 2048 - 128 * 5743) >> 12);
+	b = y + (s420_mad(cb, 7258, 2048 - 128 * 7258) >> 12);
+	/* Cr's 128 * 2925 = 1462 * 256 + 128: the multiple of 256 moves inside the mask, the 128 is OR-ed into the
+	   cleared bits by the same LOP3 */
+	int m, k128;
+	asm("mov.u32 %0, 128;" : "=r"(k128));
+	asm("lop3.b32 %0, %1, 0xffffff00, %2, 0xEA;" : "=r"(m) : "r"(s420_mad(cb, -1410, 128 * 1410 + 2048 + 1462 * 256)), "r"(k128));
+	g = y + (s420_mad(cr, -2925, m) >> 12);
 }
 
 template <int N, int NC, bool DEQ>

@@ -186,12 +186,11 @@ __device__ __forceinline__ void s420_colour(uint32_t c16, uint32_t yw, int &r, i
 	const int cr = ((int)c16) >> 24;
 	const int cb = s420_byte<0x4441>(c16);
 	const int y = s420_byte<0x4440 + YSEL>(yw);
-	const int yf = s420_mad(y, 4096, 2048);
-	const int yfb = s420_mad(y, 4096, 2048 - 128 * 7258);
-	r = s420_mad(cr, 5743, yf) >> 12;
-	b = s420_mad(cb, 7258, yfb) >> 12;
-	const int m = s420_mad(cb, -1410, 128 * 1410) & ~255;
-	g = (s420_mad(cr, -2925, yf) + m) >> 12;
+	/* y + (t >> 12) is one LEA.HI.SX32; 2048 is a multiple of 256, so it moves inside the masked term */
+	r = y + (s420_mad(cr, 5743, 2048) >> 12);
+	b = y + (s420_mad(cb, 7258, 2048 - 128 * 7258) >> 12);
+	const int m = s420_mad(cb, -1410, 128 * 1410 + 2048) & ~255;
+	g = y + (s420_mad(cr, -2925, m) >> 12);
 }
 
 /*

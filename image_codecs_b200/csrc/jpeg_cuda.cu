@@ -16,6 +16,7 @@
 #include "jpeg_entropy.cuh"
 #include "jpeg_entropy_baseline.cuh"
 #include "jpeg_selfsync.cuh"
+#include "jpeg_entropy_prog.cuh"
 #include "jpeg_output.cuh"
 #include "jpeg_fused420.cuh"
 #include "jpeg_fused1x1.cuh"
@@ -59,6 +60,7 @@ struct jcu_ctx
 	std::vector<int> wave_off; /* n_waves + 1 offsets into work_h */
 	std::vector<int> wave_nbase; /* per wave: leading work items that are baseline scans */
 	std::vector<char> wave_two;	  /* per wave: every baseline scan uses <= 2 distinct DC and <= 2 distinct AC tables */
+	std::vector<int> wave_ncoop;	  /* per wave: trailing work items that are single-segment progressive AC scans (jpeg_entropy_prog.cuh) */
 	std::vector<int> wave_nsmall;	  /* per wave: work items after the baseline ones that are progressive scans of <= 32 segments */
 	std::vector<int32_t> list_h; /* image lists per path, concatenated */
 	int list_off[4] = {0, 0, 0, 0}, list_n[4] = {0, 0, 0, 0};
@@ -357,19 +359,24 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 	c->wave_nbase.assign((size_t)b->n_waves, 0);
 	c->wave_two.assign((size_t)b->n_waves, 1);
 	c->wave_nsmall.assign((size_t)b->n_waves, 0);
+	c->wave_ncoop.assign((size_t)b->n_waves, 0);
 	for (int w = 0; w < b->n_waves; ++w)
 	{
 		c->wave_off[w] = (int)c->work_h.size();
-		/* three groups per wave, one launch each: baseline scans (k_entropy_baseline), progressive scans of at
-		   most ENT_SMALL_THREADS segments (32-thread CTAs), the other progressive scans */
-		for (int pass = 0; pass < 3; ++pass)
+		/* four groups per wave: baseline scans (k_entropy_baseline), progressive scans of at most
+		   ENT_SMALL_THREADS segments (32-thread CTAs), the other progressive scans, and progressive AC scans
+		   that are one long segment (warp-cooperative decoder, jpeg_entropy_prog.cuh; entropy_mode == 1 keeps
+		   them on the one-thread-per-segment path) */
+		for (int pass = 0; pass < 4; ++pass)
 		{
 			for (int s = 0; s < b->n_scans; ++s)
 			{
 				const jcu_scan &sc = b->scans[s];
 				if (sc.wave != w || !imgs[sc.image].ok || is_ss[s])
 					continue;
-				const int group = sc.kind == JCU_SCAN_BASELINE ? 0 : sc.nseg <= ENT_SMALL_THREADS ? 1 : 2;
+				const bool coop = (sc.kind == JCU_SCAN_PROG_AC_FIRST || sc.kind == JCU_SCAN_PROG_AC_REFINE) && sc.nseg == 1 &&
+										sc.ncomp == 1 && c->entropy_mode != 1;
+				const int group = sc.kind == JCU_SCAN_BASELINE ? 0 : coop ? 3 : sc.nseg <= ENT_SMALL_THREADS ? 1 : 2;
 				if (group != pass)
 					continue;
 				if (pass == 0)
@@ -403,7 +410,10 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 				c->wave_nbase[w] = (int)c->work_h.size() - c->wave_off[w];
 			if (pass == 1)
 				c->wave_nsmall[w] = (int)c->work_h.size() - c->wave_off[w] - c->wave_nbase[w];
+			if (pass == 2)
+				c->wave_ncoop[w] = (int)c->work_h.size(); /* start of the last group; a count after the loop */
 		}
+		c->wave_ncoop[w] = (int)c->work_h.size() - c->wave_ncoop[w];
 	}
 	c->wave_off[b->n_waves] = (int)c->work_h.size();
 
@@ -412,7 +422,7 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 	{
 		bool any_base = false;
 		for (int w = 0; w < b->n_waves; ++w)
-			any_base = any_base || c->wave_nbase[w] > 0;
+			any_base = any_base || c->wave_nbase[w] > 0 || c->wave_ncoop[w] > 0;
 		if (any_base)
 		{
 			CK(ensure(c->uslab, b->bitstream_bytes + 32 * ((size_t)b->n_segs + 4)));
@@ -501,7 +511,17 @@ extern "C" int jcu_run(jcu_ctx *c)
 					(const uint8_t *)c->uslab.p, (const uint32_t *)c->useg_len.p, (int16_t *)c->coef.p, (int32_t *)c->err.p);
 			c->launches++;
 		}
-		const int nsm = c->wave_nsmall[w];
+		const int nsm = c->wave_nsmall[w], nco = c->wave_ncoop[w];
+		if (nco > 0)
+		{
+			const EntWork *wc = wk + (n - nco);
+			k_unstuff<<<nco, ENTB_THREADS, 0, st>>>(wc, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p,
+																 (const uint8_t *)c->bits.p, (uint8_t *)c->uslab.p, (uint32_t *)c->useg_len.p);
+			k_prog_ac_coop<<<nco, PC_THREADS, 0, st>>>(wc, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p,
+																	 (const jcu_huff_spec *)c->huff.p, (const uint8_t *)c->uslab.p,
+																	 (const uint32_t *)c->useg_len.p, (int16_t *)c->coef.p, (int32_t *)c->err.p);
+			c->launches += 2;
+		}
 		if (nsm > 0)
 		{
 			k_entropy_segments<ENT_SMALL_THREADS><<<nsm, ENT_SMALL_THREADS, 0, st>>>(
@@ -509,9 +529,9 @@ extern "C" int jcu_run(jcu_ctx *c)
 				(const uint8_t *)c->bits.p, (int16_t *)c->coef.p, (int32_t *)c->err.p);
 			c->launches++;
 		}
-		if (n - nb - nsm > 0)
+		if (n - nb - nsm - nco > 0)
 		{
-			k_entropy_segments<ENT_THREADS><<<n - nb - nsm, ENT_THREADS, 0, st>>>(
+			k_entropy_segments<ENT_THREADS><<<n - nb - nsm - nco, ENT_THREADS, 0, st>>>(
 				wk + nb + nsm, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p, (const jcu_huff_spec *)c->huff.p,
 				(const uint8_t *)c->bits.p, (int16_t *)c->coef.p, (int32_t *)c->err.p);
 			c->launches++;

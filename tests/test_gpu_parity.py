@@ -176,6 +176,43 @@ def test_selfsync_full_size_444_and_gray(oracle, decoder):
     print("self-sync:", tm["selfsync_scans"], "scans,", tm["selfsync_rounds"], "refine rounds")
 
 
+@pytest.mark.parametrize("entropy_mode", [0, 1])
+def test_progressive_restartless_scans(oracle, entropy_mode):
+    """BASELINE.json configs[3]: progressive streams without restart markers.  entropy_mode 0 = warp-cooperative
+    AC scan decoder (jpeg_entropy_prog.cuh), 1 = one thread per scan.  Full-size 1080p (smooth and dense-noise
+    images, 4:2:0 / 4:4:4 / grey), deep successive-approximation scripts (long correction-bit runs, several
+    refinement passes per band), spectral selection only, and the small-size matrix."""
+    from tools import testenc as te
+
+    datas, tags = [], []
+    for kw in (dict(subsampling="420", progressive=1), dict(subsampling="444", progressive=2),
+               dict(colorspace=te.CS_GRAY, progressive=1)):
+        for i, d in enumerate(te.encode_many(2, 1920, 1080, kind=-1, base_seed=501, quality=90, **kw)):
+            datas.append(d)
+            tags.append(f"1080p {kw} #{i}")
+    deep = [(7, 0, 0, 0, 2), (1, 1, 63, 0, 3), (2, 1, 63, 0, 2), (4, 1, 63, 0, 2), (1, 1, 63, 3, 2), (1, 1, 63, 2, 1),
+            (2, 1, 63, 2, 1), (4, 1, 63, 2, 1), (7, 0, 0, 2, 1), (7, 0, 0, 1, 0), (1, 1, 63, 1, 0), (2, 1, 63, 1, 0),
+            (4, 1, 63, 1, 0)]
+    bands = [(7, 0, 0, 0, 0), (1, 1, 2, 0, 1), (1, 3, 9, 0, 1), (1, 10, 63, 0, 1), (2, 1, 63, 0, 0), (4, 1, 63, 0, 0),
+             (1, 1, 9, 1, 0), (1, 10, 63, 1, 0)]
+    for q in (50, 90, 100):
+        for kind in (0, 1, 2):
+            img = te.synth_rgb(640, 360, kind, 900 + q + kind)
+            for name, script in (("deep", deep), ("bands", bands)):
+                datas.append(te.encode(img, subsampling="420", quality=q, script=script))
+                tags.append(f"{name} q{q} kind{kind}")
+    for f, w, h, k in S.small_matrix():
+        if "prog" in f:
+            datas.append(S.stream(f, w, h, k))
+            tags.append(f"{f} {w}x{h} kind{k}")
+    d = ic.BatchDecoder(device=0, entropy_mode=entropy_mode)
+    for rc in (3, 0):
+        outs = d.decode(datas, rc)
+        for tag, data, got in zip(tags, datas, outs):
+            _check(oracle, got, data, rc, f"mode{entropy_mode} {tag} req{rc}")
+    d.close()
+
+
 @pytest.mark.parametrize("entropy_mode", [0, 2])
 def test_no_kernel_writes_past_a_device_buffer(oracle, entropy_mode):
     """Guard mode (compute-sanitizer is not available on every box): every device buffer is allocated at exactly

@@ -4,7 +4,7 @@
 #include <stdint.h>
 #define ITER 256
 #define UNR 8
-enum { IMAD, IADD, LOP, SHFN, PRMT, VMAX, SHRS, SEXT, FFMA, DP2A, I2IP, VMINRELU, LEA, SHL, NOPS };
+enum { IMAD, IADD, LOP, SHFN, PRMT, VMAX, SHRS, SEXT, FFMA, DP2A, I2IP, VMINRELU, LEA, SHL, MULHI, MADHI, FADD, FMUL, I2F, F2I, NOPS };
 template <int OP> __device__ __forceinline__ uint32_t op(uint32_t x, uint32_t a, uint32_t b)
 {
 	uint32_t d;
@@ -22,6 +22,12 @@ template <int OP> __device__ __forceinline__ uint32_t op(uint32_t x, uint32_t a,
 	else if (OP == VMINRELU) asm volatile("min.s32.relu %0, %1, %2;" : "=r"(d) : "r"(x), "r"(a));
 	else if (OP == LEA) asm volatile("{.reg .u32 t; shl.b32 t, %1, 3; add.u32 %0, t, %2;}" : "=r"(d) : "r"(x), "r"(a));
 	else if (OP == SHL) asm volatile("shl.b32 %0, %1, 3;" : "=r"(d) : "r"(x));
+	else if (OP == MULHI) asm volatile("mul.hi.s32 %0, %1, 4194304;" : "=r"(d) : "r"(x));
+	else if (OP == MADHI) asm volatile("mad.hi.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(x), "r"(a), "r"(b));
+	else if (OP == FADD) asm volatile("add.rn.f32 %0, %1, %2;" : "=r"(d) : "r"(x), "r"(a));
+	else if (OP == FMUL) asm volatile("mul.rn.f32 %0, %1, %2;" : "=r"(d) : "r"(x), "r"(a));
+	else if (OP == I2F) asm volatile("cvt.rn.f32.s32 %0, %1;" : "=r"(d) : "r"(x));
+	else if (OP == F2I) asm volatile("cvt.rni.s32.f32 %0, %1;" : "=r"(d) : "r"(x));
 	return d;
 }
 template <int A, int B, int RA, int RB> __global__ void k(uint32_t *out, uint32_t a, uint32_t b, long long *cyc)
@@ -66,6 +72,9 @@ int main()
 	R1(IMAD); R1(IADD); R1(LOP); R1(SHFN); R1(PRMT); R1(VMAX); R1(SHRS); R1(SEXT); R1(FFMA); R1(DP2A); R1(I2IP); R1(VMINRELU); R1(LEA); R1(SHL);
 	R2(IMAD, IADD); R2(IMAD, LOP); R2(IMAD, SHFN); R2(IMAD, PRMT); R2(IMAD, VMAX); R2(IMAD, SHRS); R2(IMAD, DP2A); R2(IMAD, I2IP); R2(IMAD, FFMA);
 	R2(PRMT, SHFN); R2(PRMT, IADD); R2(SHRS, IADD); R2(SHRS, PRMT); R2(DP2A, I2IP); R2(DP2A, IADD); R2(I2IP, IADD); R2(IADD, LOP); R2(VMAX, IADD); R2(DP2A, PRMT); R2(I2IP, PRMT);
+	R1(MULHI); R1(MADHI); R1(FADD); R1(FMUL); R1(I2F); R1(F2I);
+	R2(IMAD, MULHI); R2(IADD, MULHI); R2(FFMA, IADD); R2(FFMA, SHRS); R2(FFMA, MULHI); R2(FFMA, I2IP); R2(FFMA, PRMT); R2(FFMA, LEA); R2(IMAD, LEA); R2(IADD, LEA);
+	run<FFMA, IMAD, 2, 1>("2xFFMA+IMAD", out, cyc); run<FFMA, IADD, 2, 1>("2xFFMA+IADD", out, cyc); run<FFMA, IMAD, 3, 1>("3xFFMA+IMAD", out, cyc);
 	run<IMAD, IADD, 1, 2>("IMAD+2xIADD", out, cyc); run<IMAD, IADD, 1, 3>("IMAD+3xIADD", out, cyc);
 	printf("%s\n", cudaGetErrorString(cudaGetLastError()));
 	return 0;

@@ -364,7 +364,7 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 	{
 		c->wave_off[w] = (int)c->work_h.size();
 		/* four groups per wave: baseline scans (k_entropy_baseline), progressive scans of at most
-		   ENT_SMALL_THREADS segments (32-thread CTAs), the other progressive scans, and progressive AC scans
+		   ENT_SMALL_THREADS segments (32-thread CTAs), the other progressive scans, and progressive scans
 		   that are one long segment (warp-cooperative decoder, jpeg_entropy_prog.cuh; entropy_mode == 1 keeps
 		   them on the one-thread-per-segment path) */
 		for (int pass = 0; pass < 4; ++pass)
@@ -374,8 +374,10 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 				const jcu_scan &sc = b->scans[s];
 				if (sc.wave != w || !imgs[sc.image].ok || is_ss[s])
 					continue;
-				const bool coop = (sc.kind == JCU_SCAN_PROG_AC_FIRST || sc.kind == JCU_SCAN_PROG_AC_REFINE) && sc.nseg == 1 &&
-										sc.ncomp == 1 && c->entropy_mode != 1;
+				const bool ac = sc.kind == JCU_SCAN_PROG_AC_FIRST || sc.kind == JCU_SCAN_PROG_AC_REFINE;
+				/* a first DC pass clears its blocks (jpeg.c:385): only one that nothing precedes may rely on the zeroed slab */
+				const bool dc = sc.kind == JCU_SCAN_PROG_DC_REFINE || (sc.kind == JCU_SCAN_PROG_DC_FIRST && sc.wave == 0 && c->need_clear);
+				const bool coop = ((ac && sc.ncomp == 1) || dc) && sc.nseg == 1 && c->entropy_mode != 1;
 				const int group = sc.kind == JCU_SCAN_BASELINE ? 0 : coop ? 3 : sc.nseg <= ENT_SMALL_THREADS ? 1 : 2;
 				if (group != pass)
 					continue;
@@ -422,7 +424,7 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 	{
 		bool any_base = false;
 		for (int w = 0; w < b->n_waves; ++w)
-			any_base = any_base || c->wave_nbase[w] > 0 || c->wave_ncoop[w] > 0;
+			any_base = any_base || c->wave_nbase[w] > 0;
 		if (any_base)
 		{
 			CK(ensure(c->uslab, b->bitstream_bytes + 32 * ((size_t)b->n_segs + 4)));
@@ -515,12 +517,10 @@ extern "C" int jcu_run(jcu_ctx *c)
 		if (nco > 0)
 		{
 			const EntWork *wc = wk + (n - nco);
-			k_unstuff<<<nco, ENTB_THREADS, 0, st>>>(wc, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p,
-																 (const uint8_t *)c->bits.p, (uint8_t *)c->uslab.p, (uint32_t *)c->useg_len.p);
-			k_prog_ac_coop<<<nco, PC_THREADS, 0, st>>>(wc, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p,
-																	 (const jcu_huff_spec *)c->huff.p, (const uint8_t *)c->uslab.p,
-																	 (const uint32_t *)c->useg_len.p, (int16_t *)c->coef.p, (int32_t *)c->err.p);
-			c->launches += 2;
+			k_prog_coop<<<nco, PC_THREADS, 0, st>>>(wc, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p,
+																(const jcu_huff_spec *)c->huff.p, (const uint8_t *)c->bits.p, (int16_t *)c->coef.p,
+																(int32_t *)c->err.p);
+			c->launches++;
 		}
 		if (nsm > 0)
 		{

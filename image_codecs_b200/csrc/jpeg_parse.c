@@ -521,14 +521,18 @@ static int one_scan(parser *p)
 	   jpeg.c:1716; scans on disjoint data commute).  Baseline and first DC scans own the whole block (the
 	   latter clears it, jpeg.c:380). */
 	{
-		const int lo = (sc.kind == JCU_SCAN_BASELINE || sc.kind == JCU_SCAN_PROG_DC_FIRST) ? 0 : sc.ss;
-		const int hi = (sc.kind == JCU_SCAN_BASELINE || sc.kind == JCU_SCAN_PROG_DC_FIRST) ? 63 : sc.se;
+		/* write set in zig-zag positions.  A first AC pass can land up to 15 positions past its band: the
+		   reference does not check `k += r` against spec_end before it stores (jpeg.c:461-463), so on a damaged
+		   stream the stray coefficient is part of its result and later scans of those positions must see it */
+#define SCAN_LO(s) (((s)->kind == JCU_SCAN_BASELINE || (s)->kind == JCU_SCAN_PROG_DC_FIRST) ? 0 : (s)->ss)
+#define SCAN_HI(s) (((s)->kind == JCU_SCAN_BASELINE || (s)->kind == JCU_SCAN_PROG_DC_FIRST) ? 63 \
+						  : (s)->kind == JCU_SCAN_PROG_AC_FIRST ? ((s)->se + 15 > 63 ? 63 : (s)->se + 15) : (s)->se)
+		const int lo = SCAN_LO(&sc), hi = SCAN_HI(&sc);
 		int j, a, b, level = 0;
 		for (j = 0; j < r->nscans; ++j)
 		{
 			const jcu_scan *o = &r->scans[j];
-			const int olo = (o->kind == JCU_SCAN_BASELINE || o->kind == JCU_SCAN_PROG_DC_FIRST) ? 0 : o->ss;
-			const int ohi = (o->kind == JCU_SCAN_BASELINE || o->kind == JCU_SCAN_PROG_DC_FIRST) ? 63 : o->se;
+			const int olo = SCAN_LO(o), ohi = SCAN_HI(o);
 			int shared = 0;
 			for (a = 0; a < sc.ncomp; ++a)
 				for (b = 0; b < o->ncomp; ++b)

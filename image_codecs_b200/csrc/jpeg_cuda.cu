@@ -559,7 +559,8 @@ extern "C" int jcu_run(jcu_ctx *c)
 		{
 			int32_t changed = 0;
 			CK(cudaMemsetAsync(sb.changed, 0, sizeof(int32_t), st));
-			k_ss_decode<SS_REFINE><<<nw, SS_THREADS, 0, st>>>(SS_ARGS, parity);
+			k_ss_refine<<<nw, SS_THREADS, 0, st>>>(wk, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p,
+																(const jcu_huff_spec *)c->huff.p, (const uint8_t *)c->bits.p, sb, parity);
 			c->launches++;
 			parity ^= 1;
 			c->ss_rounds++;
@@ -570,7 +571,7 @@ extern "C" int jcu_run(jcu_ctx *c)
 		}
 		k_ss_scan<<<ns, 256, 0, st>>>((const SsScan *)c->ss_scans.p, sb.nblk, sb.first_blk);
 		k_ss_decode<SS_WRITE><<<nw, SS_THREADS, 0, st>>>(SS_ARGS, parity);
-		k_ss_dc<<<dim3(ns, 4), 256, 0, st>>>((const SsScan *)c->ss_scans.p, (const jcu_scan *)c->scans.p, d_img, (int16_t *)c->coef.p);
+		k_ss_dc<<<dim3(ns, 4), SS_DC_THREADS, 0, st>>>((const SsScan *)c->ss_scans.p, (const jcu_scan *)c->scans.p, d_img, (int16_t *)c->coef.p);
 		c->launches += 3;
 #undef SS_ARGS
 	}

@@ -318,6 +318,109 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 	}
 }
 
+/*
+ * Phase 2, several Jacobi iterations per launch.  Same work split as k_ss_decode.  Iteration 0 takes every
+ * entry state from the previous round (global memory); the following iterations pass exit states from thread
+ * t-1 to thread t of the same CTA through shared memory, so a correction travels up to SS_INNER subsequences
+ * per launch instead of one, and the many cheap tail rounds (a launch and a host round trip each) disappear.
+ * A thread whose entry state did not change does not decode again.
+ */
+#define SS_INNER 8
+__global__ void __launch_bounds__(SS_THREADS)
+k_ss_refine(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans, const jcu_image *__restrict__ images,
+				const uint32_t *__restrict__ seg_start, const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ bitstream,
+				SsBuffers sb, int parity)
+{
+	__shared__ EntbShared sh;
+	__shared__ SsState s_exit[SS_THREADS];
+	const int tid = threadIdx.x;
+	const SsWork w = work[blockIdx.x];
+	const jcu_scan *sc = &scans[w.scan];
+	const jcu_image *im = &images[sc->image];
+	entb_setup(sh, sc, im, huff, tid, SS_THREADS);
+	const bool valid = (uint32_t)tid < w.count;
+	const uint32_t i = w.first + (uint32_t)tid, gi = w.scan_base + i;
+	const uint8_t *__restrict__ base = bitstream + im->data_off;
+	const uint32_t scan_start = seg_start[sc->seg_first], end = sc->data_end;
+	const bool last = i + 1 == w.scan_nsub;
+	const uint32_t limit = last ? end : scan_start + (i + 1) * SS_SUB_BYTES;
+	const SsState *cur = parity ? sb.exit_b : sb.exit_a;
+	SsState *nxt = parity ? sb.exit_a : sb.exit_b;
+	const int nblk_mcu = sh.nblk;
+
+	SsState mine, used;
+	mine.pos = mine.aux = 0;
+	mine.buf = 0;
+	used = mine;
+	if (valid)
+	{
+		mine = cur[gi];
+		used = sb.entry_used[gi];
+	}
+	const SsState first = mine;
+	for (int it = 0; it < SS_INNER; ++it)
+	{
+		bool changed = false;
+		if (valid && i > 0 && (it == 0 || tid > 0))
+		{
+			const SsState en = it == 0 ? cur[gi - 1] : s_exit[tid - 1];
+			if (!ss_same(en, used))
+			{
+				used = en;
+				SBR br;
+				br.end = end;
+				br.pos = en.pos;
+				br.buf = en.buf;
+				br.nbits = (int)(en.aux & 255u);
+				int k = (int)((en.aux >> 8) & 255u), b = (int)(en.aux >> 16);
+				uint32_t nb = 0;
+				for (;;)
+				{
+					sbr_topup(base, br);
+					if (br.pos >= limit)
+						break;
+					const uint32_t ent = sh.blk[b];
+					int val, kadv;
+					if (k == 0)
+					{
+						ss_symbol<ENTB_DC_BITS, true>(br, &sh.dc[(ent >> 12) & 3u], val, kadv);
+						k = 1;
+					}
+					else
+					{
+						const bool ok = ss_symbol<ENTB_AC_BITS, false>(br, &sh.ac[(ent >> 16) & 3u], val, kadv);
+						k += ok ? kadv : 1;
+					}
+					if (k >= 64)
+					{
+						k = 0;
+						++nb;
+						b = (b + 1 == nblk_mcu) ? 0 : b + 1;
+					}
+				}
+				SsState ex;
+				ex.pos = br.pos;
+				ex.aux = (uint32_t)br.nbits | ((uint32_t)k << 8) | ((uint32_t)b << 16);
+				ex.buf = br.buf;
+				sb.nblk[gi] = nb;
+				changed = !ss_same(ex, mine);
+				mine = ex;
+			}
+		}
+		__syncthreads(); /* everyone has read s_exit of the previous iteration */
+		s_exit[tid] = mine;
+		if (!__syncthreads_or(changed))
+			break;
+	}
+	if (valid)
+	{
+		sb.entry_used[gi] = used;
+		nxt[gi] = mine;
+		if (!ss_same(mine, first))
+			atomicOr(sb.changed, 1);
+	}
+}
+
 /* Phase 3: per scan, exclusive prefix sum of the per-subsequence block counts.  grid = self-sync scans. */
 __global__ void __launch_bounds__(256)
 k_ss_scan(const SsScan *__restrict__ ss, const uint32_t *__restrict__ nblk, uint32_t *__restrict__ first_blk)
@@ -356,11 +459,12 @@ k_ss_scan(const SsScan *__restrict__ ss, const uint32_t *__restrict__ nblk, uint
  * decode order carry DC differences in coefficient 0; their running sum is the reference's dc_pred
  * (jpeg.c:323-325) and the stored value is (short)(dc * dequant[0]).
  */
-__global__ void __launch_bounds__(256)
+#define SS_DC_THREADS 1024
+__global__ void __launch_bounds__(SS_DC_THREADS)
 k_ss_dc(const SsScan *__restrict__ ss, const jcu_scan *__restrict__ scans, const jcu_image *__restrict__ images,
 		  int16_t *__restrict__ coef)
 {
-	__shared__ int s_part[256];
+	__shared__ int s_part[SS_DC_THREADS];
 	const jcu_scan *sc = &scans[ss[blockIdx.x].scan];
 	const int slot = blockIdx.y;
 	if (slot >= sc->ncomp)
@@ -373,7 +477,7 @@ k_ss_dc(const SsScan *__restrict__ ss, const jcu_scan *__restrict__ scans, const
 	const uint32_t n = (uint32_t)sc->total_units * (uint32_t)per;
 	int16_t *plane = coef + cp->coef_off;
 	const int tid = threadIdx.x;
-	const uint32_t chunk = (n + 255u) / 256u;
+	const uint32_t chunk = (n + SS_DC_THREADS - 1u) / SS_DC_THREADS;
 	const uint32_t lo = min(n, (uint32_t)tid * chunk), hi = min(n, lo + chunk);
 	auto dc_of = [&](uint32_t j) -> int16_t * {
 		const uint32_t m = j / (uint32_t)per, r = j - m * (uint32_t)per;
@@ -390,7 +494,7 @@ k_ss_dc(const SsScan *__restrict__ ss, const jcu_scan *__restrict__ scans, const
 	if (tid == 0)
 	{
 		int run = 0;
-		for (int i = 0; i < 256; ++i)
+		for (int i = 0; i < SS_DC_THREADS; ++i)
 		{
 			const int v = s_part[i];
 			s_part[i] = run;

@@ -18,6 +18,7 @@
 #include <time.h>
 #include <unistd.h>
 
+#include <math.h>
 #include "../../include/jpeg_cuda_abi.h"
 #include "jpeg_parse.h"
 
@@ -893,6 +894,136 @@ API stbi_uc *stbi_load(char const *filename, int *x, int *y, int *comp, int req_
 	fclose(f);
 	return r;
 }
+
+/* ---- 16-bit and float variants: the JPEG codec is 8-bit, the reference widens its result on the
+ *      host after the (already flipped) 8-bit load -- stbi__load_and_postprocess_16bit convert.c:108-133 with
+ *      stbi__convert_8_to_16 :18-35, stbi__loadf_main :286-304 with stbi__ldr_to_hdr common.c:391-424.  Same here:
+ *      thin host epilogues behind the GPU decode. ---- */
+static float g_l2h_gamma = 2.2f, g_l2h_scale = 1.0f; /* convert.c:402 */
+static float g_h2l_gamma_i = 1.0f / 2.2f, g_h2l_scale_i = 1.0f; /* convert.c:408; no HDR source format on this path */
+API void stbi_ldr_to_hdr_gamma(float gamma) { g_l2h_gamma = gamma; }
+API void stbi_ldr_to_hdr_scale(float scale) { g_l2h_scale = scale; }
+API void stbi_hdr_to_ldr_gamma(float gamma) { g_h2l_gamma_i = 1 / gamma; }
+API void stbi_hdr_to_ldr_scale(float scale) { g_h2l_scale_i = 1 / scale; }
+
+static stbi_us *widen_16(stbi_uc *data, const int *x, const int *y, const int *comp, int req_comp)
+{
+	size_t n, i;
+	stbi_us *out;
+	if (!data)
+		return NULL;
+	n = (size_t)*x * (size_t)*y * (size_t)(req_comp ? req_comp : *comp);
+	out = (stbi_us *)malloc(n > 0 ? n * 2 : 1);
+	if (!out)
+	{
+		free(data);
+		return (stbi_us *)err_null("outofmem");
+	}
+	for (i = 0; i < n; ++i)
+		out[i] = (stbi_us)((data[i] << 8) + data[i]); /* 0 -> 0, 255 -> 0xffff (convert.c:30) */
+	free(data);
+	return out;
+}
+
+static float *widen_float(stbi_uc *data, const int *x, const int *y, const int *comp, int req_comp)
+{
+	size_t px, i;
+	int c, k, n;
+	float *out, lut[256];
+	if (!data)
+		return (float *)err_null("unknown image type"); /* stbi__loadf_main replaces the codec's reason, convert.c:303 */
+	c = req_comp ? req_comp : *comp;
+	px = (size_t)*x * (size_t)*y;
+	out = (float *)malloc(px > 0 ? px * (size_t)c * sizeof(float) : 1);
+	if (!out)
+	{
+		free(data);
+		return (float *)err_null("outofmem");
+	}
+	n = (c & 1) ? c : c - 1; /* non-alpha components (common.c:404-407) */
+	for (k = 0; k < 256; ++k) /* the reference's per-sample expression (common.c:412) depends on the byte alone */
+		lut[k] = (float)(pow((unsigned char)k / 255.0f, g_l2h_gamma) * g_l2h_scale);
+	for (i = 0; i < px; ++i)
+	{
+		for (k = 0; k < n; ++k)
+			out[i * (size_t)c + (size_t)k] = lut[data[i * (size_t)c + (size_t)k]];
+		if (n < c)
+			out[i * (size_t)c + (size_t)n] = data[i * (size_t)c + (size_t)n] / 255.0f;
+	}
+	free(data);
+	return out;
+}
+
+API stbi_us *stbi_load_16_from_memory(stbi_uc const *buffer, int len, int *x, int *y, int *comp, int req_comp)
+{
+	int xx, yy, cc;
+	stbi_uc *d = stbi_load_from_memory(buffer, len, &xx, &yy, &cc, req_comp);
+	if (d) { if (x) *x = xx; if (y) *y = yy; if (comp) *comp = cc; }
+	return widen_16(d, &xx, &yy, &cc, req_comp);
+}
+API stbi_us *stbi_load_16_from_callbacks(stbi_io_callbacks const *clbk, void *user, int *x, int *y, int *comp, int req_comp)
+{
+	int xx, yy, cc;
+	stbi_uc *d = stbi_load_from_callbacks(clbk, user, &xx, &yy, &cc, req_comp);
+	if (d) { if (x) *x = xx; if (y) *y = yy; if (comp) *comp = cc; }
+	return widen_16(d, &xx, &yy, &cc, req_comp);
+}
+API stbi_us *stbi_load_from_file_16(FILE *f, int *x, int *y, int *comp, int req_comp)
+{
+	int xx, yy, cc;
+	stbi_uc *d = stbi_load_from_file(f, &xx, &yy, &cc, req_comp);
+	if (d) { if (x) *x = xx; if (y) *y = yy; if (comp) *comp = cc; }
+	return widen_16(d, &xx, &yy, &cc, req_comp);
+}
+API stbi_us *stbi_load_16(char const *filename, int *x, int *y, int *comp, int req_comp)
+{
+	FILE *f = fopen(filename, "rb");
+	stbi_us *r;
+	if (!f)
+		return (stbi_us *)err_null("can't fopen");
+	r = stbi_load_from_file_16(f, x, y, comp, req_comp);
+	fclose(f);
+	return r;
+}
+API float *stbi_loadf_from_memory(stbi_uc const *buffer, int len, int *x, int *y, int *comp, int req_comp)
+{
+	int xx, yy, cc;
+	stbi_uc *d = stbi_load_from_memory(buffer, len, &xx, &yy, &cc, req_comp);
+	if (d) { if (x) *x = xx; if (y) *y = yy; if (comp) *comp = cc; }
+	return widen_float(d, &xx, &yy, &cc, req_comp);
+}
+API float *stbi_loadf_from_callbacks(stbi_io_callbacks const *clbk, void *user, int *x, int *y, int *comp, int req_comp)
+{
+	int xx, yy, cc;
+	stbi_uc *d = stbi_load_from_callbacks(clbk, user, &xx, &yy, &cc, req_comp);
+	if (d) { if (x) *x = xx; if (y) *y = yy; if (comp) *comp = cc; }
+	return widen_float(d, &xx, &yy, &cc, req_comp);
+}
+API float *stbi_loadf_from_file(FILE *f, int *x, int *y, int *comp, int req_comp)
+{
+	int xx, yy, cc;
+	stbi_uc *d = stbi_load_from_file(f, &xx, &yy, &cc, req_comp);
+	if (d) { if (x) *x = xx; if (y) *y = yy; if (comp) *comp = cc; }
+	return widen_float(d, &xx, &yy, &cc, req_comp);
+}
+API float *stbi_loadf(char const *filename, int *x, int *y, int *comp, int req_comp)
+{
+	FILE *f = fopen(filename, "rb");
+	float *r;
+	if (!f)
+		return (float *)err_null("can't fopen");
+	r = stbi_loadf_from_file(f, x, y, comp, req_comp);
+	fclose(f);
+	return r;
+}
+/* a JPEG is neither HDR nor 16-bit (convert.c:345-400, image_api.c:96-145) */
+API int stbi_is_hdr_from_memory(stbi_uc const *buffer, int len) { (void)buffer; (void)len; return 0; }
+API int stbi_is_hdr_from_callbacks(stbi_io_callbacks const *clbk, void *user) { (void)clbk; (void)user; return 0; }
+API int stbi_is_hdr_from_file(FILE *f) { (void)f; return 0; }
+API int stbi_is_hdr(char const *filename) { (void)filename; return 0; }
+API int stbi_is_16_bit_from_callbacks(stbi_io_callbacks const *clbk, void *user) { (void)clbk; (void)user; return 0; }
+API int stbi_is_16_bit_from_file(FILE *f) { (void)f; return 0; }
+API int stbi_is_16_bit(char const *filename) { (void)filename; return 0; }
 
 /* ---- info: header-only, no GPU (stbi__jpeg_info_raw, jpeg.c:2466) ---- */
 API int stbi_info_from_memory(stbi_uc const *buffer, int len, int *x, int *y, int *comp)

@@ -41,6 +41,7 @@ extern "C" {
 #endif
 
 typedef unsigned char stbi_uc;
+typedef unsigned short stbi_us;
 
 enum
 {
@@ -72,8 +73,32 @@ STBIDEF int stbi_info_from_file(FILE *f, int *x, int *y, int *comp);
 STBIDEF int stbi_info_from_memory(stbi_uc const *buffer, int len, int *x, int *y, int *comp);
 STBIDEF int stbi_info_from_callbacks(stbi_io_callbacks const *clbk, void *user, int *x, int *y, int *comp);
 
-/* JPEG is never 16-bit (reference image_api.c:96-145 returns 0 for it) */
+/* ---- 16-bit and float variants (reference convert.c:213-252, 286-337): the 8-bit GPU decode widened on the host
+ *      exactly as the reference widens its own 8-bit result (v * 257; pow(v / 255, gamma) * scale) ---- */
+STBIDEF stbi_us *stbi_load_16(char const *filename, int *x, int *y, int *comp, int req_comp);
+STBIDEF stbi_us *stbi_load_from_file_16(FILE *f, int *x, int *y, int *comp, int req_comp);
+STBIDEF stbi_us *stbi_load_16_from_memory(stbi_uc const *buffer, int len, int *x, int *y, int *comp, int req_comp);
+STBIDEF stbi_us *stbi_load_16_from_callbacks(stbi_io_callbacks const *clbk, void *user, int *x, int *y, int *comp,
+															int req_comp);
+STBIDEF float *stbi_loadf(char const *filename, int *x, int *y, int *comp, int req_comp);
+STBIDEF float *stbi_loadf_from_file(FILE *f, int *x, int *y, int *comp, int req_comp);
+STBIDEF float *stbi_loadf_from_memory(stbi_uc const *buffer, int len, int *x, int *y, int *comp, int req_comp);
+STBIDEF float *stbi_loadf_from_callbacks(stbi_io_callbacks const *clbk, void *user, int *x, int *y, int *comp,
+													  int req_comp);
+STBIDEF void stbi_ldr_to_hdr_gamma(float gamma); /* convert.c:404-411 */
+STBIDEF void stbi_ldr_to_hdr_scale(float scale);
+STBIDEF void stbi_hdr_to_ldr_gamma(float gamma);
+STBIDEF void stbi_hdr_to_ldr_scale(float scale);
+
+/* JPEG is never HDR or 16-bit (reference convert.c:345-400, image_api.c:96-145 return 0 for it) */
+STBIDEF int stbi_is_hdr(char const *filename);
+STBIDEF int stbi_is_hdr_from_file(FILE *f);
+STBIDEF int stbi_is_hdr_from_memory(stbi_uc const *buffer, int len);
+STBIDEF int stbi_is_hdr_from_callbacks(stbi_io_callbacks const *clbk, void *user);
+STBIDEF int stbi_is_16_bit(char const *filename);
+STBIDEF int stbi_is_16_bit_from_file(FILE *f);
 STBIDEF int stbi_is_16_bit_from_memory(stbi_uc const *buffer, int len);
+STBIDEF int stbi_is_16_bit_from_callbacks(stbi_io_callbacks const *clbk, void *user);
 
 /* ---- result ownership / errors / flags (names used by the reference, defined in its missing header) ---- */
 STBIDEF void stbi_image_free(void *retval_from_stbi_load);

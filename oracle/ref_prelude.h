@@ -199,4 +199,10 @@ static void stbi__start_write_callbacks(stbi__write_context *s, stbi_write_func 
 }
 static int stbi__flip_vertically_on_write = 0;
 
+
+/* LDR->HDR widening (common.c:391, only with ORACLE_LINEAR): the reference defines these in convert.c:402 AFTER
+   common.c uses them, so its missing header must have carried tentative definitions like these */
+#ifndef STBI_NO_LINEAR
+static float stbi__l2h_gamma, stbi__l2h_scale;
+#endif
 #endif

@@ -28,7 +28,9 @@
 #define STBI_NO_PNM
 #define STBI_NO_HDR
 #define STBI_NO_TGA
+#ifndef ORACLE_LINEAR /* the _linear build keeps stbi_loadf* (convert.c:286-337, common.c:391-424) */
 #define STBI_NO_LINEAR
+#endif
 #define STBI_NO_STDIO
 #define STBI_NO_ZLIB
 #define STBI_WRITE_NO_STDIO
@@ -61,6 +63,9 @@ static int stbi__info_main(stbi__context *s, int *x, int *y, int *comp)
 /* ------------------------------------------------------------------------------------ */
 
 #define ORACLE_API __attribute__((visibility("default")))
+
+/* the reference's flip flag (convert.c:97-101 reads it; its setter lived in the missing header) */
+ORACLE_API void oracle_set_flip(int flag) { stbi__vertically_flip_on_load = flag; }
 
 ORACLE_API int oracle_is_sse2(void)
 {

@@ -213,6 +213,76 @@ def test_progressive_restartless_scans(oracle, entropy_mode):
     d.close()
 
 
+def test_16_bit_and_float_variants(oracle):
+    """stbi_load_16* / stbi_loadf* (reference convert.c:213-252, 286-337): the 8-bit decode widened exactly as the
+    reference widens its own (v * 257; pow(v / 255, gamma) * scale, alpha linear), with the flip flag and a changed
+    gamma/scale, and the reference's failure strings."""
+    import ctypes as C
+
+    ours = ic.lib()
+    ref = None
+    if oracle.kind.startswith("reference"):
+        try:
+            oracle.lib.stbi_loadf_from_memory, oracle.lib.oracle_set_flip
+            ref = oracle.lib
+        except AttributeError:
+            ref = None
+    ip = C.POINTER(C.c_int)
+    for L in filter(None, (ours, ref)):
+        L.stbi_load_16_from_memory.restype = C.c_void_p
+        L.stbi_load_16_from_memory.argtypes = [C.c_char_p, C.c_int, ip, ip, ip, C.c_int]
+        L.stbi_loadf_from_memory.restype = C.c_void_p
+        L.stbi_loadf_from_memory.argtypes = [C.c_char_p, C.c_int, ip, ip, ip, C.c_int]
+        L.stbi_ldr_to_hdr_gamma.argtypes = [C.c_float]
+        L.stbi_ldr_to_hdr_scale.argtypes = [C.c_float]
+        L.stbi_image_free.argtypes = [C.c_void_p]
+        L.stbi_failure_reason.restype = C.c_char_p
+
+    def call(L, fn, data, rc, dtype):
+        x, y, c = C.c_int(0), C.c_int(0), C.c_int(0)
+        p = getattr(L, fn)(data, len(data), C.byref(x), C.byref(y), C.byref(c), rc)
+        if not p:
+            return None, L.stbi_failure_reason()
+        n = rc if rc else c.value
+        ct = C.c_uint16 if dtype == np.uint16 else C.c_float
+        out = np.ctypeslib.as_array(C.cast(p, C.POINTER(ct)), shape=(y.value, x.value, n)).copy()
+        L.stbi_image_free(p)
+        return out, (x.value, y.value, c.value)
+
+    streams = [S.stream("420", 233, 177, 1), S.stream("gray", 64, 48, 0), S.stream("444_prog_ss", 129, 65, 2)]
+    for flip in (0, 1):
+        ic.set_flip_vertically_on_load(bool(flip))
+        if ref is not None:
+            ref.oracle_set_flip(flip)
+        for data in streams:
+            for rc in (0, 1, 2, 3, 4):
+                base, *_ = ic.stbi_load_from_memory(data, rc)
+                got16, meta = call(ours, "stbi_load_16_from_memory", data, rc, np.uint16)
+                assert np.array_equal(got16, base.astype(np.uint16) * 257)
+                gotf, _ = call(ours, "stbi_loadf_from_memory", data, rc, np.float32)
+                assert gotf.shape == base.shape
+                if ref is not None:
+                    w16, wmeta = call(ref, "stbi_load_16_from_memory", data, rc, np.uint16)
+                    assert meta == wmeta and np.array_equal(got16, w16)
+                    wf, _ = call(ref, "stbi_loadf_from_memory", data, rc, np.float32)
+                    assert np.array_equal(gotf.view(np.uint32), wf.view(np.uint32)), f"float widening differs (req_comp {rc})"
+    ic.set_flip_vertically_on_load(False)
+    if ref is not None:
+        ref.oracle_set_flip(0)
+        for L in (ours, ref):
+            L.stbi_ldr_to_hdr_gamma(1.8)
+            L.stbi_ldr_to_hdr_scale(2.5)
+        a, _ = call(ours, "stbi_loadf_from_memory", streams[0], 4, np.float32)
+        b, _ = call(ref, "stbi_loadf_from_memory", streams[0], 4, np.float32)
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+        for L in (ours, ref):
+            L.stbi_ldr_to_hdr_gamma(2.2)
+            L.stbi_ldr_to_hdr_scale(1.0)
+        bad = streams[0][:300]
+        assert call(ours, "stbi_loadf_from_memory", bad, 3, np.float32) == call(ref, "stbi_loadf_from_memory", bad, 3, np.float32)
+        assert call(ours, "stbi_load_16_from_memory", bad, 3, np.uint16) == call(ref, "stbi_load_16_from_memory", bad, 3, np.uint16)
+
+
 @pytest.mark.parametrize("entropy_mode", [0, 1, 2])
 def test_damaged_streams_decode_like_the_reference(oracle, entropy_mode):
     """Truncated and bit-flipped files: whatever the reference makes of them (zero bits past the end of a scan,

@@ -11,6 +11,7 @@ from .api import (  # noqa: F401
     BatchDecoder,
     LibraryMissing,
     cuda_device_count,
+    encode_batch,
     failure_reason,
     inspect,
     lib,
@@ -19,9 +20,10 @@ from .api import (  # noqa: F401
     stbi_info_from_memory,
     stbi_load,
     stbi_load_from_memory,
+    write_jpg_to_bytes,
 )
 
 __all__ = [
-    "BatchDecoder", "LibraryMissing", "cuda_device_count", "failure_reason", "inspect", "lib", "lib_path",
+    "BatchDecoder", "LibraryMissing", "cuda_device_count", "encode_batch", "write_jpg_to_bytes", "failure_reason", "inspect", "lib", "lib_path",
     "set_flip_vertically_on_load", "stbi_info_from_memory", "stbi_load", "stbi_load_from_memory",
 ]

@@ -148,6 +148,46 @@ def stbi_load(filename: str, req_comp: int = 0) -> Tuple[Optional[np.ndarray], i
     return out, x.value, y.value, c.value
 
 
+def encode_batch(images: Sequence[np.ndarray], quality: int = 90, device: int = 0) -> Tuple[List[Optional[bytes]], float]:
+    """stbi_jpeg_encode_batch: images are (h, w, comp) uint8 arrays (comp 1..4).  Returns (files, kernel_ms); the
+    bytes of each file equal what the reference's stbi_write_jpg_to_func (jpeg_write.c:368) writes."""
+    L = lib()
+    n = len(images)
+    arrs = [np.ascontiguousarray(a if a.ndim == 3 else a[:, :, None], dtype=np.uint8) for a in images]
+    px = (C.c_void_p * n)(*[a.ctypes.data for a in arrs])
+    xs = (C.c_int * n)(*[a.shape[1] for a in arrs])
+    ys = (C.c_int * n)(*[a.shape[0] for a in arrs])
+    cs = (C.c_int * n)(*[a.shape[2] for a in arrs])
+    outs = (C.c_void_p * n)()
+    lens = (C.c_int * n)()
+    ms = C.c_float(0)
+    L.stbi_jpeg_encode_batch.restype = C.c_int
+    L.stbi_jpeg_encode_batch.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p,
+                                         C.c_void_p, C.POINTER(C.c_float)]
+    L.stbi_jpeg_encode_batch(device, px, xs, ys, cs, n, quality, outs, lens, C.byref(ms))
+    files: List[Optional[bytes]] = []
+    for i in range(n):
+        if outs[i]:
+            files.append(C.string_at(outs[i], lens[i]))
+            L.stbi_image_free(C.c_void_p(outs[i]))
+        else:
+            files.append(None)
+    return files, float(ms.value)
+
+
+def write_jpg_to_bytes(image: np.ndarray, quality: int = 90) -> Optional[bytes]:
+    """stbi_write_jpg_to_func with a collecting callback (the reference's public writer entry point)."""
+    L = lib()
+    a = np.ascontiguousarray(image if image.ndim == 3 else image[:, :, None], dtype=np.uint8)
+    chunks: List[bytes] = []
+    CB = C.CFUNCTYPE(None, C.c_void_p, C.c_void_p, C.c_int)
+    cb = CB(lambda ctx, data, size: chunks.append(C.string_at(data, size)))
+    L.stbi_write_jpg_to_func.restype = C.c_int
+    L.stbi_write_jpg_to_func.argtypes = [CB, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
+    ok = L.stbi_write_jpg_to_func(cb, None, a.shape[1], a.shape[0], a.shape[2], a.ctypes.data, quality)
+    return b"".join(chunks) if ok else None
+
+
 def stbi_info_from_memory(data: bytes) -> Optional[Tuple[int, int, int]]:
     x, y, c = C.c_int(0), C.c_int(0), C.c_int(0)
     ok = lib().stbi_info_from_memory(data, len(data), C.byref(x), C.byref(y), C.byref(c))

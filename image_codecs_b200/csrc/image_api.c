@@ -1025,6 +1025,272 @@ API int stbi_is_16_bit_from_callbacks(stbi_io_callbacks const *clbk, void *user)
 API int stbi_is_16_bit_from_file(FILE *f) { (void)f; return 0; }
 API int stbi_is_16_bit(char const *filename) { (void)filename; return 0; }
 
+/* ===================================================================================== */
+/* encoder: host side of jpeg_encode.cuh; replaces stbi_write_jpg_core,  */
+/* codec/jpeg_write.c:172-366, with the same byte stream                                   */
+/* ===================================================================================== */
+/* ITU-T T.81 Annex K.3 Huffman tables (the ones jpeg_write.c:175-200 writes into every file): code counts
+   per length 1..16, then the symbols in code order */
+static const unsigned char k_dc_lum_bits[16] = {0, 1, 5, 1, 1, 1, 1, 1, 1, 0, 0, 0, 0, 0, 0, 0};
+static const unsigned char k_dc_chr_bits[16] = {0, 3, 1, 1, 1, 1, 1, 1, 1, 1, 1, 0, 0, 0, 0, 0};
+static const unsigned char k_dc_vals[12] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11};
+static const unsigned char k_ac_lum_bits[16] = {0, 2, 1, 3, 3, 2, 4, 3, 5, 5, 4, 4, 0, 0, 1, 0x7d};
+static const unsigned char k_ac_chr_bits[16] = {0, 2, 1, 2, 4, 4, 3, 4, 7, 5, 4, 4, 0, 1, 2, 0x77};
+static const unsigned char k_ac_lum_vals[162] = {
+	0x01, 0x02, 0x03, 0x00, 0x04, 0x11, 0x05, 0x12, 0x21, 0x31, 0x41, 0x06, 0x13, 0x51, 0x61, 0x07, 0x22, 0x71, 0x14, 0x32, 0x81, 0x91,
+	0xa1, 0x08, 0x23, 0x42, 0xb1, 0xc1, 0x15, 0x52, 0xd1, 0xf0, 0x24, 0x33, 0x62, 0x72, 0x82, 0x09, 0x0a, 0x16, 0x17, 0x18, 0x19, 0x1a,
+	0x25, 0x26, 0x27, 0x28, 0x29, 0x2a, 0x34, 0x35, 0x36, 0x37, 0x38, 0x39, 0x3a, 0x43, 0x44, 0x45, 0x46, 0x47, 0x48, 0x49, 0x4a, 0x53,
+	0x54, 0x55, 0x56, 0x57, 0x58, 0x59, 0x5a, 0x63, 0x64, 0x65, 0x66, 0x67, 0x68, 0x69, 0x6a, 0x73, 0x74, 0x75, 0x76, 0x77, 0x78, 0x79,
+	0x7a, 0x83, 0x84, 0x85, 0x86, 0x87, 0x88, 0x89, 0x8a, 0x92, 0x93, 0x94, 0x95, 0x96, 0x97, 0x98, 0x99, 0x9a, 0xa2, 0xa3, 0xa4, 0xa5,
+	0xa6, 0xa7, 0xa8, 0xa9, 0xaa, 0xb2, 0xb3, 0xb4, 0xb5, 0xb6, 0xb7, 0xb8, 0xb9, 0xba, 0xc2, 0xc3, 0xc4, 0xc5, 0xc6, 0xc7, 0xc8, 0xc9,
+	0xca, 0xd2, 0xd3, 0xd4, 0xd5, 0xd6, 0xd7, 0xd8, 0xd9, 0xda, 0xe1, 0xe2, 0xe3, 0xe4, 0xe5, 0xe6, 0xe7, 0xe8, 0xe9, 0xea, 0xf1, 0xf2,
+	0xf3, 0xf4, 0xf5, 0xf6, 0xf7, 0xf8, 0xf9, 0xfa};
+static const unsigned char k_ac_chr_vals[162] = {
+	0x00, 0x01, 0x02, 0x03, 0x11, 0x04, 0x05, 0x21, 0x31, 0x06, 0x12, 0x41, 0x51, 0x07, 0x61, 0x71, 0x13, 0x22, 0x32, 0x81, 0x08, 0x14,
+	0x42, 0x91, 0xa1, 0xb1, 0xc1, 0x09, 0x23, 0x33, 0x52, 0xf0, 0x15, 0x62, 0x72, 0xd1, 0x0a, 0x16, 0x24, 0x34, 0xe1, 0x25, 0xf1, 0x17,
+	0x18, 0x19, 0x1a, 0x26, 0x27, 0x28, 0x29, 0x2a, 0x35, 0x36, 0x37, 0x38, 0x39, 0x3a, 0x43, 0x44, 0x45, 0x46, 0x47, 0x48, 0x49, 0x4a,
+	0x53, 0x54, 0x55, 0x56, 0x57, 0x58, 0x59, 0x5a, 0x63, 0x64, 0x65, 0x66, 0x67, 0x68, 0x69, 0x6a, 0x73, 0x74, 0x75, 0x76, 0x77, 0x78,
+	0x79, 0x7a, 0x82, 0x83, 0x84, 0x85, 0x86, 0x87, 0x88, 0x89, 0x8a, 0x92, 0x93, 0x94, 0x95, 0x96, 0x97, 0x98, 0x99, 0x9a, 0xa2, 0xa3,
+	0xa4, 0xa5, 0xa6, 0xa7, 0xa8, 0xa9, 0xaa, 0xb2, 0xb3, 0xb4, 0xb5, 0xb6, 0xb7, 0xb8, 0xb9, 0xba, 0xc2, 0xc3, 0xc4, 0xc5, 0xc6, 0xc7,
+	0xc8, 0xc9, 0xca, 0xd2, 0xd3, 0xd4, 0xd5, 0xd6, 0xd7, 0xd8, 0xd9, 0xda, 0xe2, 0xe3, 0xe4, 0xe5, 0xe6, 0xe7, 0xe8, 0xe9, 0xea, 0xf2,
+	0xf3, 0xf4, 0xf5, 0xf6, 0xf7, 0xf8, 0xf9, 0xfa};
+/* luminance / chrominance quantisers of Annex K.1, natural order, and the raster -> zig-zag index map */
+static const int k_qt_lum[64] = {16, 11, 10, 16, 24, 40, 51, 61, 12, 12, 14, 19, 26, 58, 60, 55, 14, 13, 16, 24, 40, 57,
+											69, 56, 14, 17, 22, 29, 51, 87, 80, 62, 18, 22, 37, 56, 68, 109, 103, 77, 24, 35, 55, 64,
+											81, 104, 113, 92, 49, 64, 78, 87, 103, 121, 120, 101, 72, 92, 95, 98, 112, 100, 103, 99};
+static const int k_qt_chr[64] = {17, 18, 24, 47, 99, 99, 99, 99, 18, 21, 26, 66, 99, 99, 99, 99, 24, 26, 56, 99, 99, 99,
+											99, 99, 47, 66, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99,
+											99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99};
+static const unsigned char k_zigzag[64] = {0,	1,	 5,  6,	14, 15, 27, 28, 2,  4,	7,	 13, 16, 26, 29, 42, 3,	 8,  12, 17, 25, 30,
+														 41, 43, 9,  11, 18, 24, 31, 40, 44, 53, 10, 19, 23, 32, 39, 45, 52, 54, 20, 22, 33, 38,
+														 46, 51, 55, 60, 21, 34, 37, 47, 50, 56, 59, 61, 35, 36, 48, 49, 57, 58, 62, 63};
+
+static int g_flip_on_write;
+API void stbi_flip_vertically_on_write(int flag) { g_flip_on_write = flag; }
+
+/* canonical codes (T.81 Annex C) of one table: out[symbol] = code | length << 16 */
+static void enc_codes(const unsigned char bits[16], const unsigned char *vals, uint32_t out[256])
+{
+	unsigned code = 0;
+	int l, i, k = 0;
+	memset(out, 0, 256 * sizeof(uint32_t));
+	for (l = 1; l <= 16; ++l)
+	{
+		for (i = 0; i < bits[l - 1]; ++i)
+			out[vals[k++]] = code++ | ((uint32_t)l << 16);
+		code <<= 1;
+	}
+}
+
+/* quality -> quantiser tables (zig-zag order, as stored in DQT) and the float scale tables (jpeg_write.c:210-235) */
+static void enc_tables(int quality, int *subsample, unsigned char ytab[64], unsigned char uvtab[64], float fd_y[64], float fd_uv[64])
+{
+	static const float aasf[8] = {1.0f * 2.828427125f, 1.387039845f * 2.828427125f, 1.306562965f * 2.828427125f, 1.175875602f * 2.828427125f,
+											1.0f * 2.828427125f, 0.785694958f * 2.828427125f, 0.541196100f * 2.828427125f, 0.275899379f * 2.828427125f};
+	int i, row, col, k;
+	quality = quality ? quality : 90;
+	*subsample = quality <= 90 ? 1 : 0;
+	quality = quality < 1 ? 1 : quality > 100 ? 100 : quality;
+	quality = quality < 50 ? 5000 / quality : 200 - quality * 2;
+	for (i = 0; i < 64; ++i)
+	{
+		int yti = (k_qt_lum[i] * quality + 50) / 100, uvti = (k_qt_chr[i] * quality + 50) / 100;
+		ytab[k_zigzag[i]] = (unsigned char)(yti < 1 ? 1 : yti > 255 ? 255 : yti);
+		uvtab[k_zigzag[i]] = (unsigned char)(uvti < 1 ? 1 : uvti > 255 ? 255 : uvti);
+	}
+	for (row = 0, k = 0; row < 8; ++row)
+		for (col = 0; col < 8; ++col, ++k)
+		{
+			fd_y[k] = 1 / (ytab[k_zigzag[k]] * aasf[row] * aasf[col]);
+			fd_uv[k] = 1 / (uvtab[k_zigzag[k]] * aasf[row] * aasf[col]);
+		}
+}
+
+/* SOI, APP0, DQT, SOF0, DHT, SOS exactly as jpeg_write.c:238-262 writes them; returns the length */
+static size_t enc_header(unsigned char *h, int width, int height, int subsample, const unsigned char ytab[64], const unsigned char uvtab[64])
+{
+	static const unsigned char head0[] = {0xFF, 0xD8, 0xFF, 0xE0, 0, 0x10, 'J', 'F', 'I', 'F', 0, 1, 1, 0, 0, 1, 0, 1, 0, 0, 0xFF, 0xDB, 0, 0x84, 0};
+	static const unsigned char head2[] = {0xFF, 0xDA, 0, 0xC, 3, 1, 0, 2, 0x11, 3, 0x11, 0, 0x3F, 0};
+	const unsigned char head1[] = {0xFF, 0xC0, 0, 0x11, 8, (unsigned char)(height >> 8), (unsigned char)(height & 0xff), (unsigned char)(width >> 8),
+											 (unsigned char)(width & 0xff), 3, 1, (unsigned char)(subsample ? 0x22 : 0x11), 0, 2, 0x11, 1, 3, 0x11, 1,
+											 0xFF, 0xC4, 0x01, 0xA2, 0};
+	unsigned char *p = h;
+#define ENC_PUT(src, n) do { memcpy(p, (src), (n)); p += (n); } while (0)
+	ENC_PUT(head0, sizeof(head0));
+	ENC_PUT(ytab, 64);
+	*p++ = 1;
+	ENC_PUT(uvtab, 64);
+	ENC_PUT(head1, sizeof(head1));
+	ENC_PUT(k_dc_lum_bits, 16);
+	ENC_PUT(k_dc_vals, 12);
+	*p++ = 0x10;
+	ENC_PUT(k_ac_lum_bits, 16);
+	ENC_PUT(k_ac_lum_vals, 162);
+	*p++ = 1;
+	ENC_PUT(k_dc_chr_bits, 16);
+	ENC_PUT(k_dc_vals, 12);
+	*p++ = 0x11;
+	ENC_PUT(k_ac_chr_bits, 16);
+	ENC_PUT(k_ac_chr_vals, 162);
+	ENC_PUT(head2, sizeof(head2));
+#undef ENC_PUT
+	return (size_t)(p - h);
+}
+
+static pthread_mutex_t g_enc_lock = PTHREAD_MUTEX_INITIALIZER;
+static __thread int g_enc_pixels_on_device; /* set by stbi_jpeg_encode_batch_device around its call */
+static jcu_ctx *g_enc_ctx[16];
+
+/* New batched entry point: encodes `count` images (comps interleaved bytes per pixel, rows top-down) on `device`
+   into malloc'ed files (caller frees each with stbi_image_free).  pixels_on_device: the pointers are device
+   pointers into ONE allocation starting at pixels[0].  Returns the number of files produced; kernel_ms (optional)
+   receives the device time of the kernels. */
+API int stbi_jpeg_encode_batch(int device, const stbi_uc *const *pixels, const int *xs, const int *ys, const int *comps, int count,
+										 int quality, stbi_uc **outs, int *out_lens, float *kernel_ms)
+{
+	jcu_enc_image *imgs;
+	unsigned char *hdrs, *slab = NULL;
+	uint32_t huff[4][256], *lens;
+	size_t pix_bytes = 0, out_bytes = 0, nblocks = 0;
+	int i, nok = 0, rc;
+	jcu_ctx *ctx;
+	if (count <= 0)
+		return 0;
+	if (device < 0 || device >= 16 || jcu_device_count() <= device)
+		return err_zero("no cuda device");
+	pthread_mutex_lock(&g_enc_lock);
+	if (!g_enc_ctx[device] && jcu_ctx_create(device, 0, 0, &g_enc_ctx[device]) != 0)
+		g_enc_ctx[device] = NULL;
+	ctx = g_enc_ctx[device];
+	if (!ctx)
+	{
+		pthread_mutex_unlock(&g_enc_lock);
+		return err_zero("no cuda device");
+	}
+	imgs = (jcu_enc_image *)calloc((size_t)count, sizeof(*imgs));
+	hdrs = (unsigned char *)calloc((size_t)count, JCU_ENC_HDR_STRIDE);
+	lens = (uint32_t *)calloc((size_t)count, sizeof(uint32_t));
+	enc_codes(k_dc_lum_bits, k_dc_vals, huff[0]);
+	enc_codes(k_dc_chr_bits, k_dc_vals, huff[1]);
+	enc_codes(k_ac_lum_bits, k_ac_lum_vals, huff[2]);
+	enc_codes(k_ac_chr_bits, k_ac_chr_vals, huff[3]);
+	for (i = 0; i < count; ++i)
+	{
+		jcu_enc_image *im = &imgs[i];
+		unsigned char ytab[64], uvtab[64];
+		int sub, m;
+		outs[i] = NULL;
+		out_lens[i] = 0;
+		/* jpeg_write.c:204: !data || !width || !height || comp > 4 || comp < 1 -> 0; 16-bit SOF fields */
+		if (!pixels[i] || xs[i] <= 0 || ys[i] <= 0 || comps[i] < 1 || comps[i] > 4 || xs[i] > 65535 || ys[i] > 65535)
+			continue;
+		enc_tables(quality, &sub, ytab, uvtab, im->fdtbl_y, im->fdtbl_uv);
+		m = sub ? 16 : 8;
+		im->width = xs[i];
+		im->height = ys[i];
+		im->comp = comps[i];
+		im->subsample = sub;
+		im->flip = g_flip_on_write;
+		im->mcu_x = (xs[i] + m - 1) / m;
+		im->mcu_y = (ys[i] + m - 1) / m;
+		im->nblocks = im->mcu_x * im->mcu_y * (sub ? 6 : 3);
+		im->pix_off = pix_bytes;
+		im->blk_first = nblocks;
+		im->hdr_len = (uint32_t)enc_header(hdrs + (size_t)i * JCU_ENC_HDR_STRIDE, xs[i], ys[i], sub, ytab, uvtab);
+		/* worst case: every block full (224 bytes) and every byte stuffed */
+		im->out_cap = (uint32_t)(im->hdr_len + 2 + (size_t)im->nblocks * 448 + 16);
+		im->out_off = out_bytes;
+		out_bytes += ALIGN_UP((size_t)im->out_cap, 256);
+		pix_bytes += ALIGN_UP((size_t)xs[i] * (size_t)ys[i] * (size_t)comps[i], 16);
+		nblocks += (size_t)im->nblocks;
+	}
+	if (g_enc_pixels_on_device)
+	{
+		/* device pixels: offsets are relative to pixels[0] */
+		for (i = 0; i < count; ++i)
+			if (imgs[i].nblocks)
+				imgs[i].pix_off = (uint64_t)((uintptr_t)pixels[i] - (uintptr_t)pixels[0]);
+		rc = jcu_encode(ctx, imgs, count, (const uint8_t *)pixels[0], pix_bytes, 1, hdrs, &huff[0][0], out_bytes, lens,
+							 kernel_ms);
+	}
+	else
+	{
+		slab = (unsigned char *)jcu_host_alloc(pix_bytes ? pix_bytes : 1);
+		if (!slab)
+		{
+			free(imgs); free(hdrs); free(lens);
+			pthread_mutex_unlock(&g_enc_lock);
+			return err_zero("outofmem");
+		}
+		for (i = 0; i < count; ++i)
+			if (imgs[i].nblocks)
+				memcpy(slab + imgs[i].pix_off, pixels[i], (size_t)xs[i] * (size_t)ys[i] * (size_t)comps[i]);
+		rc = jcu_encode(ctx, imgs, count, slab, pix_bytes, 0, hdrs, &huff[0][0], out_bytes, lens, kernel_ms);
+	}
+	if (rc == 0)
+		for (i = 0; i < count; ++i)
+			if (imgs[i].nblocks && lens[i])
+			{
+				outs[i] = (stbi_uc *)malloc(lens[i]);
+				if (outs[i] && jcu_encode_fetch(ctx, imgs[i].out_off, lens[i], outs[i]) == 0)
+				{
+					out_lens[i] = (int)lens[i];
+					++nok;
+				}
+				else
+				{
+					free(outs[i]);
+					outs[i] = NULL;
+				}
+			}
+	if (slab)
+		jcu_host_free(slab);
+	free(imgs); free(hdrs); free(lens);
+	pthread_mutex_unlock(&g_enc_lock);
+	return nok;
+}
+
+/* same, with the source pixels already in device memory (all inside one allocation, pixels[0] the lowest address) */
+API int stbi_jpeg_encode_batch_device(int device, const stbi_uc *const *pixels, const int *xs, const int *ys, const int *comps, int count,
+												  int quality, stbi_uc **outs, int *out_lens, float *kernel_ms)
+{
+	int r;
+	g_enc_pixels_on_device = 1;
+	r = stbi_jpeg_encode_batch(device, pixels, xs, ys, comps, count, quality, outs, out_lens, kernel_ms);
+	g_enc_pixels_on_device = 0;
+	return r;
+}
+
+/* stbi_write_jpg_to_func (jpeg_write.c:368): same bytes, handed to `func` in one call (the reference makes many
+   small calls; their concatenation is what a caller can observe) */
+API int stbi_write_jpg_to_func(stbi_write_func *func, void *context, int x, int y, int comp, const void *data, int quality)
+{
+	const stbi_uc *px[1];
+	stbi_uc *out[1] = {NULL};
+	int len[1] = {0};
+	const char *dev = getenv("IMAGE_CODECS_B200_DEVICE");
+	if (!data || !x || !y || comp > 4 || comp < 1 || !func)
+		return 0;
+	px[0] = (const stbi_uc *)data;
+	if (stbi_jpeg_encode_batch(dev ? atoi(dev) : 0, px, &x, &y, &comp, 1, quality, out, len, NULL) != 1)
+		return 0;
+	func(context, out[0], len[0]);
+	free(out[0]);
+	return 1;
+}
+
+static void enc_file_write(void *context, void *data, int size) { fwrite(data, 1, (size_t)size, (FILE *)context); }
+API int stbi_write_jpg(char const *filename, int x, int y, int comp, const void *data, int quality)
+{
+	FILE *f = fopen(filename, "wb");
+	int r;
+	if (!f)
+		return 0;
+	r = stbi_write_jpg_to_func(enc_file_write, f, x, y, comp, data, quality);
+	fclose(f);
+	return r;
+}
+
 /* ---- info: header-only, no GPU (stbi__jpeg_info_raw, jpeg.c:2466) ---- */
 API int stbi_info_from_memory(stbi_uc const *buffer, int len, int *x, int *y, int *comp)
 {

@@ -17,6 +17,7 @@
 #include "jpeg_entropy_baseline.cuh"
 #include "jpeg_selfsync.cuh"
 #include "jpeg_entropy_prog.cuh"
+#include "jpeg_encode.cuh"
 #include "jpeg_output.cuh"
 #include "jpeg_fused420.cuh"
 #include "jpeg_fused1x1.cuh"
@@ -48,6 +49,8 @@ struct jcu_ctx
 	DevBuf bits, images, scans, segs, huff, work, coef, planes, out, err, lists;
 	DevBuf ss_work, ss_scans, ss_exit_a, ss_exit_b, ss_entry, ss_nblk, ss_first, ss_changed;
 	DevBuf uslab, useg_len; /* unstuffed copy of the baseline segments (jpeg_entropy_baseline.cuh) */
+	DevBuf enc_pix, enc_img, enc_coef, enc_nbits, enc_bitoff, enc_tot, enc_bitbuf, enc_ffcnt, enc_ffoff, enc_out, enc_len, enc_hdr; /* encoder */
+	cudaEvent_t ev_enc0 = nullptr, ev_enc1 = nullptr;
 	std::vector<SsWork> ss_work_h; /* self-synchronising decode: CTA work items over all waves */
 	std::vector<SsScan> ss_scan_h;
 	uint32_t ss_nsub_total = 0, ss_max_nsub = 0;
@@ -177,10 +180,15 @@ extern "C" void jcu_ctx_destroy(jcu_ctx *c)
 	cudaSetDevice(c->device);
 	cudaStreamSynchronize(c->stream);
 	DevBuf *bufs[] = {&c->bits, &c->images, &c->scans, &c->segs, &c->huff, &c->work, &c->coef, &c->planes, &c->out, &c->err, &c->lists,
-							&c->ss_work, &c->ss_scans, &c->ss_exit_a, &c->ss_exit_b, &c->ss_entry, &c->ss_nblk, &c->ss_first, &c->ss_changed, &c->uslab, &c->useg_len};
+							&c->ss_work, &c->ss_scans, &c->ss_exit_a, &c->ss_exit_b, &c->ss_entry, &c->ss_nblk, &c->ss_first, &c->ss_changed, &c->uslab, &c->useg_len,
+							&c->enc_pix, &c->enc_img, &c->enc_coef, &c->enc_nbits, &c->enc_bitoff, &c->enc_tot, &c->enc_bitbuf, &c->enc_ffcnt, &c->enc_ffoff, &c->enc_out, &c->enc_len, &c->enc_hdr};
 	for (auto b : bufs)
 		if (b->p)
 			cudaFree(b->p);
+	if (c->ev_enc0)
+		cudaEventDestroy(c->ev_enc0);
+	if (c->ev_enc1)
+		cudaEventDestroy(c->ev_enc1);
 	cudaEvent_t evs[] = {c->ev_h2d0, c->ev_h2d1, c->ev_run0, c->ev_ent1, c->ev_out1, c->ev_d2h0, c->ev_d2h1};
 	for (auto ev : evs)
 		if (ev)
@@ -675,6 +683,80 @@ extern "C" int jcu_get_timings(jcu_ctx *c, jcu_timings *t)
 	cudaGetLastError();
 	return 0;
 }
+
+/* ---- encoder (jpeg_encode.cuh) ---- */
+extern "C" int jcu_encode(jcu_ctx *c, const jcu_enc_image *imgs, int n, const uint8_t *pixels, size_t pixel_bytes, int pixels_on_device,
+								  const uint8_t *headers, const uint32_t *huff, size_t out_bytes, uint32_t *out_len, float *kernel_ms)
+{
+	CK(cudaSetDevice(c->device));
+	if (n <= 0)
+		return 0;
+	cudaStream_t st = c->stream;
+	size_t nblocks = 0;
+	uint32_t max_blocks = 0;
+	for (int i = 0; i < n; ++i)
+	{
+		nblocks = std::max(nblocks, (size_t)imgs[i].blk_first + (size_t)imgs[i].nblocks);
+		max_blocks = std::max(max_blocks, (uint32_t)imgs[i].nblocks);
+	}
+	const size_t nchunks = nblocks * (ENC_BLOCK_BYTES / ENC_CHUNK);
+	if (!c->ev_enc0)
+	{
+		CK(cudaEventCreate(&c->ev_enc0));
+		CK(cudaEventCreate(&c->ev_enc1));
+	}
+	if (!pixels_on_device)
+		CK(ensure(c->enc_pix, pixel_bytes + 16));
+	CK(ensure(c->enc_img, sizeof(jcu_enc_image) * (size_t)n));
+	CK(ensure(c->enc_coef, nblocks * 128 + 256));
+	CK(ensure(c->enc_nbits, nblocks * 4 + 16));
+	CK(ensure(c->enc_bitoff, nblocks * 4 + 16));
+	CK(ensure(c->enc_tot, (size_t)n * 8 + 16)); /* [0, n): bit totals, [n, 2n): 0xFF totals */
+	CK(ensure(c->enc_bitbuf, nblocks * ENC_BLOCK_BYTES + 256));
+	CK(ensure(c->enc_ffcnt, nchunks * 4 + 16));
+	CK(ensure(c->enc_ffoff, nchunks * 4 + 16));
+	CK(ensure(c->enc_out, out_bytes + 16));
+	CK(ensure(c->enc_len, (size_t)n * 4 + 16));
+	CK(ensure(c->enc_hdr, (size_t)n * JCU_ENC_HDR_STRIDE));
+	CK(cudaMemcpyToSymbolAsync(c_enc_huff, huff, sizeof(uint32_t) * 4 * 256, 0, cudaMemcpyHostToDevice, st));
+	if (!pixels_on_device)
+		CK(cudaMemcpyAsync(c->enc_pix.p, pixels, pixel_bytes, cudaMemcpyHostToDevice, st));
+	CK(cudaMemcpyAsync(c->enc_img.p, imgs, sizeof(jcu_enc_image) * (size_t)n, cudaMemcpyHostToDevice, st));
+	CK(cudaMemcpyAsync(c->enc_hdr.p, headers, (size_t)n * JCU_ENC_HDR_STRIDE, cudaMemcpyHostToDevice, st));
+	const uint8_t *d_pix = pixels_on_device ? pixels : (const uint8_t *)c->enc_pix.p;
+	const jcu_enc_image *d_img = (const jcu_enc_image *)c->enc_img.p;
+	uint32_t *d_tot = (uint32_t *)c->enc_tot.p;
+	CK(cudaEventRecord(c->ev_enc0, st));
+	CK(cudaMemsetAsync(c->enc_bitbuf.p, 0, nblocks * ENC_BLOCK_BYTES, st));
+	const dim3 gb((max_blocks + ENC_THREADS - 1) / ENC_THREADS, (unsigned)n);
+	const dim3 gc((max_blocks * (ENC_BLOCK_BYTES / ENC_CHUNK) + ENC_THREADS - 1) / ENC_THREADS, (unsigned)n);
+	k_enc_dct<<<gb, ENC_THREADS, 0, st>>>(d_img, d_pix, (int16_t *)c->enc_coef.p);
+	k_enc_count<<<gb, ENC_THREADS, 0, st>>>(d_img, (const int16_t *)c->enc_coef.p, (uint32_t *)c->enc_nbits.p);
+	k_enc_scan<<<n, 1024, 0, st>>>(d_img, (const uint32_t *)c->enc_nbits.p, (uint32_t *)c->enc_bitoff.p, d_tot, nullptr, 0);
+	k_enc_emit<<<gb, ENC_THREADS, 0, st>>>(d_img, (const int16_t *)c->enc_coef.p, (const uint32_t *)c->enc_bitoff.p, (uint8_t *)c->enc_bitbuf.p);
+	k_enc_ffcount<<<gc, ENC_THREADS, 0, st>>>(d_img, (const uint8_t *)c->enc_bitbuf.p, d_tot, (uint32_t *)c->enc_ffcnt.p);
+	k_enc_scan<<<n, 1024, 0, st>>>(d_img, (const uint32_t *)c->enc_ffcnt.p, (uint32_t *)c->enc_ffoff.p, d_tot + n, d_tot, 1);
+	k_enc_stuff<<<gc, ENC_THREADS, 0, st>>>(d_img, (const uint8_t *)c->enc_bitbuf.p, d_tot, (const uint32_t *)c->enc_ffoff.p, d_tot + n,
+														  (const uint8_t *)c->enc_hdr.p, (uint8_t *)c->enc_out.p, (uint32_t *)c->enc_len.p);
+	CK(cudaGetLastError());
+	CK(cudaEventRecord(c->ev_enc1, st));
+	CK(cudaMemcpyAsync(out_len, c->enc_len.p, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToHost, st));
+	CK(cudaStreamSynchronize(st));
+	if (kernel_ms)
+		cudaEventElapsedTime(kernel_ms, c->ev_enc0, c->ev_enc1);
+	c->launches = 7;
+	return 0;
+}
+
+extern "C" int jcu_encode_fetch(jcu_ctx *c, size_t off, size_t bytes, void *dst)
+{
+	CK(cudaSetDevice(c->device));
+	CK(cudaMemcpyAsync(dst, (const uint8_t *)c->enc_out.p + off, bytes, cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaStreamSynchronize(c->stream));
+	return 0;
+}
+
+extern "C" void *jcu_encode_device_out(jcu_ctx *c) { return c->enc_out.p; }
 
 /* ---- stage-level test entry points ---- */
 __global__ void k_test_idct(const int16_t *coef, const uint16_t *qt, int n, uint8_t *out)

@@ -105,6 +105,17 @@ STBIDEF void stbi_image_free(void *retval_from_stbi_load);
 STBIDEF const char *stbi_failure_reason(void); /* thread-local */
 STBIDEF void stbi_set_flip_vertically_on_load(int flag_true_if_should_flip); /* convert.c:97-101 */
 
+/* ---- JPEG writer (reference codec/jpeg_write.c:368-390): same byte stream, encoded on the GPU ---- */
+typedef void stbi_write_func(void *context, void *data, int size);
+STBIDEF int stbi_write_jpg_to_func(stbi_write_func *func, void *context, int x, int y, int comp, const void *data, int quality);
+STBIDEF int stbi_write_jpg(char const *filename, int x, int y, int comp, const void *data, int quality);
+STBIDEF void stbi_flip_vertically_on_write(int flag);
+/* batched (new): files are malloc'ed, free each with stbi_image_free; returns the number produced */
+STBIDEF int stbi_jpeg_encode_batch(int device, const stbi_uc *const *pixels, const int *xs, const int *ys, const int *comps,
+											  int count, int quality, stbi_uc **outs, int *out_lens, float *kernel_ms);
+STBIDEF int stbi_jpeg_encode_batch_device(int device, const stbi_uc *const *pixels, const int *xs, const int *ys, const int *comps,
+														int count, int quality, stbi_uc **outs, int *out_lens, float *kernel_ms);
+
 /* ===================================================================================== */
 /* Batched decode (new; semantics per image identical to stbi_load_from_memory)          */
 /* ===================================================================================== */

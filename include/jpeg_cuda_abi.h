@@ -173,6 +173,31 @@ JCU_API int jcu_debug_guards_ok(jcu_ctx *c);
 JCU_API int jcu_test_ycbcr(jcu_ctx *c, const uint8_t *y, const uint8_t *cb, const uint8_t *cr, int n, int step, uint8_t *out);
 JCU_API int jcu_read_coefs(jcu_ctx *c, size_t elem_off, size_t elems, int16_t *dst); /* coefficient slab after run */
 
+/* ---- encoder (replaces stbi_write_jpg_core, codec/jpeg_write.c:172-366) ---- */
+#define JCU_ENC_HDR_STRIDE 1024 /* bytes reserved per image in the header staging array */
+typedef struct
+{
+	int32_t width, height, comp; /* source pixels: comp interleaved bytes per pixel (1..4), rows top-down */
+	int32_t subsample;			  /* 1 = 4:2:0 (16x16 MCUs, quality <= 90 in the reference), 0 = 4:4:4 */
+	int32_t flip;					  /* read the rows bottom-up (stbi__flip_vertically_on_write) */
+	int32_t mcu_x, mcu_y, nblocks;
+	uint64_t pix_off;	  /* bytes into the pixel slab */
+	uint64_t blk_first; /* index of the image's first block among all blocks of the batch */
+	uint64_t out_off;	  /* bytes into the output slab */
+	uint32_t out_cap;	  /* room at out_off */
+	uint32_t hdr_len;	  /* bytes of this image's header in the staging array */
+	float fdtbl_y[64], fdtbl_uv[64]; /* 1 / (quantiser * AAN scale), natural order (jpeg_write.c:227-234) */
+} jcu_enc_image;
+
+/* Encodes n images: pixels -> complete JPEG files in the encoder's device output slab.  `pixels` is a host
+   pointer (copied) or, with pixels_on_device, a device pointer used in place.  huff = code | length << 16 per
+   [Y DC, UV DC, Y AC, UV AC][symbol].  out_len (host, n entries) receives each file's length, 0 = out_cap too
+   small.  kernel_ms (optional) = device time of the kernels alone. */
+JCU_API int jcu_encode(jcu_ctx *c, const jcu_enc_image *imgs, int n, const uint8_t *pixels, size_t pixel_bytes, int pixels_on_device,
+							  const uint8_t *headers, const uint32_t *huff, size_t out_bytes, uint32_t *out_len, float *kernel_ms);
+JCU_API int jcu_encode_fetch(jcu_ctx *c, size_t off, size_t bytes, void *dst); /* synchronous D2H from the output slab */
+JCU_API void *jcu_encode_device_out(jcu_ctx *c);
+
 #ifdef __cplusplus
 }
 #endif

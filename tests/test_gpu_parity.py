@@ -213,6 +213,49 @@ def test_progressive_restartless_scans(oracle, entropy_mode):
     d.close()
 
 
+def test_encoder_matches_reference_writer(oracle):
+    """the GPU encoder must produce the byte stream of the reference's stbi_write_jpg_to_func
+    (jpeg_write.c:368): float AAN DCT without FMA contraction, quantiser tables per quality, 4:2:0 at quality <= 90
+    and 4:4:4 above, edge replication for sizes that are not MCU multiples, 1-4 input components, byte stuffing."""
+    if not oracle.has_writer:
+        pytest.skip("oracle without jpeg_write.c")
+    from tools import testenc as te
+
+    cases = []
+    for (w, h) in ((64, 48), (233, 177), (17, 9), (1, 1), (16, 16), (640, 360), (1920, 1080)):
+        for kind in (0, 1):
+            img = te.synth_rgb(w, h, kind, 100 + w + kind)
+            for q in ((90, 95, 30) if w < 1000 else (90,)):
+                cases.append((f"{w}x{h} kind{kind} q{q} rgb", img, q))
+    rng = np.random.default_rng(3)
+    noise = rng.integers(0, 256, (200, 312, 3), dtype=np.uint8)  # dense noise: long codes, many 0xFF bytes
+    for q in (1, 50, 90, 100, 0):
+        cases.append((f"noise q{q}", noise, q))
+    base = te.synth_rgb(100, 75, 0, 9)
+    cases.append(("grey comp1", np.ascontiguousarray(base[:, :, :1]), 90))
+    cases.append(("grey+alpha comp2", np.ascontiguousarray(base[:, :, :2]), 92))
+    cases.append(("rgba comp4", np.concatenate([base, base[:, :, :1]], axis=2), 75))
+    cases.append(("white", np.full((40, 56, 3), 255, np.uint8), 90))
+    cases.append(("black", np.zeros((33, 47, 3), np.uint8), 100))
+    for q in sorted({c[2] for c in cases}):
+        group = [c for c in cases if c[2] == q]
+        files, ms = ic.encode_batch([c[1] for c in group], q)
+        for (tag, img, _), got in zip(group, files):
+            want = oracle.write_jpg(img, q)
+            assert got is not None, tag
+            assert len(got) == len(want), f"{tag}: {len(got)} bytes, reference {len(want)}"
+            if got != want:
+                first = next(i for i in range(len(want)) if got[i] != want[i])
+                raise AssertionError(f"{tag}: first difference at byte {first} of {len(want)}")
+    # the reference-named entry point, and a round trip through the decoder
+    img = te.synth_rgb(233, 177, 1, 5)
+    data = ic.write_jpg_to_bytes(img, 90)
+    assert data == oracle.write_jpg(img, 90)
+    back, x, y, c = ic.stbi_load_from_memory(data, 3)
+    want, *_ = oracle.load_from_memory(data, 3)
+    assert (x, y, c) == (233, 177, 3) and np.array_equal(back, want)
+
+
 def test_16_bit_and_float_variants(oracle):
     """stbi_load_16* / stbi_loadf* (reference convert.c:213-252, 286-337): the 8-bit decode widened exactly as the
     reference widens its own (v * 257; pow(v / 255, gamma) * scale, alpha linear), with the flip flag and a changed

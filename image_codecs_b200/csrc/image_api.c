@@ -1149,7 +1149,7 @@ API int stbi_jpeg_encode_batch(int device, const stbi_uc *const *pixels, const i
 										 int quality, stbi_uc **outs, int *out_lens, float *kernel_ms)
 {
 	jcu_enc_image *imgs;
-	unsigned char *hdrs, *slab = NULL;
+	unsigned char *hdrs;
 	uint32_t huff[4][256], *lens;
 	size_t pix_bytes = 0, out_bytes = 0, nblocks = 0;
 	int i, nok = 0, rc;
@@ -1210,41 +1210,31 @@ API int stbi_jpeg_encode_batch(int device, const stbi_uc *const *pixels, const i
 		for (i = 0; i < count; ++i)
 			if (imgs[i].nblocks)
 				imgs[i].pix_off = (uint64_t)((uintptr_t)pixels[i] - (uintptr_t)pixels[0]);
-		rc = jcu_encode(ctx, imgs, count, (const uint8_t *)pixels[0], pix_bytes, 1, hdrs, &huff[0][0], out_bytes, lens,
+		rc = jcu_encode(ctx, imgs, count, (const uint8_t *)pixels[0], NULL, pix_bytes, 1, hdrs, &huff[0][0], out_bytes, lens,
 							 kernel_ms);
 	}
 	else
-	{
-		slab = (unsigned char *)jcu_host_alloc(pix_bytes ? pix_bytes : 1);
-		if (!slab)
-		{
-			free(imgs); free(hdrs); free(lens);
-			pthread_mutex_unlock(&g_enc_lock);
-			return err_zero("outofmem");
-		}
-		for (i = 0; i < count; ++i)
-			if (imgs[i].nblocks)
-				memcpy(slab + imgs[i].pix_off, pixels[i], (size_t)xs[i] * (size_t)ys[i] * (size_t)comps[i]);
-		rc = jcu_encode(ctx, imgs, count, slab, pix_bytes, 0, hdrs, &huff[0][0], out_bytes, lens, kernel_ms);
-	}
+		rc = jcu_encode(ctx, imgs, count, NULL, (const uint8_t *const *)pixels, pix_bytes, 0, hdrs, &huff[0][0], out_bytes, lens, kernel_ms);
 	if (rc == 0)
+	{
 		for (i = 0; i < count; ++i)
 			if (imgs[i].nblocks && lens[i])
 			{
 				outs[i] = (stbi_uc *)malloc(lens[i]);
-				if (outs[i] && jcu_encode_fetch(ctx, imgs[i].out_off, lens[i], outs[i]) == 0)
-				{
-					out_lens[i] = (int)lens[i];
-					++nok;
-				}
-				else
+				if (!outs[i] || jcu_encode_fetch(ctx, imgs[i].out_off, lens[i], outs[i]) != 0)
 				{
 					free(outs[i]);
 					outs[i] = NULL;
 				}
 			}
-	if (slab)
-		jcu_host_free(slab);
+		if (jcu_encode_sync(ctx) == 0)
+			for (i = 0; i < count; ++i)
+				if (outs[i])
+				{
+					out_lens[i] = (int)lens[i];
+					++nok;
+				}
+	}
 	free(imgs); free(hdrs); free(lens);
 	pthread_mutex_unlock(&g_enc_lock);
 	return nok;

@@ -685,8 +685,8 @@ extern "C" int jcu_get_timings(jcu_ctx *c, jcu_timings *t)
 }
 
 /* ---- encoder (jpeg_encode.cuh) ---- */
-extern "C" int jcu_encode(jcu_ctx *c, const jcu_enc_image *imgs, int n, const uint8_t *pixels, size_t pixel_bytes, int pixels_on_device,
-								  const uint8_t *headers, const uint32_t *huff, size_t out_bytes, uint32_t *out_len, float *kernel_ms)
+extern "C" int jcu_encode(jcu_ctx *c, const jcu_enc_image *imgs, int n, const uint8_t *pixels, const uint8_t *const *pix_ptrs,
+								  size_t pixel_bytes, int pixels_on_device, const uint8_t *headers, const uint32_t *huff, size_t out_bytes, uint32_t *out_len, float *kernel_ms)
 {
 	CK(cudaSetDevice(c->device));
 	if (n <= 0)
@@ -720,7 +720,10 @@ extern "C" int jcu_encode(jcu_ctx *c, const jcu_enc_image *imgs, int n, const ui
 	CK(ensure(c->enc_hdr, (size_t)n * JCU_ENC_HDR_STRIDE));
 	CK(cudaMemcpyToSymbolAsync(c_enc_huff, huff, sizeof(uint32_t) * 4 * 256, 0, cudaMemcpyHostToDevice, st));
 	if (!pixels_on_device)
-		CK(cudaMemcpyAsync(c->enc_pix.p, pixels, pixel_bytes, cudaMemcpyHostToDevice, st));
+		for (int i = 0; i < n; ++i)
+			if (imgs[i].nblocks && pix_ptrs[i])
+				CK(cudaMemcpyAsync((uint8_t *)c->enc_pix.p + imgs[i].pix_off, pix_ptrs[i],
+										 (size_t)imgs[i].width * imgs[i].height * imgs[i].comp, cudaMemcpyHostToDevice, st));
 	CK(cudaMemcpyAsync(c->enc_img.p, imgs, sizeof(jcu_enc_image) * (size_t)n, cudaMemcpyHostToDevice, st));
 	CK(cudaMemcpyAsync(c->enc_hdr.p, headers, (size_t)n * JCU_ENC_HDR_STRIDE, cudaMemcpyHostToDevice, st));
 	const uint8_t *d_pix = pixels_on_device ? pixels : (const uint8_t *)c->enc_pix.p;
@@ -752,6 +755,12 @@ extern "C" int jcu_encode_fetch(jcu_ctx *c, size_t off, size_t bytes, void *dst)
 {
 	CK(cudaSetDevice(c->device));
 	CK(cudaMemcpyAsync(dst, (const uint8_t *)c->enc_out.p + off, bytes, cudaMemcpyDeviceToHost, c->stream));
+	return 0;
+}
+
+extern "C" int jcu_encode_sync(jcu_ctx *c)
+{
+	CK(cudaSetDevice(c->device));
 	CK(cudaStreamSynchronize(c->stream));
 	return 0;
 }

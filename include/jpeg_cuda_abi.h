@@ -189,13 +189,15 @@ typedef struct
 	float fdtbl_y[64], fdtbl_uv[64]; /* 1 / (quantiser * AAN scale), natural order (jpeg_write.c:227-234) */
 } jcu_enc_image;
 
-/* Encodes n images: pixels -> complete JPEG files in the encoder's device output slab.  `pixels` is a host
-   pointer (copied) or, with pixels_on_device, a device pointer used in place.  huff = code | length << 16 per
+/* Encodes n images: pixels -> complete JPEG files in the encoder's device output slab.  `pixels` is a device
+   pointer used in place (pixels_on_device; pix_off relative to it), else NULL and pix_ptrs[i] are the host
+   pointers of the images, each copied to pix_off of the encoder's own pixel slab.  huff = code | length << 16 per
    [Y DC, UV DC, Y AC, UV AC][symbol].  out_len (host, n entries) receives each file's length, 0 = out_cap too
    small.  kernel_ms (optional) = device time of the kernels alone. */
-JCU_API int jcu_encode(jcu_ctx *c, const jcu_enc_image *imgs, int n, const uint8_t *pixels, size_t pixel_bytes, int pixels_on_device,
-							  const uint8_t *headers, const uint32_t *huff, size_t out_bytes, uint32_t *out_len, float *kernel_ms);
-JCU_API int jcu_encode_fetch(jcu_ctx *c, size_t off, size_t bytes, void *dst); /* synchronous D2H from the output slab */
+JCU_API int jcu_encode(jcu_ctx *c, const jcu_enc_image *imgs, int n, const uint8_t *pixels, const uint8_t *const *pix_ptrs,
+							  size_t pixel_bytes, int pixels_on_device, const uint8_t *headers, const uint32_t *huff, size_t out_bytes, uint32_t *out_len, float *kernel_ms);
+JCU_API int jcu_encode_fetch(jcu_ctx *c, size_t off, size_t bytes, void *dst); /* asynchronous D2H from the output slab */
+JCU_API int jcu_encode_sync(jcu_ctx *c);
 JCU_API void *jcu_encode_device_out(jcu_ctx *c);
 
 #ifdef __cplusplus

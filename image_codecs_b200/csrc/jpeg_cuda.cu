@@ -733,7 +733,18 @@ extern "C" int jcu_encode(jcu_ctx *c, const jcu_enc_image *imgs, int n, const ui
 	CK(cudaMemsetAsync(c->enc_bitbuf.p, 0, nblocks * ENC_BLOCK_BYTES, st));
 	const dim3 gb((max_blocks + ENC_THREADS - 1) / ENC_THREADS, (unsigned)n);
 	const dim3 gc((max_blocks * (ENC_BLOCK_BYTES / ENC_CHUNK) + ENC_THREADS - 1) / ENC_THREADS, (unsigned)n);
-	k_enc_dct<<<gb, ENC_THREADS, 0, st>>>(d_img, d_pix, (int16_t *)c->enc_coef.p);
+	{
+		uint32_t max_tiles = 0, max_generic = 0;
+		for (int i = 0; i < n; ++i)
+			if (imgs[i].subsample)
+				max_tiles = std::max(max_tiles, (uint32_t)(((imgs[i].mcu_x + ENC_TILE_MCUS - 1) / ENC_TILE_MCUS) * imgs[i].mcu_y));
+			else
+				max_generic = std::max(max_generic, (uint32_t)imgs[i].nblocks);
+		if (max_generic)
+			k_enc_dct<<<dim3((max_generic + ENC_THREADS - 1) / ENC_THREADS, (unsigned)n), ENC_THREADS, 0, st>>>(d_img, d_pix, (int16_t *)c->enc_coef.p);
+		if (max_tiles)
+			k_enc_dct420<<<dim3(max_tiles, (unsigned)n), ENC_THREADS, 0, st>>>(d_img, d_pix, (int16_t *)c->enc_coef.p);
+	}
 	k_enc_count<<<gb, ENC_THREADS, 0, st>>>(d_img, (const int16_t *)c->enc_coef.p, (uint32_t *)c->enc_nbits.p);
 	k_enc_scan<<<n, 1024, 0, st>>>(d_img, (const uint32_t *)c->enc_nbits.p, (uint32_t *)c->enc_bitoff.p, d_tot, nullptr, 0);
 	k_enc_emit<<<gb, ENC_THREADS, 0, st>>>(d_img, (const int16_t *)c->enc_coef.p, (const uint32_t *)c->enc_bitoff.p, (uint8_t *)c->enc_bitbuf.p);

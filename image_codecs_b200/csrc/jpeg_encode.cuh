@@ -125,8 +125,8 @@ k_enc_dct(const jcu_enc_image *__restrict__ images, const uint8_t *__restrict__ 
 {
 	const jcu_enc_image &im = images[blockIdx.y];
 	const uint32_t b = blockIdx.x * ENC_THREADS + threadIdx.x;
-	if (b >= (uint32_t)im.nblocks)
-		return;
+	if (b >= (uint32_t)im.nblocks || im.subsample)
+		return; /* 4:2:0 images go to k_enc_dct420 */
 	int which, x0, y0;
 	bool sub;
 	enc_locate(im, b, which, x0, y0, sub);
@@ -160,6 +160,90 @@ k_enc_dct(const jcu_enc_image *__restrict__ images, const uint8_t *__restrict__ 
 	{
 		const float q = EF_M(v[j], fd[j]);
 		out[c_enc_zigzag[j]] = (int16_t)(int)(q < 0 ? EF_S(q, 0.5f) : EF_A(q, 0.5f)); /* jpeg_write.c:117 */
+	}
+}
+
+/*
+ * 4:2:0 files (the reference's choice at quality <= 90): the same arithmetic on a shared-memory tile.  A CTA takes
+ * ENC_TILE_MCUS consecutive MCUs of one MCU row (16 x 256 pixels).  Phase 1: one 2x2 pixel quad per thread step --
+ * neighbouring threads read neighbouring pixels -- converts each source pixel ONCE into Y (four samples) and the
+ * averaged U and V sample (jpeg_write.c:321-323, 337-338).  Phase 2: one thread = one block, in encode order,
+ * DCT + quantise from the tile.  The generic kernel reads every pixel three times with strided byte loads.
+ */
+#define ENC_TILE_MCUS 16
+#define ENC_TILE_W (16 * ENC_TILE_MCUS)
+__global__ void __launch_bounds__(ENC_THREADS)
+k_enc_dct420(const jcu_enc_image *__restrict__ images, const uint8_t *__restrict__ pixels, int16_t *__restrict__ coef)
+{
+	__shared__ float sY[16][ENC_TILE_W + 4];
+	__shared__ float sU[8][ENC_TILE_W / 2 + 2], sV[8][ENC_TILE_W / 2 + 2];
+	const jcu_enc_image &im = images[blockIdx.y];
+	if (!im.subsample)
+		return;
+	const int tiles_x = (im.mcu_x + ENC_TILE_MCUS - 1) / ENC_TILE_MCUS;
+	if ((int)blockIdx.x >= tiles_x * im.mcu_y)
+		return;
+	const int ty = blockIdx.x / tiles_x, tx = blockIdx.x - ty * tiles_x;
+	const int m0 = tx * ENC_TILE_MCUS, nm = min(ENC_TILE_MCUS, im.mcu_x - m0);
+	const int x0 = m0 * 16, y0 = ty * 16;
+	const uint8_t *pix = pixels + im.pix_off;
+	const int ofs_g = im.comp > 2 ? 1 : 0, ofs_b = im.comp > 2 ? 2 : 0;
+	for (int q = threadIdx.x; q < 8 * nm * 8; q += ENC_THREADS)
+	{
+		const int qy = q / (nm * 8), qx = q - qy * (nm * 8);
+		float u[4], v[4];
+#pragma unroll
+		for (int i = 0; i < 4; ++i)
+		{
+			const int row = y0 + 2 * qy + (i >> 1), col = x0 + 2 * qx + (i & 1);
+			const int cr = row < im.height ? row : im.height - 1, cc = col < im.width ? col : im.width - 1;
+			const size_t p = ((size_t)(im.flip ? im.height - 1 - cr : cr) * im.width + cc) * im.comp;
+			const float r = pix[p], g = pix[p + ofs_g], b = pix[p + ofs_b];
+			sY[2 * qy + (i >> 1)][2 * qx + (i & 1)] = EF_S(EF_A(EF_A(EF_M(0.29900f, r), EF_M(0.58700f, g)), EF_M(0.11400f, b)), 128.0f);
+			u[i] = EF_A(EF_S(EF_M(-0.16874f, r), EF_M(0.33126f, g)), EF_M(0.50000f, b));
+			v[i] = EF_S(EF_S(EF_M(0.50000f, r), EF_M(0.41869f, g)), EF_M(0.08131f, b));
+		}
+		sU[qy][qx] = EF_M(EF_A(EF_A(EF_A(u[0], u[1]), u[2]), u[3]), 0.25f);
+		sV[qy][qx] = EF_M(EF_A(EF_A(EF_A(v[0], v[1]), v[2]), v[3]), 0.25f);
+	}
+	__syncthreads();
+	const int t = threadIdx.x;
+	if (t >= nm * 6)
+		return;
+	const int m = t / 6, j = t - m * 6;
+	float d[64];
+	if (j < 4)
+	{
+		const int r0 = (j >> 1) * 8, c0 = m * 16 + (j & 1) * 8;
+#pragma unroll
+		for (int y = 0; y < 8; ++y)
+#pragma unroll
+			for (int x = 0; x < 8; ++x)
+				d[y * 8 + x] = sY[r0 + y][c0 + x];
+	}
+	else
+	{
+		const float(*sC)[ENC_TILE_W / 2 + 2] = j == 4 ? sU : sV;
+#pragma unroll
+		for (int y = 0; y < 8; ++y)
+#pragma unroll
+			for (int x = 0; x < 8; ++x)
+				d[y * 8 + x] = sC[y][m * 8 + x];
+	}
+#pragma unroll
+	for (int y = 0; y < 8; ++y)
+		enc_dct8(d[y * 8], d[y * 8 + 1], d[y * 8 + 2], d[y * 8 + 3], d[y * 8 + 4], d[y * 8 + 5], d[y * 8 + 6], d[y * 8 + 7]);
+#pragma unroll
+	for (int x = 0; x < 8; ++x)
+		enc_dct8(d[x], d[x + 8], d[x + 16], d[x + 24], d[x + 32], d[x + 40], d[x + 48], d[x + 56]);
+	const float *fd = j < 4 ? im.fdtbl_y : im.fdtbl_uv;
+	const uint32_t b = ((uint32_t)ty * (uint32_t)im.mcu_x + (uint32_t)(m0 + m)) * 6u + (uint32_t)j;
+	int16_t *out = coef + ((size_t)im.blk_first + b) * 64;
+#pragma unroll
+	for (int i = 0; i < 64; ++i)
+	{
+		const float q = EF_M(d[i], fd[i]);
+		out[c_enc_zigzag[i]] = (int16_t)(int)(q < 0 ? EF_S(q, 0.5f) : EF_A(q, 0.5f));
 	}
 }
 

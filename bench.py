@@ -139,6 +139,34 @@ def cpu_reference_run(streams, nthreads, target_s, req_comp=3):
     return mps, kind, desc
 
 
+def bind_to_gpu_numa(local_rank):
+    """Pin this rank (and the library threads it will start) to the cores of the NUMA node its GPU hangs off, so
+    that the pinned staging buffers (first touch) and the parser threads sit next to the PCIe root port the
+    copies go through.  Returns a description for the JSON line, or None where the topology is not exposed."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+        bus = pynvml.nvmlDeviceGetPciInfo(h).busId
+        bus = (bus.decode() if isinstance(bus, bytes) else bus).lower()
+        if len(bus.split(":")[0]) == 8:
+            bus = bus[4:]
+        node = int(open(f"/sys/bus/pci/devices/{bus}/numa_node").read())
+        if node < 0:
+            return {"gpu_bus": bus, "node": node, "bound": False}
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return {"gpu_bus": bus, "node": node, "bound": False}
+        os.sched_setaffinity(0, cpus)
+        return {"gpu_bus": bus, "node": node, "bound": True, "cpus": len(cpus)}
+    except Exception as e:  # no sysfs / nvml: stay unbound
+        return {"bound": False, "why": str(e)[:80]}
+
+
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -178,9 +206,13 @@ def main():
 
     if ic.cuda_device_count() < 1:
         raise SystemExit("bench.py: no CUDA device -- this path has no CPU fallback")
+    numa = bind_to_gpu_numa(local_rank) if world > 1 and not os.environ.get("BENCH_NO_NUMA") else None
+    if numa is not None:
+        print(f"[bench] rank {rank}: numa {numa}", file=sys.stderr)
     torch.cuda.set_device(local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # stdout carries the one JSON line only
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
 
     def barrier():
@@ -291,7 +323,7 @@ def main():
         # chunk size of the library's host pipeline (a public tuning parameter): about 3 GB of pixels per chunk
         e2e_chunk = int(min(1024, max(64, 2 ** round(np.log2(3.2e9 / (args.width * args.height * 3))))))
         e_dec = ic.BatchDecoder(device=local_rank, profile=False, chunk_images=int(os.environ.get("BENCH_CHUNK", "0")) or e2e_chunk,
-                                host_threads=max(2, ncores // world))  # ranks share the host cores
+                                host_threads=max(2, min(ncores // world, len(os.sched_getaffinity(0)))))  # ranks share the host cores
         e_dec.decode_into(bufs, lens, n_e, 3, outs, caps, None, None, None, st)  # warm-up (allocations)
         barrier()
         t0 = time.perf_counter()
@@ -325,7 +357,8 @@ def main():
             "config": {"workload": workload_name(args), "distinct_streams": len(distinct),
                        "cache": "inputs larger than L2 (coefficient slab %.1f GB, pixels %.1f GB per GPU)" % (
                            tm["coef_bytes"] / 1e9, tm["out_bytes"] / 1e9),
-                       "req_comp": 3, "parallelism": f"image-sharded x{world}, no collective"},
+                       "req_comp": 3, "parallelism": f"image-sharded x{world}, no collective",
+                       "numa_binding": numa},
             "clocks": clocks,
             "e2e": e2e,
             "gpu_launches": launches,

@@ -82,6 +82,7 @@ struct stbi_jpeg_batch
 	size_t slab_cap, slab_bytes;
 	size_t coef_elems, plane_bytes, out_bytes;
 	int need_clear;
+	int flip; /* stbi_set_flip_vertically_on_load as it stood when the batch was prepared: the kernels store bottom-up */
 
 	stbi_jpeg_batch_timings tm;
 
@@ -304,6 +305,7 @@ static int batch_parse(stbi_jpeg_batch *b, const stbi_uc *const *bufs, const int
 		b->scans = (jcu_scan *)grow_buf(b->scans, &b->cap_scans, ns + 1, sizeof(jcu_scan));
 		b->segs = (uint32_t *)grow_buf(b->segs, &b->cap_segs, ng + 1, sizeof(uint32_t));
 		b->huff = (jcu_huff_spec *)grow_buf(b->huff, &b->cap_huff, nh + 1, sizeof(jcu_huff_spec));
+		b->flip = g_flip_on_load != 0;
 		ns = ng = nh = 0;
 		for (i = 0; i < count; ++i)
 		{
@@ -316,6 +318,7 @@ static int batch_parse(stbi_jpeg_batch *b, const stbi_uc *const *bufs, const int
 				continue;
 			}
 			*im = r->img;
+			im->flip = (uint32_t)b->flip;
 			{
 				int q;
 				for (k = 0; k < 4; ++k)
@@ -511,22 +514,6 @@ static int batch_enqueue_fetch(stbi_jpeg_batch *b, int image, stbi_uc *out, size
 	return jcu_download(b->ctx, im->out_off, n, out) == 0;
 }
 
-static void flip_rows(stbi_uc *px, int w, int h, int n)
-{
-	/* stbi__vertical_flip (convert.c:37) */
-	size_t row = (size_t)w * n;
-	stbi_uc *tmp = (stbi_uc *)malloc(row);
-	int y;
-	for (y = 0; y < h / 2; ++y)
-	{
-		stbi_uc *a = px + row * y, *c = px + row * (size_t)(h - 1 - y);
-		memcpy(tmp, a, row);
-		memcpy(a, c, row);
-		memcpy(c, tmp, row);
-	}
-	free(tmp);
-}
-
 /* enqueue the downloads of images [0, n) of the batch into outs[0..n): neighbours that are contiguous both in
    the device pixel slab and in host memory travel as one copy (up to 64 MB), which takes the per-copy launch
    gaps off the PCIe link (one 6 MB copy per 1080p image otherwise) */
@@ -575,8 +562,6 @@ API int stbi_jpeg_batch_fetch(stbi_jpeg_batch *b, int image, stbi_uc *out, size_
 		return 0;
 	if (b->dev_err[image])
 		return err_zero("bad huffman code");
-	if (g_flip_on_load)
-		flip_rows(out, b->images[image].width, b->images[image].height, b->images[image].n_out);
 	return 1;
 }
 
@@ -590,11 +575,7 @@ API int stbi_jpeg_batch_fetch_all(stbi_jpeg_batch *b, stbi_uc *const *outs, cons
 		return -1;
 	for (i = 0; i < b->count; ++i)
 		if (stbi_jpeg_batch_status(b, i) == STBI_JPEG_OK)
-		{
-			if (g_flip_on_load)
-				flip_rows(outs[i], b->images[i].width, b->images[i].height, b->images[i].n_out);
 			++n;
-		}
 	return n;
 }
 
@@ -695,11 +676,7 @@ API int stbi_jpeg_decode_batch(stbi_jpeg_batch *b, const stbi_uc *const *bufs, c
 								 status ? status + first : NULL);
 				for (i = 0; i < n; ++i)
 					if (stbi_jpeg_batch_status(s, i) == STBI_JPEG_OK)
-					{
-						if (g_flip_on_load)
-							flip_rows(outs[first + i], s->images[i].width, s->images[i].height, s->images[i].n_out);
 						++nok;
-					}
 				acc.parse_ms += s->tm.parse_ms;
 				acc.h2d_ms += s->tm.h2d_ms;
 				acc.entropy_ms += s->tm.entropy_ms;
@@ -749,7 +726,13 @@ API int stbi_jpeg_decode_batch(stbi_jpeg_batch *b, const stbi_uc *const *bufs, c
 static pthread_mutex_t g_default_lock = PTHREAD_MUTEX_INITIALIZER;
 static stbi_jpeg_batch *g_default;
 
-static stbi_uc *load_from_buffer(const stbi_uc *buffer, size_t len, int *x, int *y, int *comp, int req_comp)
+/* 16-bit / float variants: state of the reference's setters, convert.c:402-411 */
+static float g_l2h_gamma = 2.2f, g_l2h_scale = 1.0f;
+enum { WIDE_NONE = 0, WIDE_16 = 1, WIDE_FLOAT = 2 };
+
+/* widen = WIDE_NONE: 8-bit samples; WIDE_16 / WIDE_FLOAT: the widening kernel of jpeg_widen.cuh runs behind the
+   output stage and the wide samples are what crosses the bus */
+static void *load_from_buffer_as(const stbi_uc *buffer, size_t len, int *x, int *y, int *comp, int req_comp, int widen)
 {
 	jp_result probe;
 	stbi_uc *out = NULL;
@@ -782,13 +765,46 @@ static stbi_uc *load_from_buffer(const stbi_uc *buffer, size_t len, int *x, int 
 		{
 			int n = req_comp ? req_comp : cs;
 			size_t bytes = (size_t)n * (size_t)xs * (size_t)ys;
-			out = (stbi_uc *)malloc(bytes + 1); /* +1 as stbi__malloc_mad3(n, x, y, 1), jpeg.c:2293 */
-			if (!out)
-				err_null("outofmem");
-			else if (!stbi_jpeg_batch_fetch(g_default, 0, out, bytes))
+			if (widen == WIDE_NONE)
 			{
-				free(out);
-				out = NULL;
+				out = (stbi_uc *)malloc(bytes + 1); /* +1 as stbi__malloc_mad3(n, x, y, 1), jpeg.c:2293 */
+				if (!out)
+					err_null("outofmem");
+				else if (!stbi_jpeg_batch_fetch(g_default, 0, out, bytes))
+				{
+					free(out);
+					out = NULL;
+				}
+			}
+			else
+			{
+				const int elem = widen == WIDE_16 ? 2 : 4;
+				const int nonalpha = (n & 1) ? n : n - 1; /* common.c:404-407 */
+				float lut[512];
+				int k;
+				if (widen == WIDE_FLOAT)
+					for (k = 0; k < 256; ++k)
+					{
+						/* the reference's per-sample expressions (common.c:412, :417) depend on the byte alone */
+						lut[k] = (float)(pow((unsigned char)k / 255.0f, g_l2h_gamma) * g_l2h_scale);
+						lut[256 + k] = (unsigned char)k / 255.0f;
+					}
+				out = (stbi_uc *)malloc(bytes > 0 ? bytes * (size_t)elem : 1);
+				if (!out)
+					err_null("outofmem");
+				else if (jcu_widen(g_default->ctx, g_default->images[0].out_off, bytes, elem, n, nonalpha, lut) != 0 ||
+							jcu_download_wide(g_default->ctx, bytes * (size_t)elem, out) != 0 || !stbi_jpeg_batch_sync(g_default))
+				{
+					err_null("cuda widen");
+					free(out);
+					out = NULL;
+				}
+				else if (g_default->dev_err[0])
+				{
+					err_null("bad huffman code");
+					free(out);
+					out = NULL;
+				}
 			}
 		}
 		else if (g_default->count == 1 && !g_default->res[0].ok)
@@ -801,6 +817,11 @@ static stbi_uc *load_from_buffer(const stbi_uc *buffer, size_t len, int *x, int 
 	if (y) *y = ys;
 	if (comp) *comp = cs;
 	return out;
+}
+
+static stbi_uc *load_from_buffer(const stbi_uc *buffer, size_t len, int *x, int *y, int *comp, int req_comp)
+{
+	return (stbi_uc *)load_from_buffer_as(buffer, len, x, y, comp, req_comp, WIDE_NONE);
 }
 
 API stbi_uc *stbi_load_from_memory(stbi_uc const *buffer, int len, int *x, int *y, int *comp, int req_comp)
@@ -895,126 +916,87 @@ API stbi_uc *stbi_load(char const *filename, int *x, int *y, int *comp, int req_
 	return r;
 }
 
-/* ---- 16-bit and float variants: the JPEG codec is 8-bit, the reference widens its result on the
- *      host after the (already flipped) 8-bit load -- stbi__load_and_postprocess_16bit convert.c:108-133 with
- *      stbi__convert_8_to_16 :18-35, stbi__loadf_main :286-304 with stbi__ldr_to_hdr common.c:391-424.  Same here:
- *      thin host epilogues behind the GPU decode. ---- */
-static float g_l2h_gamma = 2.2f, g_l2h_scale = 1.0f; /* convert.c:402 */
+/* ---- 16-bit and float variants: the JPEG codec is 8-bit and the reference widens its (already
+ *      flipped) result on the host -- stbi__load_and_postprocess_16bit convert.c:108-133 with stbi__convert_8_to_16
+ *      :18-35, stbi__loadf_main :286-304 with stbi__ldr_to_hdr common.c:391-424.  Here both are store epilogues on
+ *      the device (jpeg_widen.cuh) behind the output kernels, which also apply the flip. ---- */
 static float g_h2l_gamma_i = 1.0f / 2.2f, g_h2l_scale_i = 1.0f; /* convert.c:408; no HDR source format on this path */
 API void stbi_ldr_to_hdr_gamma(float gamma) { g_l2h_gamma = gamma; }
 API void stbi_ldr_to_hdr_scale(float scale) { g_l2h_scale = scale; }
 API void stbi_hdr_to_ldr_gamma(float gamma) { g_h2l_gamma_i = 1 / gamma; }
 API void stbi_hdr_to_ldr_scale(float scale) { g_h2l_scale_i = 1 / scale; }
 
-static stbi_us *widen_16(stbi_uc *data, const int *x, const int *y, const int *comp, int req_comp)
+static void *wide_from_memory(stbi_uc const *buffer, size_t len, int *x, int *y, int *comp, int req_comp, int widen)
 {
-	size_t n, i;
-	stbi_us *out;
-	if (!data)
-		return NULL;
-	n = (size_t)*x * (size_t)*y * (size_t)(req_comp ? req_comp : *comp);
-	out = (stbi_us *)malloc(n > 0 ? n * 2 : 1);
-	if (!out)
-	{
-		free(data);
-		return (stbi_us *)err_null("outofmem");
-	}
-	for (i = 0; i < n; ++i)
-		out[i] = (stbi_us)((data[i] << 8) + data[i]); /* 0 -> 0, 255 -> 0xffff (convert.c:30) */
-	free(data);
-	return out;
+	void *r = load_from_buffer_as(buffer, len, x, y, comp, req_comp, widen);
+	if (!r && widen == WIDE_FLOAT)
+		err_null("unknown image type"); /* stbi__loadf_main replaces the codec's reason, convert.c:303 */
+	return r;
 }
-
-static float *widen_float(stbi_uc *data, const int *x, const int *y, const int *comp, int req_comp)
+static void *wide_from_callbacks(stbi_io_callbacks const *clbk, void *user, int *x, int *y, int *comp, int req_comp, int widen)
 {
-	size_t px, i;
-	int c, k, n;
-	float *out, lut[256];
-	if (!data)
-		return (float *)err_null("unknown image type"); /* stbi__loadf_main replaces the codec's reason, convert.c:303 */
-	c = req_comp ? req_comp : *comp;
-	px = (size_t)*x * (size_t)*y;
-	out = (float *)malloc(px > 0 ? px * (size_t)c * sizeof(float) : 1);
-	if (!out)
-	{
-		free(data);
-		return (float *)err_null("outofmem");
-	}
-	n = (c & 1) ? c : c - 1; /* non-alpha components (common.c:404-407) */
-	for (k = 0; k < 256; ++k) /* the reference's per-sample expression (common.c:412) depends on the byte alone */
-		lut[k] = (float)(pow((unsigned char)k / 255.0f, g_l2h_gamma) * g_l2h_scale);
-	for (i = 0; i < px; ++i)
-	{
-		for (k = 0; k < n; ++k)
-			out[i * (size_t)c + (size_t)k] = lut[data[i * (size_t)c + (size_t)k]];
-		if (n < c)
-			out[i * (size_t)c + (size_t)n] = data[i * (size_t)c + (size_t)n] / 255.0f;
-	}
-	free(data);
-	return out;
+	size_t len = 0;
+	stbi_uc *buf = drain_callbacks(clbk, user, &len);
+	void *r;
+	if (!buf)
+		return err_null("outofmem");
+	r = wide_from_memory(buf, len, x, y, comp, req_comp, widen);
+	free(buf);
+	return r;
+}
+static void *wide_from_file(FILE *f, int *x, int *y, int *comp, int req_comp, int widen)
+{
+	size_t len = 0;
+	stbi_uc *buf = drain_file(f, &len);
+	void *r;
+	if (!buf)
+		return err_null("outofmem");
+	r = wide_from_memory(buf, len, x, y, comp, req_comp, widen);
+	free(buf);
+	return r;
+}
+static void *wide_from_path(char const *filename, int *x, int *y, int *comp, int req_comp, int widen)
+{
+	FILE *f = fopen(filename, "rb");
+	void *r;
+	if (!f)
+		return err_null("can't fopen");
+	r = wide_from_file(f, x, y, comp, req_comp, widen);
+	fclose(f);
+	return r;
 }
 
 API stbi_us *stbi_load_16_from_memory(stbi_uc const *buffer, int len, int *x, int *y, int *comp, int req_comp)
 {
-	int xx, yy, cc;
-	stbi_uc *d = stbi_load_from_memory(buffer, len, &xx, &yy, &cc, req_comp);
-	if (d) { if (x) *x = xx; if (y) *y = yy; if (comp) *comp = cc; }
-	return widen_16(d, &xx, &yy, &cc, req_comp);
+	return (stbi_us *)wide_from_memory(buffer, len > 0 ? (size_t)len : 0, x, y, comp, req_comp, WIDE_16);
 }
 API stbi_us *stbi_load_16_from_callbacks(stbi_io_callbacks const *clbk, void *user, int *x, int *y, int *comp, int req_comp)
 {
-	int xx, yy, cc;
-	stbi_uc *d = stbi_load_from_callbacks(clbk, user, &xx, &yy, &cc, req_comp);
-	if (d) { if (x) *x = xx; if (y) *y = yy; if (comp) *comp = cc; }
-	return widen_16(d, &xx, &yy, &cc, req_comp);
+	return (stbi_us *)wide_from_callbacks(clbk, user, x, y, comp, req_comp, WIDE_16);
 }
 API stbi_us *stbi_load_from_file_16(FILE *f, int *x, int *y, int *comp, int req_comp)
 {
-	int xx, yy, cc;
-	stbi_uc *d = stbi_load_from_file(f, &xx, &yy, &cc, req_comp);
-	if (d) { if (x) *x = xx; if (y) *y = yy; if (comp) *comp = cc; }
-	return widen_16(d, &xx, &yy, &cc, req_comp);
+	return (stbi_us *)wide_from_file(f, x, y, comp, req_comp, WIDE_16);
 }
 API stbi_us *stbi_load_16(char const *filename, int *x, int *y, int *comp, int req_comp)
 {
-	FILE *f = fopen(filename, "rb");
-	stbi_us *r;
-	if (!f)
-		return (stbi_us *)err_null("can't fopen");
-	r = stbi_load_from_file_16(f, x, y, comp, req_comp);
-	fclose(f);
-	return r;
+	return (stbi_us *)wide_from_path(filename, x, y, comp, req_comp, WIDE_16);
 }
 API float *stbi_loadf_from_memory(stbi_uc const *buffer, int len, int *x, int *y, int *comp, int req_comp)
 {
-	int xx, yy, cc;
-	stbi_uc *d = stbi_load_from_memory(buffer, len, &xx, &yy, &cc, req_comp);
-	if (d) { if (x) *x = xx; if (y) *y = yy; if (comp) *comp = cc; }
-	return widen_float(d, &xx, &yy, &cc, req_comp);
+	return (float *)wide_from_memory(buffer, len > 0 ? (size_t)len : 0, x, y, comp, req_comp, WIDE_FLOAT);
 }
 API float *stbi_loadf_from_callbacks(stbi_io_callbacks const *clbk, void *user, int *x, int *y, int *comp, int req_comp)
 {
-	int xx, yy, cc;
-	stbi_uc *d = stbi_load_from_callbacks(clbk, user, &xx, &yy, &cc, req_comp);
-	if (d) { if (x) *x = xx; if (y) *y = yy; if (comp) *comp = cc; }
-	return widen_float(d, &xx, &yy, &cc, req_comp);
+	return (float *)wide_from_callbacks(clbk, user, x, y, comp, req_comp, WIDE_FLOAT);
 }
 API float *stbi_loadf_from_file(FILE *f, int *x, int *y, int *comp, int req_comp)
 {
-	int xx, yy, cc;
-	stbi_uc *d = stbi_load_from_file(f, &xx, &yy, &cc, req_comp);
-	if (d) { if (x) *x = xx; if (y) *y = yy; if (comp) *comp = cc; }
-	return widen_float(d, &xx, &yy, &cc, req_comp);
+	return (float *)wide_from_file(f, x, y, comp, req_comp, WIDE_FLOAT);
 }
 API float *stbi_loadf(char const *filename, int *x, int *y, int *comp, int req_comp)
 {
-	FILE *f = fopen(filename, "rb");
-	float *r;
-	if (!f)
-		return (float *)err_null("can't fopen");
-	r = stbi_loadf_from_file(f, x, y, comp, req_comp);
-	fclose(f);
-	return r;
+	return (float *)wide_from_path(filename, x, y, comp, req_comp, WIDE_FLOAT);
 }
 /* a JPEG is neither HDR nor 16-bit (convert.c:345-400, image_api.c:96-145) */
 API int stbi_is_hdr_from_memory(stbi_uc const *buffer, int len) { (void)buffer; (void)len; return 0; }

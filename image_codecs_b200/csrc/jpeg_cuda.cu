@@ -18,6 +18,7 @@
 #include "jpeg_selfsync.cuh"
 #include "jpeg_entropy_prog.cuh"
 #include "jpeg_encode.cuh"
+#include "jpeg_widen.cuh"
 #include "jpeg_output.cuh"
 #include "jpeg_fused420.cuh"
 #include "jpeg_fused1x1.cuh"
@@ -48,6 +49,7 @@ struct jcu_ctx
 	bool d2h_open = false;
 	DevBuf bits, images, scans, segs, huff, work, coef, planes, out, err, lists;
 	DevBuf ss_work, ss_scans, ss_exit_a, ss_exit_b, ss_entry, ss_nblk, ss_first, ss_changed;
+	DevBuf wide, wide_lut; /* 16-bit / float copy of one image and its look-up table (jpeg_widen.cuh) */
 	DevBuf uslab, useg_len; /* unstuffed copy of the baseline segments (jpeg_entropy_baseline.cuh) */
 	DevBuf enc_pix, enc_img, enc_coef, enc_nbits, enc_bitoff, enc_tot, enc_bitbuf, enc_ffcnt, enc_ffoff, enc_out, enc_len, enc_hdr; /* encoder */
 	cudaEvent_t ev_enc0 = nullptr, ev_enc1 = nullptr;
@@ -181,7 +183,7 @@ extern "C" void jcu_ctx_destroy(jcu_ctx *c)
 	cudaStreamSynchronize(c->stream);
 	DevBuf *bufs[] = {&c->bits, &c->images, &c->scans, &c->segs, &c->huff, &c->work, &c->coef, &c->planes, &c->out, &c->err, &c->lists,
 							&c->ss_work, &c->ss_scans, &c->ss_exit_a, &c->ss_exit_b, &c->ss_entry, &c->ss_nblk, &c->ss_first, &c->ss_changed, &c->uslab, &c->useg_len,
-							&c->enc_pix, &c->enc_img, &c->enc_coef, &c->enc_nbits, &c->enc_bitoff, &c->enc_tot, &c->enc_bitbuf, &c->enc_ffcnt, &c->enc_ffoff, &c->enc_out, &c->enc_len, &c->enc_hdr};
+							&c->enc_pix, &c->enc_img, &c->enc_coef, &c->enc_nbits, &c->enc_bitoff, &c->enc_tot, &c->enc_bitbuf, &c->enc_ffcnt, &c->enc_ffoff, &c->enc_out, &c->enc_len, &c->enc_hdr, &c->wide, &c->wide_lut};
 	for (auto b : bufs)
 		if (b->p)
 			cudaFree(b->p);
@@ -654,6 +656,39 @@ extern "C" int jcu_download(jcu_ctx *c, size_t off, size_t bytes, void *dst)
 	CK(cudaMemcpyAsync(dst, (const uint8_t *)c->out.p + off, bytes, cudaMemcpyDeviceToHost, c->dl_use));
 	return 0;
 }
+
+/* ---- widening epilogues (jpeg_widen.cuh) ---- */
+extern "C" int jcu_widen(jcu_ctx *c, size_t off, size_t count, int elem_bytes, int comp, int nonalpha, const float *lut512)
+{
+	CK(cudaSetDevice(c->device));
+	if ((elem_bytes != 2 && elem_bytes != 4) || comp < 1 || (off & 15) || off + count > c->out.cap)
+		return set_err(c, cudaErrorInvalidValue, "jcu_widen: bad arguments");
+	CK(ensure(c->wide, count * (size_t)elem_bytes + 256));
+	if (count == 0)
+		return 0;
+	const unsigned grid = (unsigned)((count + (size_t)WIDEN_THREADS * WIDEN_PER_THREAD - 1) / ((size_t)WIDEN_THREADS * WIDEN_PER_THREAD));
+	if (elem_bytes == 2)
+		k_widen16<<<grid, WIDEN_THREADS, 0, c->stream>>>((const uint8_t *)c->out.p + off, (uint16_t *)c->wide.p, count);
+	else
+	{
+		CK(ensure(c->wide_lut, 512 * sizeof(float)));
+		CK(cudaMemcpyAsync(c->wide_lut.p, lut512, 512 * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+		k_widenf<<<grid, WIDEN_THREADS, 0, c->stream>>>((const uint8_t *)c->out.p + off, (float *)c->wide.p, count, comp, nonalpha,
+																		(const float *)c->wide_lut.p);
+	}
+	++c->launches;
+	CK(cudaGetLastError());
+	return 0;
+}
+
+extern "C" int jcu_download_wide(jcu_ctx *c, size_t bytes, void *dst)
+{
+	CK(cudaSetDevice(c->device));
+	CK(cudaMemcpyAsync(dst, c->wide.p, bytes, cudaMemcpyDeviceToHost, c->stream)); /* same stream as the kernel; jcu_sync waits */
+	return 0;
+}
+
+extern "C" void *jcu_device_wide(jcu_ctx *c) { return c->wide.p; }
 
 extern "C" int jcu_image_errors(jcu_ctx *c, int32_t *errs, int n)
 {

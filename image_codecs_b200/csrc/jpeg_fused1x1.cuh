@@ -102,7 +102,8 @@ k_fused1x1_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 
 	const bool vec_ok = (W & 7) == 0; /* every row starts 8-byte aligned for N = 1, 3; N = 2, 4 need less */
 	const int G = nb;						 /* 8-pixel groups per row of the strip */
-	uint8_t *obase = out + im->out_off;
+	const int pitch = im->flip ? -W * N : W * N; /* flip on load as a store epilogue, as in jpeg_fused420.cuh */
+	uint8_t *obase = out + im->out_off + (im->flip ? (size_t)(im->height - 1) * (size_t)(W * N) : 0);
 
 #pragma unroll 1
 	for (int by = by0; by < by1; ++by)
@@ -135,7 +136,7 @@ k_fused1x1_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 				continue;
 			const int count = min(8, W - gx0);
 			const bool whole = vec_ok && count == 8;
-			uint8_t *o = obase + ((size_t)gy * W + gx0) * N;
+			uint8_t *o = obase + (long long)gy * pitch + gx0 * N;
 			const uint2 yv = *reinterpret_cast<const uint2 *>(sS + ly * (BS * 8) + g * 8);
 			if (NC == 3)
 			{

@@ -273,7 +273,10 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 
 	const bool vec_ok = (N == 4) ? ((W & 3) == 0) : ((W & 7) == 0);
 	const bool full_w = vec_ok && (m0 + Ms) * 16 <= W; /* CTA-uniform: every 8-pixel group of the strip is whole */
-	uint8_t *obase = out + im->out_off;
+	/* vertical flip on load (stbi__vertical_flip convert.c:37) is a store epilogue: the row pitch
+	   turns negative and the base moves to the last row */
+	const int pitch = im->flip ? -W * N : W * N;
+	uint8_t *obase = out + im->out_off + (im->flip ? (size_t)(H - 1) * (size_t)(W * N) : 0);
 	const int G = 2 * Ms; /* 8-pixel groups per row of the strip */
 	const int ly_first = tid / G, g_first = tid - ly_first * G;
 	const int dly = S420_THREADS / G, dg = S420_THREADS - dly * G;
@@ -366,7 +369,7 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 		/* ---- pixel phase: MCU row r, one task = 8 pixels of one row ---- */
 		if (doY)
 		{
-			uint8_t *orow0 = obase + ((size_t)r * 16 * W + (size_t)m0 * 16) * N;
+			uint8_t *orow0 = obase + (long long)(r * 16) * pitch + m0 * 16 * N;
 			int ly = ly_first, g = g_first;
 #pragma unroll 1
 			while (ly < 16)
@@ -397,7 +400,7 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 					s420_colour<1>(3u * t[3] + t[4], yv.y, R[5], Gc[5], B[5]);
 					s420_colour<2>(3u * t[4] + t[3], yv.y, R[6], Gc[6], B[6]);
 					s420_colour<3>(3u * t[4] + t[5], yv.y, R[7], Gc[7], B[7]);
-					uint8_t *o = orow0 + (unsigned)(ly * W + g * 8) * N;
+					uint8_t *o = orow0 + (ly * pitch + g * 8 * N);
 					if (full_w || (vec_ok && gx0 + 8 <= W))
 					{
 						if (N == 3)

@@ -230,7 +230,7 @@ k_generic_color(const int32_t *__restrict__ list, const jcu_image *__restrict__ 
 				break;
 			s[k] = generic_sample(&im->comp[k], planes + im->comp[k].plane_off, x, y);
 		}
-		uint8_t *o = out + im->out_off + (size_t)p * n;
+		uint8_t *o = out + im->out_off + ((size_t)(im->flip ? H - 1 - y : y) * W + x) * n; /* flip on load: convert.c:37 */
 		int r, g, b;
 		switch (mode)
 		{

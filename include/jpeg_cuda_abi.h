@@ -92,7 +92,7 @@ typedef struct
 	uint64_t out_off;	  /* byte offset of the packed output in the pixel slab */
 	uint64_t data_off;  /* byte offset of the file in the bitstream slab (16-byte aligned) */
 	uint32_t data_len;
-	uint32_t pad2;
+	uint32_t flip; /* 1 = store the rows bottom-up (stbi_set_flip_vertically_on_load, convert.c:97-101) */
 } jcu_image;
 
 typedef struct
@@ -163,6 +163,15 @@ JCU_API int jcu_download(jcu_ctx *c, size_t off, size_t bytes, void *dst);	  /* 
 JCU_API int jcu_image_errors(jcu_ctx *c, int32_t *errs, int n);					  /* per-image device error flags (after sync) */
 JCU_API void *jcu_device_out(jcu_ctx *c);
 JCU_API int jcu_get_timings(jcu_ctx *c, jcu_timings *t);
+
+/* Widening epilogues: `count` samples of the pixel slab starting at byte `off` (16-byte aligned) become
+   16-bit (elem_bytes 2: v * 257, stbi__convert_8_to_16 codec/convert.c:18-35) or float (elem_bytes 4: lut512[v] for
+   the first `nonalpha` of every `comp` interleaved channels, lut512[256 + v] for the alpha channel, stbi__ldr_to_hdr
+   codec/common.c:391-424) in the context's wide buffer; asynchronous on the ctx stream.  The pageable host table is
+   read before the call returns. */
+JCU_API int jcu_widen(jcu_ctx *c, size_t off, size_t count, int elem_bytes, int comp, int nonalpha, const float *lut512);
+JCU_API int jcu_download_wide(jcu_ctx *c, size_t bytes, void *dst); /* async D2H of the wide buffer; jcu_sync waits */
+JCU_API void *jcu_device_wide(jcu_ctx *c);
 
 /* stage-level entry points for the parity tests (host pointers in, host pointers out) */
 JCU_API int jcu_test_idct_blocks(jcu_ctx *c, const int16_t *coef, const uint16_t *qt, int nblocks, uint8_t *out64);

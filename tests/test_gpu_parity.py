@@ -256,6 +256,39 @@ def test_encoder_matches_reference_writer(oracle):
     assert (x, y, c) == (233, 177, 3) and np.array_equal(back, want)
 
 
+def test_flip_on_load_is_a_store_epilogue(oracle):
+    """stbi_set_flip_vertically_on_load (reference convert.c:37-61, 97-101): the output kernels store bottom-up, so
+    the batched calls -- host buffers and device-resident results alike -- return flipped rows without a host pass."""
+    cases = [("420", 233, 177), ("420", 64, 16), ("444", 129, 65), ("gray", 31, 9), ("440", 50, 37), ("ycck", 48, 33),
+             ("420_prog", 100, 71)]
+    datas = [S.stream(f, w, h, i % 3) for i, (f, w, h) in enumerate(cases)]
+    try:
+        ic.set_flip_vertically_on_load(True)
+        d = ic.BatchDecoder(device=0)
+        for rc in (0, 1, 3, 4):
+            outs = d.decode(datas, rc)
+            for (f, w, h), s_, o in zip(cases, datas, outs):
+                want, *_ = oracle.load_from_memory(s_, rc)
+                assert o is not None and np.array_equal(o, want[::-1]), f"{f} {w}x{h} req_comp {rc}"
+        # device-resident result: read the pixel slab where the kernels left it
+        import torch
+
+        d.prepare(datas, 3)
+        d.run()
+        d.sync()
+        for i, s_ in enumerate(datas):
+            ptr, nbytes = d.device_pixels(i)
+            want, *_ = oracle.load_from_memory(s_, 3)
+            assert nbytes == want.size
+            view = type("DevView", (), {"__cuda_array_interface__": {
+                "shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}})()
+            host = torch.as_tensor(view, device="cuda:0").cpu().numpy()
+            assert np.array_equal(host.reshape(want.shape), want[::-1]), cases[i]
+        d.close()
+    finally:
+        ic.set_flip_vertically_on_load(False)
+
+
 def test_16_bit_and_float_variants(oracle):
     """stbi_load_16* / stbi_loadf* (reference convert.c:213-252, 286-337): the 8-bit decode widened exactly as the
     reference widens its own (v * 257; pow(v / 255, gamma) * scale, alpha linear), with the flip flag and a changed
@@ -292,7 +325,9 @@ def test_16_bit_and_float_variants(oracle):
         L.stbi_image_free(p)
         return out, (x.value, y.value, c.value)
 
-    streams = [S.stream("420", 233, 177, 1), S.stream("gray", 64, 48, 0), S.stream("444_prog_ss", 129, 65, 2)]
+    # fused 4:2:0, fused 1x1 (1 and 3 components) and the generic two-pass output path (4:2:2, CMYK)
+    streams = [S.stream("420", 233, 177, 1), S.stream("gray", 64, 48, 0), S.stream("444_prog_ss", 129, 65, 2),
+               S.stream("422", 75, 53, 1), S.stream("cmyk", 40, 31, 0)]
     for flip in (0, 1):
         ic.set_flip_vertically_on_load(bool(flip))
         if ref is not None:

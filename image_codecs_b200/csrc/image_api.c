@@ -99,6 +99,13 @@ static int online_cpus(void)
 	return (int)n;
 }
 
+/* failure word of the device decoders -> the reference's string */
+static const char *dev_reason(int word)
+{
+	return JCU_ERR_CODE(word) == JCU_ERR_UNKNOWN_MARKER ? "unknown marker" /* jpeg.c:1469 */
+																		 : "bad huffman code"; /* jpeg.c:317,351,444,499,521 */
+}
+
 API int stbi_jpeg_cuda_device_count(void) { return jcu_device_count(); }
 
 API stbi_jpeg_batch *stbi_jpeg_batch_create(const stbi_jpeg_batch_params *params)
@@ -483,7 +490,7 @@ API const char *stbi_jpeg_batch_reason(stbi_jpeg_batch *b, int image)
 	if (!b->res[image].ok)
 		return b->res[image].reason ? b->res[image].reason : "corrupt jpeg";
 	if (b->dev_err_valid && b->dev_err[image])
-		return "bad huffman code"; /* jpeg.c:317,351,444,499,521 */
+		return dev_reason(b->dev_err[image]);
 	return NULL;
 }
 
@@ -561,7 +568,7 @@ API int stbi_jpeg_batch_fetch(stbi_jpeg_batch *b, int image, stbi_uc *out, size_
 	if (!stbi_jpeg_batch_sync(b))
 		return 0;
 	if (b->dev_err[image])
-		return err_zero("bad huffman code");
+		return err_zero(dev_reason(b->dev_err[image]));
 	return 1;
 }
 
@@ -801,7 +808,7 @@ static void *load_from_buffer_as(const stbi_uc *buffer, size_t len, int *x, int 
 				}
 				else if (g_default->dev_err[0])
 				{
-					err_null("bad huffman code");
+					err_null(dev_reason(g_default->dev_err[0]));
 					free(out);
 					out = NULL;
 				}

@@ -113,6 +113,81 @@ __device__ __forceinline__ void hufflut_build(HuffLut *L, const jcu_huff_spec *s
 }
 
 /* MSB-first bit reader over one restart segment */
+/* ---- per-image failure word.  The reference stops at the first failing event in file order, so the word keeps
+ * the smallest key (scan ordinal, restart segment, code); it is stored complemented so that 0 = no failure and
+ * atomicMax keeps the earliest event (JCU_ERR_CODE in jpeg_cuda_abi.h reads the code back). ---- */
+__device__ __forceinline__ void report_failure(int32_t *img_err, const jcu_scan *sc, uint32_t seg, uint32_t code)
+{
+	const uint32_t key = (((min((uint32_t)sc->wave, 1023u) << 20) | min(seg, 0xfffffu)) << 2) | code;
+	atomicMax(reinterpret_cast<unsigned int *>(&img_err[sc->image]), ~key);
+}
+
+/*
+ * "Left-over bytes" rule.  The reference leaves a restart interval through
+ *     if (code_bits < 24) grow_buffer(); if (!RESTART(marker)) return 1;        (jpeg.c:1180-1189, 1223-1230, ...)
+ * and after a scan looks for the next marker by skipping to the next 0xFF byte and taking the byte behind it
+ * (jpeg.c:1722-1735).  A segment of a damaged stream that is decoded before its bytes are used up therefore
+ * (a) ends the scan if it is not the last one -- the RSTn marker, or a stuffed FF 00 before it, is then taken
+ * for the next marker segment: "unknown marker" -- and (b) if it is the last one, fails the same way when the
+ * unread bytes contain a stuffed 0xFF.  grow_buffer fills to 25..32 bits, so with R real bits left behind the
+ * end position the marker has been seen iff R <= 24 (R == 24 with exactly 24 bits buffered is the one case
+ * that depends on the refill history; it is taken as seen), and the reader has consumed 24 + (R % 8 ? R % 8 : 8)
+ * bits beyond the end position.  That is exact wherever the interval ends with the refill above (`at_restart`:
+ * every segment but the last, and the last one too when the scan's units are a multiple of the interval).  A
+ * scan that simply runs out of units ends without it: the bits the reference then holds (R % 8 plus 0, 8, 16
+ * or 24) depend on where its last refill happened, i.e. on the whole history of the segment, which a parallel
+ * decoder does not have; the middle value is assumed, so a stuffed 0xFF within two bytes of that point can be
+ * judged differently.
+ */
+__device__ __forceinline__ int leftover_ahead_bits(int R, bool at_restart)
+{
+	return (at_restart ? 24 : 16) + ((R & 7) ? (R & 7) : 8);
+}
+
+/* next raw byte of a segment with the stuffing resolved; false at the marker that ends it (or the end of the file) */
+__device__ __forceinline__ bool raw_next_unstuffed(const uint8_t *&q, const uint8_t *end, uint32_t &b)
+{
+	if (q >= end)
+		return false;
+	b = *q++;
+	if (b == 0xff)
+	{
+		const uint8_t *r = q;
+		uint32_t c = r < end ? *r : 0u;
+		while (c == 0xff)
+		{
+			++r;
+			c = r < end ? *r : 0u;
+		}
+		if (c != 0)
+			return false;
+		q = r < end ? r + 1 : end;
+	}
+	return true;
+}
+
+/* serial form of the rule for a decoder that only knows where it stopped: pos = unstuffed bits consumed since
+   seg_begin.  With i0 = ceil((pos + 25) / 8) -- the first byte the reference has not consumed -- and L unstuffed
+   bytes in the segment: nothing happens when L < i0; otherwise a segment that is not the last trips, and the last
+   one trips iff a byte in [i0, L) is 0xFF (i0 one byte earlier when the scan does not end at a restart boundary,
+   see above).  O(segment) for one thread: callers run it only when L >= i0. */
+__device__ __noinline__ bool leftover_trips_serial(const uint8_t *seg_begin, const uint8_t *file_end, long long pos, bool last_segment,
+																	bool at_restart)
+{
+	const long long i0 = ((pos + 25 + 7) >> 3) - ((last_segment && !at_restart) ? 1 : 0);
+	const uint8_t *q = seg_begin;
+	uint32_t b;
+	for (long long i = 0; i < i0; ++i)
+		if (!raw_next_unstuffed(q, file_end, b))
+			return false;
+	if (!last_segment)
+		return true;
+	while (raw_next_unstuffed(q, file_end, b))
+		if (b == 0xffu)
+			return true;
+	return false;
+}
+
 struct BitReader
 {
 	const uint8_t *p;
@@ -120,6 +195,7 @@ struct BitReader
 	uint64_t buf; /* valid bits are the top nbits */
 	int nbits;
 	int stopped; /* a marker was reached: feed zero bits from now on (jpeg.c:171-183) */
+	int pad;		 /* zero bits appended behind the stream so far (they sit at the bottom of the valid bits) */
 };
 
 __device__ __forceinline__ void br_init(BitReader &br, const uint8_t *p, const uint8_t *end)
@@ -129,6 +205,7 @@ __device__ __forceinline__ void br_init(BitReader &br, const uint8_t *p, const u
 	br.buf = 0;
 	br.nbits = 0;
 	br.stopped = 0;
+	br.pad = 0;
 }
 
 /* one byte with the reference's stuffing rules: FF 00 -> FF, FF FF.. fill, FF xx -> stop */
@@ -137,8 +214,10 @@ __device__ __noinline__ void br_refill_slow(BitReader &br)
 	do
 	{
 		uint32_t b = 0;
+		bool real = false;
 		if (!br.stopped && br.p < br.end)
 		{
+			real = true;
 			b = *br.p++;
 			if (b == 0xff)
 			{
@@ -155,9 +234,12 @@ __device__ __noinline__ void br_refill_slow(BitReader &br)
 				{
 					br.stopped = 1;
 					b = 0;
+					real = false;
 				}
 			}
 		}
+		if (!real)
+			br.pad += 8;
 		br.buf |= (uint64_t)b << (56 - br.nbits);
 		br.nbits += 8;
 	} while (br.nbits <= 56 && (br.stopped || br.p >= br.end || ((uintptr_t)br.p & 3) != 0));
@@ -182,6 +264,41 @@ __device__ __forceinline__ void br_refill(BitReader &br)
 		}
 		br_refill_slow(br);
 	}
+}
+
+/* the left-over rule (above) for a segment that this reader has just finished; true = the reference fails here */
+__device__ __noinline__ bool br_reference_trips(const BitReader &br, bool last_segment, bool at_restart)
+{
+	const int real = br.nbits - br.pad; /* stream bits still buffered */
+	const uint8_t *q = br.p;
+	uint32_t b;
+	int R = real;
+	bool more = !br.stopped;
+	while (more && R < 25)
+	{
+		more = raw_next_unstuffed(q, br.end, b);
+		if (more)
+			R += 8;
+	}
+	if (R < 25)
+		return false;
+	if (!last_segment)
+		return true;
+	/* last segment: is there a (stuffed) 0xFF in what the reference has not consumed? */
+	const int a = leftover_ahead_bits(real, at_restart);
+	for (int o = a; o + 8 <= real; o += 8)
+		if (((br.buf >> (56 - o)) & 0xffu) == 0xffu)
+			return true;
+	if (br.stopped)
+		return false;
+	q = br.p;
+	for (int skip = a - real; skip > 0; skip -= 8)
+		if (!raw_next_unstuffed(q, br.end, b))
+			return false;
+	while (raw_next_unstuffed(q, br.end, b))
+		if (b == 0xffu)
+			return true;
+	return false;
 }
 
 __device__ __forceinline__ uint32_t br_peek(const BitReader &br, int n) /* 1 <= n <= 32 */
@@ -518,5 +635,7 @@ k_entropy_segments(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 		}
 	}
 	if (failed)
-		atomicOr(&img_err[sc->image], 1);
+		report_failure(img_err, sc, seg, JCU_ERR_BAD_HUFFMAN);
+	else if (active && u0 < total && br_reference_trips(br, seg + 1 >= sc->nseg, ri > 0 && total % ri == 0))
+		report_failure(img_err, sc, seg, JCU_ERR_UNKNOWN_MARKER);
 }

@@ -228,7 +228,7 @@ __device__ __forceinline__ void entb_setup(EntbSharedT<ND, NA> &sh, const jcu_sc
  * followed by one all-zero 16-byte unit (the source of every fetch past the end).  Raw segments are at least
  * 2 bytes apart (the RSTn marker) and never grow, so in 16-byte units the area of segment g holds
  * ceil(s'/16) - ceil(s/16) + 2 >= ceil(raw/16) + 1 units: the areas cannot overlap; the slab needs
- * bitstream_bytes + 32 * (n_segs + 2) bytes.  useg_len[g] = bytes produced, rounded up to 16.
+ * bitstream_bytes + 32 * (n_segs + 2) bytes.  useg_len[g] = bytes produced, rounded up to 16, + the padding bytes (0..15) in the low 4 bits.
  * ------------------------------------------------------------------------------------------------------ */
 __device__ __forceinline__ size_t entb_useg_off(uint64_t data_off, uint32_t seg_start, uint32_t g)
 {
@@ -323,12 +323,13 @@ k_unstuff(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans, 
 	}
 	if (!active)
 		return;
+	const uint32_t exact = o.words * 4u + o.nacc; /* bytes of the segment once the stuffing is gone */
 	if (o.nacc)
 		unstuff_put(o, o.pend);
 	while (o.words & 3u)
 		unstuff_put(o, 0u);
 	*reinterpret_cast<uint4 *>(o.wp) = make_uint4(0u, 0u, 0u, 0u);
-	useg_len[g] = o.words * 4u;
+	useg_len[g] = o.words * 4u + (o.words * 4u - exact); /* padded length (multiple of 16) + padding bytes in the low 4 bits */
 }
 
 /* ------------------------------------------------------------------------------------------------------
@@ -508,7 +509,7 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 	if (active)
 	{
 		const uint32_t g = (uint32_t)sc->seg_first + seg;
-		br.nwords = useg_len[g] >> 2;
+		br.nwords = (useg_len[g] & ~15u) >> 2;
 		br.src = reinterpret_cast<const uint32_t *>(uslab + entb_useg_off(im->data_off, seg_start[g], g));
 	}
 	ebr_checkpoint<ENTB_RING_WORDS / 4, false>(ring_lane, br);
@@ -636,5 +637,25 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 	}
 	asm volatile("cp.async.wait_all;" ::: "memory"); /* no copy may land after the CTA's shared memory is reassigned */
 	if (failed)
-		atomicOr(&img_err[sc->image], 1);
+		report_failure(img_err, sc, seg, JCU_ERR_BAD_HUFFMAN);
+	else if (active && u0 < total)
+	{
+		/* the left-over rule of jpeg_entropy.cuh on the unstuffed copy: R = real bits behind the end position */
+		const uint32_t ul = useg_len[(uint32_t)sc->seg_first + seg];
+		const int exact = (int)(ul & ~15u) - (int)(ul & 15u), pos = (int)(br.bp - 64u);
+		const int R = 8 * exact - pos;
+		if (R >= 25)
+		{
+			bool trips = seg + 1 < sc->nseg;
+			if (!trips)
+			{
+				/* last segment: a 0xFF data byte (a stuffed FF 00 in the file) among the bytes the reference has not consumed */
+				const uint8_t *ub = reinterpret_cast<const uint8_t *>(br.src);
+				for (int i = (pos + leftover_ahead_bits(R, ri > 0 && total % ri == 0)) >> 3; i < exact && !trips; ++i)
+					trips = ub[i ^ 3] == 0xffu; /* the slab holds big-endian words */
+			}
+			if (trips)
+				report_failure(img_err, sc, seg, JCU_ERR_UNKNOWN_MARKER);
+		}
+	}
 }

@@ -73,6 +73,7 @@ struct PcStream
 	uint32_t start, end; /* entropy-coded bytes of the scan: [start, end) */
 	uint32_t load_end;	/* loads stay below this offset */
 	uint32_t out_bytes;	/* unstuffed bytes appended so far */
+	uint32_t total;		/* unstuffed bytes of the whole scan, known once `ended` */
 	uint32_t carry;		/* last raw byte of the previous chunk */
 	uint32_t pend;			/* this lane's raw word of the chunk at raw_pos */
 	bool ended;
@@ -142,6 +143,8 @@ __device__ __forceinline__ void pc_produce(PcStream &s, uint8_t *ring_b, int lan
 		if ((uint32_t)i < cnt)
 			ring_b[(pos + (uint32_t)i) & (PC_RING_BYTES - 1)] = (uint8_t)(packed >> (8 * i));
 	s.out_bytes += __shfl_sync(PC_FULL, incl, 31);
+	if (e)
+		s.total = s.out_bytes;
 	__syncwarp();
 }
 
@@ -161,6 +164,7 @@ __device__ __forceinline__ void pc_open(PcStream &s, uint32_t *ring, const uint8
 	s.load_end = (data_len + 3u) & ~3u; /* the slab is padded past every file (jpeg_cuda.cu) */
 	s.raw_pos = start & ~127u;
 	s.out_bytes = 0;
+	s.total = 0;
 	s.carry = 0;
 	s.ended = false;
 	s.pend = pc_raw(s, s.raw_pos + 4u * (uint32_t)lane);
@@ -256,7 +260,7 @@ k_prog_coop(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans
 			if (spec < 0)
 			{
 				if (lane == 0)
-					atomicOr(&img_err[sc->image], 1);
+					report_failure(img_err, sc, 0u, JCU_ERR_BAD_HUFFMAN);
 				return;
 			}
 			int alias = -1;
@@ -631,6 +635,22 @@ k_prog_coop(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans
 			}
 		}
 	}
-	if (failed && lane == 0)
-		atomicOr(&img_err[sc->image], 1);
+	if (failed)
+	{
+		if (lane == 0)
+			report_failure(img_err, sc, 0u, JCU_ERR_BAD_HUFFMAN);
+	}
+	else
+	{
+		/* the left-over rule of jpeg_entropy.cuh (this scan is its own last segment): only when at least 25 real bits
+		   lie behind the end position does one lane walk the scan's bytes */
+		const long long pos = 32ll * (long long)st.widx - (long long)st.nb;
+		if (lane == 0 && (!st.ended || (long long)st.total >= ((pos + 32) >> 3)))
+		{
+			const uint8_t *file = bitstream + im->data_off;
+			if (leftover_trips_serial(file + seg_start[sc->seg_first + w.seg_first], file + im->data_len, pos, true,
+													 sc->restart_interval > 0 && total % sc->restart_interval == 0))
+				report_failure(img_err, sc, 0u, JCU_ERR_UNKNOWN_MARKER);
+		}
+	}
 }

@@ -42,7 +42,7 @@
 struct SsState
 {
 	uint32_t pos; /* read offset in the file (next byte to load) */
-	uint32_t aux; /* buffered bits | zig-zag index k << 8 | block-in-MCU << 16 */
+	uint32_t aux; /* buffered bits | zig-zag index k << 8 | block-in-MCU << 16 | zero bytes among the buffered bits << 28 */
 	uint64_t buf; /* the buffered bits themselves (implied by pos/aux; kept so a successor can resume) */
 };
 __device__ __forceinline__ bool ss_same(const SsState &a, const SsState &b) { return a.pos == b.pos && a.aux == b.aux; }
@@ -72,6 +72,7 @@ struct SBR
 	uint32_t pos, end;
 	uint64_t buf;
 	int nbits;
+	int pad; /* zero bits appended past the scan's end that are still buffered (bottom of the valid bits); a function of the position */
 };
 
 /* canonical top-up: > 56 valid bits; past the scan's end (or a marker) feeds zero bits */
@@ -80,8 +81,10 @@ __device__ __forceinline__ void sbr_topup(const uint8_t *__restrict__ base, SBR 
 	while (br.nbits <= 56)
 	{
 		uint32_t b = 0;
+		bool real = false;
 		if (br.pos < br.end)
 		{
+			real = true;
 			b = base[br.pos++];
 			if (b == 0xff)
 			{
@@ -98,9 +101,12 @@ __device__ __forceinline__ void sbr_topup(const uint8_t *__restrict__ base, SBR 
 				{
 					br.pos = br.end;
 					b = 0;
+					real = false;
 				}
 			}
 		}
+		if (!real)
+			br.pad += 8;
 		br.buf |= (uint64_t)b << (56 - br.nbits);
 		br.nbits += 8;
 	}
@@ -201,6 +207,7 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 		br.pos = pos;
 		br.buf = 0;
 		br.nbits = 0;
+		br.pad = 0;
 	}
 	else
 	{
@@ -218,7 +225,8 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 		br.buf = en.buf;
 		br.nbits = (int)(en.aux & 255u);
 		k = (int)((en.aux >> 8) & 255u);
-		b = (int)(en.aux >> 16);
+		b = (int)((en.aux >> 16) & 0xfffu);
+		br.pad = (int)(en.aux >> 28) << 3;
 	}
 
 	/* write phase: global block counter and the address of the block in progress */
@@ -236,6 +244,7 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 		blk = coef + sh.coff[s] + ((size_t)by * sh.bw[s] + bx) * 64;
 		key = coef_key(blk);
 	};
+	const uint32_t g_entry = g;
 	if (MODE == SS_WRITE && g < total_blocks)
 		locate(g);
 
@@ -293,12 +302,25 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 	if (MODE == SS_WRITE)
 	{
 		if (failed)
-			atomicOr(&img_err[sc->image], 1);
+			report_failure(img_err, sc, 0u, JCU_ERR_BAD_HUFFMAN);
+		else if (g_entry < total_blocks && g >= total_blocks)
+		{
+			/* this thread finished the scan's last block: the left-over rule of jpeg_entropy.cuh (one segment, the last) */
+			BitReader t;
+			t.p = base + br.pos;
+			t.end = base + end;
+			t.buf = br.buf;
+			t.nbits = br.nbits;
+			t.stopped = br.pos >= end;
+			t.pad = min(br.pad, br.nbits);
+			if (br_reference_trips(t, true, false))
+				report_failure(img_err, sc, 0u, JCU_ERR_UNKNOWN_MARKER);
+		}
 		return;
 	}
 	SsState ex;
 	ex.pos = br.pos;
-	ex.aux = (uint32_t)br.nbits | ((uint32_t)k << 8) | ((uint32_t)b << 16);
+	ex.aux = (uint32_t)br.nbits | ((uint32_t)k << 8) | ((uint32_t)b << 16) | ((uint32_t)(min(br.pad, br.nbits) >> 3) << 28);
 	ex.buf = br.buf;
 	sb.nblk[gi] = nb;
 	if (MODE == SS_GUESS)
@@ -372,7 +394,8 @@ k_ss_refine(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 				br.pos = en.pos;
 				br.buf = en.buf;
 				br.nbits = (int)(en.aux & 255u);
-				int k = (int)((en.aux >> 8) & 255u), b = (int)(en.aux >> 16);
+				br.pad = (int)(en.aux >> 28) << 3;
+				int k = (int)((en.aux >> 8) & 255u), b = (int)((en.aux >> 16) & 0xfffu);
 				uint32_t nb = 0;
 				for (;;)
 				{
@@ -400,7 +423,7 @@ k_ss_refine(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 				}
 				SsState ex;
 				ex.pos = br.pos;
-				ex.aux = (uint32_t)br.nbits | ((uint32_t)k << 8) | ((uint32_t)b << 16);
+				ex.aux = (uint32_t)br.nbits | ((uint32_t)k << 8) | ((uint32_t)b << 16) | ((uint32_t)(min(br.pad, br.nbits) >> 3) << 28);
 				ex.buf = br.buf;
 				sb.nblk[gi] = nb;
 				changed = !ss_same(ex, mine);

@@ -160,6 +160,11 @@ JCU_API int jcu_upload(jcu_ctx *c, const jcu_batch *b);								  /* H2D, asynchr
 JCU_API int jcu_run(jcu_ctx *c);															  /* entropy waves + output stage, asynchronous */
 JCU_API int jcu_sync(jcu_ctx *c);
 JCU_API int jcu_download(jcu_ctx *c, size_t off, size_t bytes, void *dst);	  /* async D2H on the ctx stream */
+/* per-image failure word: 0 = decoded; else JCU_ERR_CODE(word) says why (the earliest event in file order wins) */
+#define JCU_ERR_BAD_HUFFMAN 1u	 /* "bad huffman code", jpeg.c:317, 351, 446, 505, 549 */
+#define JCU_ERR_UNKNOWN_MARKER 2u /* a segment was decoded before its bytes were used up: the reference takes what follows
+												for a marker segment, jpeg.c:1186, 1722-1735 -> "unknown marker" (:1469) */
+#define JCU_ERR_CODE(word) ((~(uint32_t)(word)) & 3u)
 JCU_API int jcu_image_errors(jcu_ctx *c, int32_t *errs, int n);					  /* per-image device error flags (after sync) */
 JCU_API void *jcu_device_out(jcu_ctx *c);
 JCU_API int jcu_get_timings(jcu_ctx *c, jcu_timings *t);

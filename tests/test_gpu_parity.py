@@ -1,4 +1,5 @@
 """GPU parity tests proper: CUDA path vs the oracle, through the C-ABI (bit-exact)."""
+import collections
 import os
 
 import numpy as np
@@ -361,43 +362,71 @@ def test_16_bit_and_float_variants(oracle):
         assert call(ours, "stbi_load_16_from_memory", bad, 3, np.uint16) == call(ref, "stbi_load_16_from_memory", bad, 3, np.uint16)
 
 
+def _marker_list(b):
+    return [b[i + 1] for i in range(len(b) - 1) if b[i] == 0xFF and b[i + 1] not in (0x00, 0xFF)]
+
+
 @pytest.mark.parametrize("entropy_mode", [0, 1, 2])
 def test_damaged_streams_decode_like_the_reference(oracle, entropy_mode):
-    """Truncated and bit-flipped files: whatever the reference makes of them (zero bits past the end of a scan,
-    coefficients stored past a band, wrapped values, 'bad huffman code') the CUDA path must make too, byte for
-    byte.  One documented divergence: when a damaged scan is decoded before its bytes are used up,
-    the reference trips over the next stuffed FF 00 in the left-over bytes and fails with 'unknown marker';
-    the host parser here cannot know how far the device decoder will read, and decodes the file."""
+    """Truncated, bit-flipped, shortened and lengthened files: whatever the reference makes of them (zero bits past
+    the end of a scan, coefficients stored past a band, wrapped values, 'bad huffman code', and 'unknown marker' when
+    a restart segment is decoded before its bytes are used up -- jpeg.c:1186, 1722-1735) the CUDA path must make too:
+    same verdict, same failure string, same bytes.  Damage that changes the marker structure itself (a lost table or
+    RSTn) is left out: the reference then reads tables / sample planes it never initialised.  One narrow window is
+    tolerated and counted: a stuffed 0xFF within two bytes of where the reference's bit buffer happens to stand
+    when a scan runs out of MCUs (its fill level depends on the whole refill history)."""
     rng = np.random.default_rng(11)
-    fmts = ["420", "420_rst16", "444", "gray", "420_prog", "420_prog_rst5", "444_prog_ss", "gray_prog", "420_nonint",
-            "420_opt", "422"]
+    fmts = ["420", "420_rst16", "420_rst1", "444", "444_rst7", "gray", "gray_rst5", "420_prog", "420_prog_rst5", "444_prog_ss",
+            "gray_prog", "420_nonint", "420_nonint_rst11", "420_opt", "422", "420_rst3_fill", "420_dri_late"]
     cases = []
     for f in fmts:
         for (w, h) in ((233, 177), (64, 48)):
             raw = S.stream(f, w, h, 1)
             n = len(raw)
+            sos = raw.index(b"\xff\xda")
             for frac in (0.5, 0.8, 0.97):
                 cases.append((f"{f} {w}x{h} cut{frac}", bytes(raw[: int(n * frac)])))
-            for t in range(8):
+            for t in range(14):
                 b = bytearray(raw)
-                pos = int(rng.integers(n // 3, n - 2))
-                b[pos] ^= 1 << int(rng.integers(0, 8))
-                cases.append((f"{f} {w}x{h} flip{t}@{pos}", bytes(b)))
+                kind = t % 4
+                pos = int(rng.integers(max(n // 3, sos + 16), n - 2))
+                if kind < 2:
+                    b[pos] ^= 1 << int(rng.integers(0, 8))
+                elif kind == 2:
+                    del b[pos : pos + int(rng.integers(1, 9))]
+                else:
+                    b[pos:pos] = b[pos : pos + int(rng.integers(1, 9))]
+                if _marker_list(b) == _marker_list(raw):
+                    cases.append((f"{f} {w}x{h} damage{kind}.{t}@{pos}", bytes(b)))
     d = ic.BatchDecoder(device=0, entropy_mode=entropy_mode)
     outs = d.decode([c[1] for c in cases], 3)
-    tolerated = 0
+    reasons = collections.Counter()
+    window = 0  # verdicts that hinge on the reference's read-ahead at the end of a scan (DESIGN.md 7)
     for (tag, data), got in zip(cases, outs):
         want, *_ = oracle.load_from_memory(data, 3)
         if want is None:
-            if oracle.failure_reason() == "unknown marker" and got is not None:
-                tolerated += 1
+            why = oracle.failure_reason()
+            reasons[why] += 1
+            if got is not None and why == "unknown marker":
+                window += 1
                 continue
-            assert got is None, f"mode{entropy_mode} {tag}: reference fails ({oracle.failure_reason()}), gpu decodes"
+            assert got is None, f"mode{entropy_mode} {tag}: reference fails ({why}), gpu decodes"
         else:
-            assert got is not None, f"mode{entropy_mode} {tag}: reference decodes, gpu fails"
+            if got is None:
+                ic.stbi_load_from_memory(data, 3)
+                assert ic.failure_reason() == "unknown marker", f"mode{entropy_mode} {tag}: reference decodes, gpu fails"
+                window += 1
+                continue
             assert np.array_equal(got, want), f"mode{entropy_mode} {tag}: pixels differ"
-    assert tolerated < len(cases) // 8, tolerated
+    assert reasons["unknown marker"] > 10 and reasons["bad huffman code"] > 0, reasons  # both rules were exercised
+    assert window <= len(cases) // 50, (window, len(cases))
     d.close()
+    # the failure string itself, through the per-image entry point
+    for tag, data in cases[:: max(1, len(cases) // 40)]:
+        want, *_ = oracle.load_from_memory(data, 3)
+        got, *_ = ic.stbi_load_from_memory(data, 3)
+        if want is None and got is None:
+            assert ic.failure_reason() == oracle.failure_reason(), tag
 
 
 @pytest.mark.parametrize("entropy_mode", [0, 2])

@@ -44,6 +44,10 @@ static int err_zero(const char *why)
 API const char *stbi_failure_reason(void) { return tl_reason; }
 API void stbi_image_free(void *p) { free(p); }
 API void stbi_set_flip_vertically_on_load(int flag) { g_flip_on_load = flag; }
+/* PNG-only switches of the reference (convert.c / png.c): accepted so that callers link unchanged; a JPEG has no
+   alpha to un-premultiply and no CgBI chunk */
+API void stbi_set_unpremultiply_on_load(int flag) { (void)flag; }
+API void stbi_convert_iphone_png_to_rgb(int flag) { (void)flag; }
 
 static double now_ms(void)
 {
@@ -901,15 +905,30 @@ static stbi_uc *drain_file(FILE *f, size_t *len)
 	return buf;
 }
 
+/* The reference reads the FILE through a 128-byte window and, after a successful load, seeks back by what it had
+   buffered but not used (convert.c:208, :222): the stream is left just behind the image's EOI marker, so that
+   images stored back to back can be loaded one after the other.  Here the whole rest of the file was drained. */
+static void seek_behind_image(FILE *f, long start, const stbi_uc *buf, size_t len)
+{
+	jp_result r;
+	memset(&r, 0, sizeof(r));
+	if (start >= 0 && jp_parse(buf, len, 0, JP_MODE_LOAD, &r))
+		fseek(f, start + (long)r.consumed, SEEK_SET);
+	jp_result_free(&r);
+}
+
 API stbi_uc *stbi_load_from_file(FILE *f, int *x, int *y, int *comp, int req_comp)
 {
 	size_t len = 0;
+	const long start = ftell(f);
 	stbi_uc *buf = drain_file(f, &len), *r;
 	if (!buf)
 		return (stbi_uc *)err_null("outofmem");
 	r = load_from_buffer(buf, len, x, y, comp, req_comp);
+	if (r)
+		seek_behind_image(f, start, buf, len);
 	free(buf);
-	return r; /* the file is left at EOF (the reference seeks back to just after the image, convert.c:208) */
+	return r;
 }
 
 API stbi_uc *stbi_load(char const *filename, int *x, int *y, int *comp, int req_comp)
@@ -954,11 +973,14 @@ static void *wide_from_callbacks(stbi_io_callbacks const *clbk, void *user, int 
 static void *wide_from_file(FILE *f, int *x, int *y, int *comp, int req_comp, int widen)
 {
 	size_t len = 0;
+	const long start = ftell(f);
 	stbi_uc *buf = drain_file(f, &len);
 	void *r;
 	if (!buf)
 		return err_null("outofmem");
 	r = wide_from_memory(buf, len, x, y, comp, req_comp, widen);
+	if (r && widen == WIDE_16)
+		seek_behind_image(f, start, buf, len); /* convert.c:222; stbi_loadf_from_file leaves the stream where the reader stopped */
 	free(buf);
 	return r;
 }

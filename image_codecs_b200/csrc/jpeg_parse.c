@@ -687,6 +687,7 @@ int jp_parse(const unsigned char *buf, size_t len, int req_comp, int mode, jp_re
 			memcpy(r->img.qt[i], p->dequant[p->tq[i]], sizeof(r->img.qt[0]));
 
 	choose_output(p, req_comp);
+	r->consumed = p->cur.pos < p->cur.len ? p->cur.pos : p->cur.len;
 	r->img.ok = 1;
 	return 1;
 }

@@ -39,6 +39,7 @@ typedef struct
 	jcu_huff_spec *huff;
 	int nhuff, cap_huff;
 
+	size_t consumed; /* bytes of the file the reference has read when it returns: up to and including the EOI marker */
 	double entropy_bytes; /* entropy-coded bytes over all scans (incl. stuffing, excl. markers) */
 	long long coef_blocks; /* blocks the output stage reads (MCU-padded, decode_n components) */
 } jp_result;

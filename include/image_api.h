@@ -104,6 +104,9 @@ STBIDEF int stbi_is_16_bit_from_callbacks(stbi_io_callbacks const *clbk, void *u
 STBIDEF void stbi_image_free(void *retval_from_stbi_load);
 STBIDEF const char *stbi_failure_reason(void); /* thread-local */
 STBIDEF void stbi_set_flip_vertically_on_load(int flag_true_if_should_flip); /* convert.c:97-101 */
+/* PNG-only switches of the reference, accepted and ignored (a JPEG has neither alpha nor a CgBI chunk) */
+STBIDEF void stbi_set_unpremultiply_on_load(int flag_true_if_should_unpremultiply);
+STBIDEF void stbi_convert_iphone_png_to_rgb(int flag_true_if_should_convert);
 
 /* ---- JPEG writer (reference codec/jpeg_write.c:368-390): same byte stream, encoded on the GPU ---- */
 typedef void stbi_write_func(void *context, void *data, int size);

@@ -257,6 +257,48 @@ def test_encoder_matches_reference_writer(oracle):
     assert (x, y, c) == (233, 177, 3) and np.array_equal(back, want)
 
 
+def test_load_from_file_leaves_the_stream_behind_the_image(oracle, tmp_path):
+    """stbi_load_from_file / stbi_load_from_file_16 (reference convert.c:199-226) 'unget' what the reader buffered but
+    did not use: the FILE is left just behind the EOI marker, so images stored back to back load one after the other."""
+    import ctypes as C
+
+    a, b = S.stream("420_rst16", 97, 61, 1), S.stream("gray_prog", 40, 33, 2)
+    path = tmp_path / "two.jpg"
+    path.write_bytes(a + b + b"trailing")
+    libc = C.CDLL(None)
+    libc.fopen.restype = C.c_void_p
+    libc.fopen.argtypes = [C.c_char_p, C.c_char_p]
+    libc.ftell.restype = C.c_long
+    libc.ftell.argtypes = [C.c_void_p]
+    libc.fclose.argtypes = [C.c_void_p]
+    L = ic.lib()
+    ip = C.POINTER(C.c_int)
+    for fn, ctype, scale in (("stbi_load_from_file", C.c_uint8, 1), ("stbi_load_from_file_16", C.c_uint16, 257)):
+        f = getattr(L, fn)
+        f.restype = C.c_void_p
+        f.argtypes = [C.c_void_p, ip, ip, ip, C.c_int]
+        L.stbi_image_free.argtypes = [C.c_void_p]
+        fp = libc.fopen(str(path).encode(), b"rb")
+        assert fp
+        try:
+            end = 0
+            for data in (a, b):
+                x, y, c = C.c_int(0), C.c_int(0), C.c_int(0)
+                p_ = f(fp, C.byref(x), C.byref(y), C.byref(c), 3)
+                assert p_, ic.failure_reason()
+                got = np.ctypeslib.as_array(C.cast(p_, C.POINTER(ctype)), shape=(y.value, x.value, 3)).copy()
+                L.stbi_image_free(p_)
+                want, *_ = oracle.load_from_memory(data, 3)
+                assert np.array_equal(got, want.astype(got.dtype) * scale)
+                end += len(data)
+                assert libc.ftell(fp) == end
+            # what follows is no image: the call fails like the reference does on the same bytes
+            x, y, c = C.c_int(0), C.c_int(0), C.c_int(0)
+            assert not f(fp, C.byref(x), C.byref(y), C.byref(c), 3)
+        finally:
+            libc.fclose(fp)
+
+
 def test_flip_on_load_is_a_store_epilogue(oracle):
     """stbi_set_flip_vertically_on_load (reference convert.c:37-61, 97-101): the output kernels store bottom-up, so
     the batched calls -- host buffers and device-resident results alike -- return flipped rows without a host pass."""

@@ -110,6 +110,32 @@ def test_per_image_api(oracle):
     assert ic.failure_reason() == "bad req_comp"
 
 
+def test_batch_edge_cases(oracle):
+    """Empty batch, empty and foreign buffers, header rejects and device-level failures between good images (a bad
+    neighbour must not disturb the others), 1x1 / 1xN / Nx1 images, a batch that spans several pipeline chunks."""
+    d = ic.BatchDecoder(device=0, chunk_images=4)
+    assert d.decode([], 3) == []
+    good = [S.stream("420", 1, 1, 0), S.stream("444", 1, 37, 1), S.stream("gray", 41, 1, 2), S.stream("420_rst1", 17, 9, 0),
+            S.stream("420_prog", 8, 8, 1), S.stream("422", 15, 15, 2)]
+    sof = good[3].index(b"\xff\xc0")
+    bad_header = bytearray(good[3])
+    bad_header[sof + 4] = 12  # 12-bit precision: "only 8-bit"
+    truncated = good[4][:40]
+    mixed = [good[0], b"", good[1], b"GIF89a-not-a-jpeg", good[2], bytes(bad_header), good[3], truncated, good[4], good[5]] * 3
+    for rc in (0, 3):
+        outs = d.decode(mixed, rc)
+        assert len(outs) == len(mixed)
+        for i, (data, got) in enumerate(zip(mixed, outs)):
+            want, *_ = oracle.load_from_memory(data, rc) if data else (None,)
+            if want is None:
+                assert got is None, i
+            else:
+                assert got is not None and np.array_equal(got, want), i
+    d.close()
+    for data, why in ((b"", "unknown image type"), (bytes(bad_header), "only 8-bit")):
+        assert ic.stbi_load_from_memory(data, 3)[0] is None and ic.failure_reason() == why
+
+
 @pytest.mark.parametrize("rows_per_band", [0, 1, 5, 64])
 def test_fused_420_strips_and_bands(oracle, rows_per_band):
     """4:2:0 strip kernel: images wider than one 640-pixel strip (2 and 3 strips, a 1-MCU last strip,

@@ -840,11 +840,14 @@ API stbi_uc *stbi_load_from_memory(stbi_uc const *buffer, int len, int *x, int *
 	return load_from_buffer(buffer, len > 0 ? (size_t)len : 0, x, y, comp, req_comp);
 }
 
-/* the GPU path needs the whole stream: callbacks / FILE* sources are drained into one buffer
-   (the reference instead refills a 128-byte window, common.c:10) */
-static stbi_uc *drain_callbacks(stbi_io_callbacks const *c, void *user, size_t *len)
+/* The GPU path needs the whole image in memory, the reference refills a 128-byte window (common.c:10) and so reads
+   at most 128 bytes past the image.  A callback source may be a stream with more behind the image (or a socket
+   that blocks), so it is read in growing steps only until the marker walk reaches the EOI of the image: whenever
+   the buffer has doubled, the host parser is tried on what is there, and a parse that succeeds never looks at
+   later bytes.  A file that is damaged or cut short is read to its end, like the reference would. */
+static stbi_uc *drain_callbacks(stbi_io_callbacks const *c, void *user, size_t *len, int mode)
 {
-	size_t cap = 1 << 16, n = 0;
+	size_t cap = 1 << 12, n = 0;
 	stbi_uc *buf = (stbi_uc *)malloc(cap);
 	while (buf)
 	{
@@ -855,7 +858,15 @@ static stbi_uc *drain_callbacks(stbi_io_callbacks const *c, void *user, size_t *
 		n += (size_t)got;
 		if (n == cap)
 		{
-			stbi_uc *nb = (stbi_uc *)realloc(buf, cap * 2);
+			stbi_uc *nb;
+			jp_result r;
+			int complete;
+			memset(&r, 0, sizeof(r));
+			complete = jp_parse(buf, n, 0, mode, &r);
+			jp_result_free(&r);
+			if (complete)
+				break;
+			nb = (stbi_uc *)realloc(buf, cap * 2);
 			if (!nb)
 			{
 				free(buf);
@@ -872,7 +883,7 @@ static stbi_uc *drain_callbacks(stbi_io_callbacks const *c, void *user, size_t *
 API stbi_uc *stbi_load_from_callbacks(stbi_io_callbacks const *clbk, void *user, int *x, int *y, int *comp, int req_comp)
 {
 	size_t len = 0;
-	stbi_uc *buf = drain_callbacks(clbk, user, &len), *r;
+	stbi_uc *buf = drain_callbacks(clbk, user, &len, JP_MODE_LOAD), *r;
 	if (!buf)
 		return (stbi_uc *)err_null("outofmem");
 	r = load_from_buffer(buf, len, x, y, comp, req_comp);
@@ -962,7 +973,7 @@ static void *wide_from_memory(stbi_uc const *buffer, size_t len, int *x, int *y,
 static void *wide_from_callbacks(stbi_io_callbacks const *clbk, void *user, int *x, int *y, int *comp, int req_comp, int widen)
 {
 	size_t len = 0;
-	stbi_uc *buf = drain_callbacks(clbk, user, &len);
+	stbi_uc *buf = drain_callbacks(clbk, user, &len, JP_MODE_LOAD);
 	void *r;
 	if (!buf)
 		return err_null("outofmem");
@@ -1307,7 +1318,7 @@ API int stbi_info_from_memory(stbi_uc const *buffer, int len, int *x, int *y, in
 API int stbi_info_from_callbacks(stbi_io_callbacks const *c, void *user, int *x, int *y, int *comp)
 {
 	size_t len = 0;
-	stbi_uc *buf = drain_callbacks(c, user, &len);
+	stbi_uc *buf = drain_callbacks(c, user, &len, JP_MODE_HEADER); /* stbi__jpeg_info_raw stops behind the frame header */
 	int ok;
 	if (!buf)
 		return err_zero("outofmem");

@@ -325,6 +325,30 @@ def test_load_from_file_leaves_the_stream_behind_the_image(oracle, tmp_path):
             libc.fclose(fp)
 
 
+def test_load_from_callbacks_stops_behind_the_image(oracle):
+    """stbi_load_from_callbacks (reference convert.c:261): pixels as from memory, with short reads; a stream with
+    more behind the image is read only until the image is complete (the reference: at most 128 bytes further)."""
+    import ctypes as C
+
+    L = ic.lib()
+    ip = C.POINTER(C.c_int)
+    L.stbi_load_from_callbacks.restype = C.c_void_p
+    L.stbi_load_from_callbacks.argtypes = [C.c_void_p, C.c_void_p, ip, ip, ip, C.c_int]
+    L.stbi_image_free.argtypes = [C.c_void_p]
+    for fmt, w, h in (("420_rst16", 233, 177), ("444_prog_ss", 129, 65), ("gray", 31, 9)):
+        data = S.stream(fmt, w, h, 1)
+        want, *_ = oracle.load_from_memory(data, 3)
+        for max_read in (1 << 30, 1000):
+            src = S.CallbackSource(data + bytes(4 << 20), max_read)
+            x, y, c = C.c_int(0), C.c_int(0), C.c_int(0)
+            p_ = L.stbi_load_from_callbacks(C.byref(src.struct), None, C.byref(x), C.byref(y), C.byref(c), 3)
+            assert p_, ic.failure_reason()
+            got = np.ctypeslib.as_array(C.cast(p_, C.POINTER(C.c_uint8)), shape=(y.value, x.value, 3)).copy()
+            L.stbi_image_free(p_)
+            assert np.array_equal(got, want)
+            assert src.pos <= max(2 * len(data), 8192), (src.pos, len(data))
+
+
 def test_flip_on_load_is_a_store_epilogue(oracle):
     """stbi_set_flip_vertically_on_load (reference convert.c:37-61, 97-101): the output kernels store bottom-up, so
     the batched calls -- host buffers and device-resident results alike -- return flipped rows without a host pass."""

@@ -151,3 +151,34 @@ def test_scan_waves_follow_data_dependencies():
     # spectral selection only: DC of all components, then two bands per component: the components are independent of each other
     ss = api.inspect_scans(S.stream("444_prog_ss", 64, 48))
     assert ss[0] == 0 and set(ss[1:]) == {1, 2} and len(ss) == 7
+
+
+def test_info_from_callbacks_reads_no_further_than_the_header(oracle):
+    """stbi_info_from_callbacks (reference image_api.c:126): same answer as the reference's, short reads tolerated,
+    and a source with more behind the frame header is not drained (the reference stops behind the SOF)."""
+    import ctypes as C
+
+    L = ic.lib()
+    ip = C.POINTER(C.c_int)
+    L.stbi_info_from_callbacks.restype = C.c_int
+    L.stbi_info_from_callbacks.argtypes = [C.c_void_p, C.c_void_p, ip, ip, ip]
+    ref = oracle.lib if oracle.kind.startswith("reference") else None
+    if ref is not None:
+        ref.stbi_info_from_callbacks.restype = C.c_int
+        ref.stbi_info_from_callbacks.argtypes = [C.c_void_p, C.c_void_p, ip, ip, ip]
+    for fmt, w, h in (("420", 233, 177), ("gray_prog", 64, 48), ("cmyk", 40, 31)):
+        data = S.stream(fmt, w, h, 0) + bytes(1 << 20)
+        for max_read in (1 << 30, 7):
+            src = S.CallbackSource(data, max_read)
+            x, y, c = C.c_int(0), C.c_int(0), C.c_int(0)
+            assert L.stbi_info_from_callbacks(C.byref(src.struct), None, C.byref(x), C.byref(y), C.byref(c)) == 1
+            assert (x.value, y.value) == (w, h)
+            assert src.pos <= 2 * 4096 + 4096, src.pos  # one doubling step past the header, not the whole megabyte
+            if ref is not None:
+                src2 = S.CallbackSource(data, max_read)
+                rx, ry, rc = C.c_int(0), C.c_int(0), C.c_int(0)
+                assert ref.stbi_info_from_callbacks(C.byref(src2.struct), None, C.byref(rx), C.byref(ry), C.byref(rc)) == 1
+                assert (rx.value, ry.value, rc.value) == (x.value, y.value, c.value)
+    src = S.CallbackSource(b"no image here" * 100)
+    x, y, c = C.c_int(0), C.c_int(0), C.c_int(0)
+    assert L.stbi_info_from_callbacks(C.byref(src.struct), None, C.byref(x), C.byref(y), C.byref(c)) == 0

@@ -516,11 +516,13 @@ extern "C" int jcu_run(jcu_ctx *c)
 			if (c->wave_two[w])
 				k_entropy_baseline<2, 2><<<nb, ENTB_THREADS, ENTB_DYN_SMEM, st>>>(
 					wk, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p, (const jcu_huff_spec *)c->huff.p,
-					(const uint8_t *)c->uslab.p, (const uint32_t *)c->useg_len.p, (int16_t *)c->coef.p, (int32_t *)c->err.p);
+					(const uint8_t *)c->uslab.p, (const uint32_t *)c->useg_len.p, (int16_t *)c->coef.p, (int32_t *)c->err.p,
+					(const uint8_t *)c->bits.p);
 			else
 				k_entropy_baseline<4, 4><<<nb, ENTB_THREADS, ENTB_DYN_SMEM, st>>>(
 					wk, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p, (const jcu_huff_spec *)c->huff.p,
-					(const uint8_t *)c->uslab.p, (const uint32_t *)c->useg_len.p, (int16_t *)c->coef.p, (int32_t *)c->err.p);
+					(const uint8_t *)c->uslab.p, (const uint32_t *)c->useg_len.p, (int16_t *)c->coef.p, (int32_t *)c->err.p,
+					(const uint8_t *)c->bits.p);
 			c->launches++;
 		}
 		const int nsm = c->wave_nsmall[w], nco = c->wave_ncoop[w];

@@ -301,6 +301,30 @@ __device__ __noinline__ bool br_reference_trips(const BitReader &br, bool last_s
 	return false;
 }
 
+/* distance in bits from the reader's position to the first 0xFF data byte that lies wholly behind it (a stuffed
+   FF 00 in the file), -1 if the segment has none */
+__device__ __noinline__ int br_first_ff_ahead(const BitReader &br)
+{
+	const int real = br.nbits - br.pad;
+	if (real < 0)
+		return -1;
+	for (int o = real & 7; o + 8 <= real; o += 8)
+		if (((br.buf >> (56 - o)) & 0xffu) == 0xffu)
+			return o;
+	if (br.stopped)
+		return -1;
+	const uint8_t *q = br.p;
+	uint32_t b;
+	for (int o = real; raw_next_unstuffed(q, br.end, b); o += 8)
+	{
+		if (b == 0xffu)
+			return o;
+		if (o > (1 << 30))
+			break;
+	}
+	return -1;
+}
+
 __device__ __forceinline__ uint32_t br_peek(const BitReader &br, int n) /* 1 <= n <= 32 */
 {
 	return (uint32_t)(br.buf >> (64 - n));
@@ -636,6 +660,6 @@ k_entropy_segments(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 	}
 	if (failed)
 		report_failure(img_err, sc, seg, JCU_ERR_BAD_HUFFMAN);
-	else if (active && u0 < total && br_reference_trips(br, seg + 1 >= sc->nseg, ri > 0 && total % ri == 0))
+	else if (active && u0 < total && br_reference_trips(br, seg + 1 >= sc->nseg && !sc->end_rst, ri > 0 && total % ri == 0))
 		report_failure(img_err, sc, seg, JCU_ERR_UNKNOWN_MARKER);
 }

@@ -464,6 +464,118 @@ __device__ __forceinline__ bool entb_symbol(uint32_t ring_lane, EBR &br, uint32_
 	return true;
 }
 
+/* ------------------------------------------------------------------------------------------------------
+ * Rare path of the left-over rule (jpeg_entropy.cuh).  When a scan simply runs out of units, how many bytes the
+ * reference's reader holds beyond the end position depends on where its last refill happened.  If a stuffed 0xFF
+ * lies inside that window (within 32 bits of the end position -- damaged files only), one thread replays the
+ * reference's reader literally over the raw bytes of the segment: stbi__grow_buffer_unsafe (jpeg.c:167-187), the
+ * code_bits bookkeeping of stbi__jpeg_huff_decode (:205-243) and stbi__extend_receive (:249-266), the refill
+ * checks of stbi__jpeg_decode_block (:308-370) and the restart check (:1180-1189).  No coefficient is produced.
+ * Returns true when the reference leaves the scan without having seen the marker behind it and its marker loop
+ * (jpeg.c:1722-1735) then runs into an 0xFF before that marker.
+ * ------------------------------------------------------------------------------------------------------ */
+struct ReplayReader
+{
+	const uint8_t *base;
+	uint32_t len, pos, buf;
+	int cb;
+	bool nomore;
+};
+__device__ __forceinline__ uint32_t replay_get8(ReplayReader &r)
+{
+	const uint32_t b = r.pos < r.len ? r.base[r.pos] : 0u; /* stbi__get8 at the end of the data: 0 */
+	++r.pos;
+	return b;
+}
+__device__ __noinline__ void replay_grow(ReplayReader &r)
+{
+	do
+	{
+		const uint32_t b = r.nomore ? 0u : replay_get8(r);
+		if (b == 0xffu)
+		{
+			uint32_t c = replay_get8(r);
+			while (c == 0xffu)
+				c = replay_get8(r);
+			if (c != 0u)
+			{
+				r.nomore = true;
+				return;
+			}
+		}
+		if (b)
+			r.buf |= b << (24 - r.cb);
+		r.cb += 8;
+	} while (r.cb <= 24);
+}
+template <int BITS>
+__device__ __forceinline__ bool replay_symbol(ReplayReader &r, const EntbLutT<BITS> *__restrict__ L, bool is_dc, uint32_t &e)
+{
+	if (r.cb < 16)
+		replay_grow(r);
+	const uint32_t top = r.buf;
+	e = L->fast[top >> (32 - BITS)];
+	if (e == 0u)
+	{
+		const uint32_t t16 = top >> 16;
+		int l = BITS + 1;
+		while (t16 >= L->limit[l])
+			++l;
+		if (l > 16)
+			return false;
+		e = entb_entry(L->vals[(L->base[l] + (int)(t16 >> (16 - l))) & 255], l, is_dc);
+	}
+	const int len = (int)ENTB_E_LEN(e), size = (int)ENTB_E_SIZE(e);
+	if (len > r.cb)
+		return false; /* jpeg.c:218, 237 */
+	r.buf <<= len;
+	r.cb -= len;
+	if (size)
+	{
+		if (r.cb < size)
+			replay_grow(r);
+		r.buf <<= size;
+		r.cb -= size;
+	}
+	return true;
+}
+template <typename SH>
+__device__ __noinline__ bool entb_replay_trips(const SH &sh, const uint8_t *base, uint32_t len, uint32_t start, int n_units,
+															  bool at_restart, uint32_t data_end)
+{
+	ReplayReader r;
+	r.base = base;
+	r.len = len;
+	r.pos = start;
+	r.buf = 0u;
+	r.cb = 0;
+	r.nomore = false;
+	const int nb = sh.nblk;
+	for (int u = 0; u < n_units; ++u)
+		for (int b = 0; b < nb; ++b)
+		{
+			const uint32_t ent = sh.blk[b];
+			uint32_t e;
+			if (!replay_symbol<ENTB_DC_BITS>(r, &sh.dc[(ent >> 12) & 3u], true, e))
+				return false;
+			int k = 1;
+			do
+			{
+				if (!replay_symbol<ENTB_AC_BITS>(r, &sh.ac[(ent >> 16) & 3u], false, e))
+					return false;
+				k += (int)ENTB_E_KADV(e);
+			} while (k < 64);
+		}
+	if (at_restart && r.cb < 24)
+		replay_grow(r);
+	if (r.nomore)
+		return false;
+	for (uint32_t q = r.pos; q < len && q < data_end; ++q)
+		if (base[q] == 0xffu)
+			return true;
+	return false;
+}
+
 /*
  * grid = CTA work items (EntWork) of one wave restricted to baseline scans; thread t decodes restart
  * segment (work.seg_first + t) of the CTA's scan from the unstuffed slab.  <ND, NA> = distinct DC / AC
@@ -480,7 +592,8 @@ __global__ void __launch_bounds__(ENTB_THREADS)
 k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 						 const jcu_image *__restrict__ images, const uint32_t *__restrict__ seg_start,
 						 const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ uslab,
-						 const uint32_t *__restrict__ useg_len, int16_t *__restrict__ coef, int32_t *__restrict__ img_err)
+						 const uint32_t *__restrict__ useg_len, int16_t *__restrict__ coef, int32_t *__restrict__ img_err,
+						 const uint8_t *__restrict__ bitstream)
 {
 	__shared__ EntbSharedT<ND, NA> sh;
 	extern __shared__ __align__(16) uint32_t s_dyn[];
@@ -641,21 +754,33 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 	else if (active && u0 < total)
 	{
 		/* the left-over rule of jpeg_entropy.cuh on the unstuffed copy: R = real bits behind the end position */
-		const uint32_t ul = useg_len[(uint32_t)sc->seg_first + seg];
+		const uint32_t g = (uint32_t)sc->seg_first + seg;
+		const uint32_t ul = useg_len[g];
 		const int exact = (int)(ul & ~15u) - (int)(ul & 15u), pos = (int)(br.bp - 64u);
 		const int R = 8 * exact - pos;
-		if (R >= 25)
+		const bool at_restart = ri > 0 && total % ri == 0;
+		bool trips = false;
+		if (seg + 1 < sc->nseg || sc->end_rst)
+			trips = R >= 25; /* the marker loop runs into the RSTn itself */
+		else if (R >= 9)
 		{
-			bool trips = seg + 1 < sc->nseg;
-			if (!trips)
+			/* last segment: the first 0xFF data byte (a stuffed FF 00 in the file) wholly behind the end position */
+			const uint8_t *ub = reinterpret_cast<const uint8_t *>(br.src);
+			int f = -1;
+			for (int i = (pos + 7) >> 3; i < exact && f < 0; ++i)
+				if (ub[i ^ 3] == 0xffu) /* the slab holds big-endian words */
+					f = i;
+			if (f >= 0)
 			{
-				/* last segment: a 0xFF data byte (a stuffed FF 00 in the file) among the bytes the reference has not consumed */
-				const uint8_t *ub = reinterpret_cast<const uint8_t *>(br.src);
-				for (int i = (pos + leftover_ahead_bits(R, ri > 0 && total % ri == 0)) >> 3; i < exact && !trips; ++i)
-					trips = ub[i ^ 3] == 0xffu; /* the slab holds big-endian words */
+				if (8 * f >= pos + 32)
+					trips = true; /* beyond anything the reference can have buffered */
+				else if (at_restart)
+					trips = R >= 25 && 8 * f >= pos + leftover_ahead_bits(R, true);
+				else
+					trips = entb_replay_trips(sh, bitstream + im->data_off, im->data_len, seg_start[g], u1 - u0, false, sc->data_end);
 			}
-			if (trips)
-				report_failure(img_err, sc, seg, JCU_ERR_UNKNOWN_MARKER);
 		}
+		if (trips)
+			report_failure(img_err, sc, seg, JCU_ERR_UNKNOWN_MARKER);
 	}
 }

@@ -435,9 +435,27 @@ static void walk_entropy_segments(parser *p, jcu_scan *sc)
 			pos = q + 1;
 			continue;
 		}
-		p->pending = code;
 		sc->data_end = (uint32_t)at;
 		pos = q + 1;
+		if (ri && code >= 0xd0 && code <= 0xd7 && sc->total_units % ri == 0)
+		{
+			/* One RSTn too many behind a scan whose last interval is complete: the restart check at the end of that
+			   interval (jpeg.c:1180-1189) takes it for a restart and clears it, the scan returns without a pending
+			   marker, and the marker loop skips to the next 0xFF and takes the byte behind it as the marker
+			   (jpeg.c:1722-1735), whatever lies in between. */
+			const unsigned char *nf = pos < len ? (const unsigned char *)memchr(buf + pos, 0xff, len - pos) : NULL;
+			sc->end_rst = 1;
+			if (!nf)
+			{
+				pos = len;
+				break;
+			}
+			pos = (size_t)(nf - buf) + 2;
+			code = pos - 1 < len ? buf[pos - 1] : 0;
+			if (pos > len)
+				pos = len + 1; /* the missing byte read as 0 (cur_u8 past the end) */
+		}
+		p->pending = code;
 		break;
 	}
 	p->cur.pos = pos;

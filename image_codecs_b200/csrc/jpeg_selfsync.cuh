@@ -313,7 +313,10 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 			t.nbits = br.nbits;
 			t.stopped = br.pos >= end;
 			t.pad = min(br.pad, br.nbits);
-			if (br_reference_trips(t, true, false))
+			/* a stuffed 0xFF more than 32 bits behind the end position is certainly unread; one inside the window needs
+			   the exact fill level of the reference's bit buffer: replay its reader over the scan (rare, damaged files) */
+			const int d_ff = br_first_ff_ahead(t);
+			if (d_ff >= 32 || (d_ff >= 0 && entb_replay_trips(sh, base, im->data_len, scan_start, sc->total_units, false, end)))
 				report_failure(img_err, sc, 0u, JCU_ERR_UNKNOWN_MARKER);
 		}
 		return;

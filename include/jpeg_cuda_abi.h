@@ -111,7 +111,7 @@ typedef struct
 	uint32_t seg_first;		  /* first entry in the segment-offset array */
 	uint32_t nseg;
 	uint32_t data_end;		  /* offset (in the file) of the marker that terminates the scan */
-	uint32_t pad;
+	uint32_t end_rst;			  /* 1 = that marker is an RSTn behind the last expected interval (the reference's restart check consumes it) */
 } jcu_scan;
 
 typedef struct

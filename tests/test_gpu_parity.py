@@ -466,7 +466,9 @@ def test_damaged_streams_decode_like_the_reference(oracle, entropy_mode):
     same verdict, same failure string, same bytes.  Damage that changes the marker structure itself (a lost table or
     RSTn) is left out: the reference then reads tables / sample planes it never initialised.  One narrow window is
     tolerated and counted: a stuffed 0xFF within two bytes of where the reference's bit buffer happens to stand
-    when a scan runs out of MCUs (its fill level depends on the whole refill history)."""
+    when a progressive scan (or one decoded by the generic per-segment kernel) runs out of MCUs -- its fill level
+    depends on the whole refill history; baseline scans replay the reference's reader there and are exact
+    (DESIGN.md 7)."""
     rng = np.random.default_rng(11)
     fmts = ["420", "420_rst16", "420_rst1", "444", "444_rst7", "gray", "gray_rst5", "420_prog", "420_prog_rst5", "444_prog_ss",
             "gray_prog", "420_nonint", "420_nonint_rst11", "420_opt", "422", "420_rst3_fill", "420_dri_late"]
@@ -490,6 +492,15 @@ def test_damaged_streams_decode_like_the_reference(oracle, entropy_mode):
                     b[pos:pos] = b[pos : pos + int(rng.integers(1, 9))]
                 if _marker_list(b) == _marker_list(raw):
                     cases.append((f"{f} {w}x{h} damage{kind}.{t}@{pos}", bytes(b)))
+    # one restart interval too many: a complete last interval swallows the extra RSTn and the marker loop skips what
+    # follows (jpeg.c:1180-1189, 1722-1735); an incomplete one runs into it ("unknown marker")
+    for f, w, h in (("420_rst1", 64, 48), ("gray_rst5", 80, 40), ("420_rst16", 233, 177), ("420_prog_rst5", 80, 80)):
+        raw = S.stream(f, w, h, 1)
+        rst = [i for i in range(len(raw) - 1) if raw[i] == 0xFF and 0xD0 <= raw[i + 1] <= 0xD7]
+        for k in (0, len(rst) // 2, len(rst) - 2):
+            b = bytearray(raw)
+            b[rst[k + 1] : rst[k + 1]] = raw[rst[k] : rst[k + 1]]  # RSTn + its interval, twice
+            cases.append((f"{f} {w}x{h} interval {k} doubled", bytes(b)))
     d = ic.BatchDecoder(device=0, entropy_mode=entropy_mode)
     outs = d.decode([c[1] for c in cases], 3)
     reasons = collections.Counter()

@@ -616,11 +616,40 @@ API int stbi_jpeg_batch_timings_get(stbi_jpeg_batch *b, stbi_jpeg_batch_timings 
 /* ===================================================================================== */
 /* one-call batched decode with host buffers                                             */
 /* ===================================================================================== */
+/* marker walk up to the first scan: a progressive frame (SOF2) with no restart interval in force */
+static int looks_serial(const stbi_uc *buf, int len)
+{
+	int i = 2, progressive = 0, dri = 0;
+	if (!buf || len < 4 || buf[0] != 0xff || buf[1] != 0xd8)
+		return 0;
+	while (i + 4 <= len)
+	{
+		int m, l;
+		if (buf[i] != 0xff)
+			return 0;
+		m = buf[i + 1];
+		if (m == 0xff)
+		{
+			++i;
+			continue;
+		}
+		l = (buf[i + 2] << 8) | buf[i + 3];
+		if (m == 0xda)
+			break;
+		if (m == 0xc2)
+			progressive = 1;
+		if (m == 0xdd && l >= 4 && i + 6 <= len)
+			dri = (buf[i + 4] << 8) | buf[i + 5];
+		i += 2 + l;
+	}
+	return progressive && dri == 0;
+}
+
 API int stbi_jpeg_decode_batch(stbi_jpeg_batch *b, const stbi_uc *const *bufs, const int *lens, int count,
 										 int req_comp, stbi_uc *const *outs, const size_t *out_caps, int *xs, int *ys,
 										 int *comps, int *status)
 {
-	int done = 0, nok = 0, chunk, depth, k0;
+	int done = 0, nok = 0, chunk, depth, k0, serial;
 	stbi_jpeg_batch_timings acc;
 	if (!b || count < 0)
 		return -1;
@@ -643,8 +672,12 @@ API int stbi_jpeg_decode_batch(stbi_jpeg_batch *b, const stbi_uc *const *bufs, c
 	   PCIe) is the floor.  Three deep, not two: with two, both downloads in flight finish together and the link
 	   idles while the host prepares the next chunk (measured: 11 ms of 155 per 1024 x 1080p).  Each object
 	   downloads on its own stream: one shared FIFO download stream measured 10-20 % slower. */
+	/* Progressive files without restart markers decode one warp per scan (jpeg_entropy_prog.cuh): a chunk takes about
+	   as long as its longest scan chain however few images it holds, so such batches are not ramped or split below
+	   `chunk`.  Everything else is pipelined as soon as there are enough images to overlap anything. */
+	serial = count > 0 && looks_serial(bufs[0], lens[0]) && looks_serial(bufs[count / 2], lens[count / 2]);
 	depth = 1;
-	if (count > chunk)
+	if (count > chunk || (count >= 64 && !serial))
 	{
 		const char *dv = getenv("IMAGE_CODECS_B200_PIPE_DEPTH"); /* tuning hook */
 		depth = dv ? atoi(dv) : 3;
@@ -707,7 +740,7 @@ API int stbi_jpeg_decode_batch(stbi_jpeg_batch *b, const stbi_uc *const *bufs, c
 			if (done < count)
 			{
 				/* ramp the first chunks (16, 32, 64, ...) so the first download starts early */
-				const int want = (k < 4 && (16 << k) < chunk) ? (16 << k) : chunk;
+				const int want = (!serial && depth > 1 && k < 4 && (16 << k) < chunk) ? (16 << k) : chunk;
 				const int n = count - done < want ? count - done : want;
 				if (stbi_jpeg_batch_prepare(s, bufs + done, lens + done, n, req_comp, NULL, NULL, NULL, NULL) < 0)
 					return -1;

@@ -538,27 +538,27 @@ def test_no_kernel_writes_past_a_device_buffer(oracle, entropy_mode):
     the size the host asked for plus a 4 KB canary; after decoding the whole format matrix (all entropy paths:
     restart segments, progressive, serial and self-synchronising restart-less scans; all output kernels) and a
     set of corrupted streams, every canary must be intact and the pixels still bit-exact."""
-    os.environ["IMAGE_CODECS_B200_GUARD"] = "1"
+    os.environ["IMAGE_CODECS_B200_GUARD"] = "1"  # read whenever a context is created; decode() creates its pipeline objects lazily
     try:
         d = ic.BatchDecoder(device=0, entropy_mode=entropy_mode)
+        cases = S.small_matrix()
+        datas = [S.stream(f, w, h, k) for f, w, h, k in cases]
+        for rc in (0, 3, 4):
+            outs = d.decode(datas, rc)
+            assert d.guards_ok() == 1, f"req_comp {rc}"
+            for (f, w, h, k), data, got in zip(cases, datas, outs):
+                _check(oracle, got, data, rc, f"guard {f} {w}x{h} kind{k} req{rc}")
+        # truncated and bit-flipped entropy data must not make a kernel run off its buffers either
+        rng = np.random.default_rng(5)
+        bad = []
+        for f, w, h, k in cases[:12]:
+            raw = bytearray(S.stream(f, w, h, k))
+            cut = bytes(raw[: max(200, len(raw) * 2 // 3)])
+            for _ in range(8):
+                raw[int(rng.integers(len(raw) // 2, len(raw) - 2))] ^= 1 << int(rng.integers(0, 8))
+            bad += [cut, bytes(raw)]
+        d.decode(bad, 3)
+        assert d.guards_ok() == 1, "corrupted streams"
+        d.close()
     finally:
         del os.environ["IMAGE_CODECS_B200_GUARD"]
-    cases = S.small_matrix()
-    datas = [S.stream(f, w, h, k) for f, w, h, k in cases]
-    for rc in (0, 3, 4):
-        outs = d.decode(datas, rc)
-        assert d.guards_ok() == 1, f"req_comp {rc}"
-        for (f, w, h, k), data, got in zip(cases, datas, outs):
-            _check(oracle, got, data, rc, f"guard {f} {w}x{h} kind{k} req{rc}")
-    # truncated and bit-flipped entropy data must not make a kernel run off its buffers either
-    rng = np.random.default_rng(5)
-    bad = []
-    for f, w, h, k in cases[:12]:
-        raw = bytearray(S.stream(f, w, h, k))
-        cut = bytes(raw[: max(200, len(raw) * 2 // 3)])
-        for _ in range(8):
-            raw[int(rng.integers(len(raw) // 2, len(raw) - 2))] ^= 1 << int(rng.integers(0, 8))
-        bad += [cut, bytes(raw)]
-    d.decode(bad, 3)
-    assert d.guards_ok() == 1, "corrupted streams"
-    d.close()

@@ -414,6 +414,13 @@ __device__ __forceinline__ void ebr_checkpoint(uint32_t ring_lane, EBR &br)
 	asm volatile("cp.async.commit_group;" ::: "memory");
 }
 
+/* Additions of the symbol loop issued on the FMA pipe: the loop is bound by the ALU pipe (ncu: 73 % busy, math-pipe
+   throttle 1.3 stalls per issue) while the FMA pipe idles at 15 %.  The multiplier comes from constant memory so
+   that ptxas cannot fold the multiply-add back into an IADD3 / LEA. */
+__constant__ uint32_t c_entb_one = 1u;
+__device__ __forceinline__ uint32_t fma_add(uint32_t a, uint32_t b) { return a * c_entb_one + b; }
+__device__ __forceinline__ uint32_t fma_sub(uint32_t a, uint32_t b) { return b * (0u - c_entb_one) + a; } /* a - b */
+
 __device__ __forceinline__ uint32_t shr_clamp(uint32_t x, uint32_t n) /* n >= 32 gives 0 (PTX shr semantics) */
 {
 	uint32_t d;
@@ -431,7 +438,7 @@ __device__ __forceinline__ bool entb_symbol(uint32_t ring_lane, EBR &br, uint32_
 														  int &value, uint32_t &e, F between)
 {
 	const uint32_t top = __funnelshift_l(br.nxt, br.cur, br.bp);
-	e = lds_u16(fast_addr + ((top >> (32 - BITS)) << 1));
+	e = lds_u16(fma_add((top >> (32 - BITS)) << 1, fast_addr));
 	between();
 	if (e == 0u)
 	{
@@ -445,17 +452,17 @@ __device__ __forceinline__ bool entb_symbol(uint32_t ring_lane, EBR &br, uint32_
 	}
 	const uint32_t len = ENTB_E_LEN(e), size = ENTB_E_SIZE(e);
 	const uint32_t after = top << len;
-	const uint32_t s32 = 32u - size;
+	const uint32_t s32 = fma_sub(32u, size);
 	const uint32_t v = shr_clamp(after, s32), mask = shr_clamp(0xffffffffu, s32);
 	const int t = (int)after >> 31;
-	value = (int)v - (int)(mask & ~(uint32_t)t);
-	const uint32_t nbp = br.bp + len + size;
+	value = (int)fma_sub(v, mask & ~(uint32_t)t);
+	const uint32_t nbp = fma_add(len, br.bp) + size;
 	/* a symbol is < 32 bits: at most one word boundary.  Predicated in place: no temporary whose copy would
 	   wait for the read that was just issued. */
 	/* ring address of word nbp / 32 (the new nx2): unit (w / 4) % 4 at ENTB_RING_ROW strides, word w % 4 inside it;
 	   both fields come from bits 5..8 of nbp */
 	const uint32_t m = nbp & 0x1e0u;
-	const uint32_t ra = ring_lane + (((m >> 3) | (m << ENTB_RING_UNIT_SHIFT)) & (0xcu | (3u * ENTB_RING_ROW)));
+	const uint32_t ra = fma_add(((m >> 3) | (m << ENTB_RING_UNIT_SHIFT)) & (0xcu | (3u * ENTB_RING_ROW)), ring_lane);
 	asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %3, 0;\n\t@p mov.u32 %0, %1;\n\t@p mov.u32 %1, %2;\n\t"
 					 "@p ld.shared.u32 %2, [%4];\n\t}"
 					 : "+r"(br.cur), "+r"(br.nxt), "+r"(br.nx2)

@@ -24,6 +24,10 @@
  * `bias` is added to the four even-part sums (x0..x3 in the reference): 512 in the column pass,
  * 65536 + (128<<17) in the row pass.  Outputs are NOT yet shifted.  int32 wrap-around addition is
  * associative, so the regrouping below gives the reference's exact 32-bit values. ---- */
+/* FMA_A: the two shift-adds a0, a1 as multiply-adds whose multiplier comes from constant memory (ptxas cannot turn
+   them back into LEA): the fused kernels are bound by the ALU pipe, the FMA pipe has room */
+__constant__ int c_idct_4096 = 4096;
+template <bool FMA_A = false>
 __device__ __forceinline__ void idct_1d(int s0, int s1, int s2, int s3, int s4, int s5, int s6, int s7, int bias,
 													 int (&o)[8])
 {
@@ -31,8 +35,8 @@ __device__ __forceinline__ void idct_1d(int s0, int s1, int s2, int s3, int s4, 
 	const int z = (s2 + s6) * 2217;
 	const int e2 = z + s6 * -7567;
 	const int e3 = z + s2 * 3135;
-	const int a0 = (s0 + s4) * 4096 + bias;
-	const int a1 = (s0 - s4) * 4096 + bias;
+	const int a0 = FMA_A ? (s0 + s4) * c_idct_4096 + bias : (s0 + s4) * 4096 + bias;
+	const int a1 = FMA_A ? (s0 - s4) * c_idct_4096 + bias : (s0 - s4) * 4096 + bias;
 	/* odd part (jpeg.c:592-612) multiplied out: in the ring Z/2^32 the reference's factored butterfly
 	   (p5 = (p3+p4)*f2f(1.175875602), t0..t3 *= ..., t3 += p1+p4, ...) equals this 4x4 integer matrix,
 	   e.g. d3 = s1*(6149+4816-3685-1597) + s3*4816 + s5*(4816-1597) + s7*(4816-3685); 16 multiply-adds, no adds */

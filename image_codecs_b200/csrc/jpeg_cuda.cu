@@ -906,3 +906,78 @@ extern "C" int jcu_read_coefs(jcu_ctx *c, size_t elem_off, size_t elems, int16_t
 	}
 	return 0;
 }
+
+/* ---- allocation-free stage entry point (include/jpeg_cuda_abi.h: jcu_idct_blocks_noalloc) ----
+ * jcu_test_idct_blocks keeps its slab-layout copy of the input blocks in a cudaMalloc'ed scratch buffer.  Callers
+ * that may not allocate (CUDA graph capture, serving loops) get the same kernel over a scratch slab that lives in
+ * this file-scope device array: every GPU that loads the library holds its 4 MiB until exit. */
+#include <pthread.h>
+static __device__ __align__(256) int16_t g_noalloc_slab[(size_t)JCU_NOALLOC_MAX_BLOCKS * 64];
+
+#define JCU_NOALLOC_MAX_DEVICES 64
+/* In host code `g_noalloc_slab` is only a handle for the runtime, not a device address: the address each device
+   gave its copy of the array is looked up once per device (with that device current) and kept here. */
+static int16_t *g_noalloc_ptr[JCU_NOALLOC_MAX_DEVICES];
+static pthread_mutex_t g_noalloc_mu = PTHREAD_MUTEX_INITIALIZER;
+
+static cudaError_t noalloc_slab_address(int device, int16_t **out)
+{
+	*out = nullptr;
+	if (device < 0 || device >= JCU_NOALLOC_MAX_DEVICES)
+		return cudaErrorInvalidDevice;
+	cudaError_t e = cudaSuccess;
+	pthread_mutex_lock(&g_noalloc_mu);
+	if (!g_noalloc_ptr[device])
+	{
+		void *p = nullptr;
+		e = cudaGetSymbolAddress(&p, g_noalloc_slab); /* the caller made `device` current */
+		if (e == cudaSuccess && !p)
+			e = cudaErrorInvalidSymbol;
+		if (e == cudaSuccess)
+			g_noalloc_ptr[device] = (int16_t *)p;
+	}
+	*out = g_noalloc_ptr[device];
+	pthread_mutex_unlock(&g_noalloc_mu);
+	return e;
+}
+
+/* natural-order blocks (caller's memory) -> slab layout (jpeg_coef_layout.cuh) in the scratch: one 16-byte chunk
+   (= one coefficient row) per thread.  Every chunk of blocks [0, n) is rewritten, so nothing a previous call
+   left in the scratch is ever read and nothing needs clearing. */
+__global__ void k_noalloc_stage(const uint4 *__restrict__ in, int16_t *slab, int n)
+{
+	const int g = blockIdx.x * blockDim.x + threadIdx.x;
+	if (g >= n * 8)
+		return;
+	const int b = g >> 3, r = g & 7;
+	int16_t *blk = slab + (size_t)b * 64;
+	reinterpret_cast<uint4 *>(blk)[r ^ (int)coef_key(blk)] = in[g];
+}
+
+extern "C" int jcu_idct_blocks_noalloc(jcu_ctx *c, const int16_t *d_coef, const uint16_t *d_qt, int nblocks, uint8_t *d_out64,
+													void *stream)
+{
+	if (!c)
+		return (int)cudaErrorInvalidValue;
+	if (nblocks < 0 || nblocks > JCU_NOALLOC_MAX_BLOCKS)
+	{
+		snprintf(c->errstr, sizeof(c->errstr), "jcu_idct_blocks_noalloc: %d blocks exceed the scratch of JCU_NOALLOC_MAX_BLOCKS = %d blocks",
+					nblocks, JCU_NOALLOC_MAX_BLOCKS);
+		return (int)cudaErrorInvalidValue;
+	}
+	if (nblocks == 0)
+		return 0;
+	if (!d_coef || !d_qt || !d_out64 || ((uintptr_t)d_coef & 15) || ((uintptr_t)d_qt & 1) || ((uintptr_t)d_out64 & 3))
+	{
+		snprintf(c->errstr, sizeof(c->errstr), "jcu_idct_blocks_noalloc: null or misaligned device pointer (coef 16, qt 2, out 4 bytes)");
+		return (int)cudaErrorInvalidValue;
+	}
+	CK(cudaSetDevice(c->device));
+	int16_t *slab = nullptr;
+	CK(noalloc_slab_address(c->device, &slab));
+	cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
+	k_noalloc_stage<<<(nblocks * 8 + 255) / 256, 256, 0, st>>>(reinterpret_cast<const uint4 *>(d_coef), slab, nblocks);
+	k_test_idct<<<(nblocks + 63) / 64, 64, 0, st>>>(slab, d_qt, nblocks, d_out64);
+	CK(cudaGetLastError());
+	return 0;
+}

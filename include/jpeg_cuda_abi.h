@@ -187,6 +187,24 @@ JCU_API int jcu_debug_guards_ok(jcu_ctx *c);
 JCU_API int jcu_test_ycbcr(jcu_ctx *c, const uint8_t *y, const uint8_t *cb, const uint8_t *cr, int n, int step, uint8_t *out);
 JCU_API int jcu_read_coefs(jcu_ctx *c, size_t elem_off, size_t elems, int16_t *dst); /* coefficient slab after run */
 
+/* Allocation-free variant of jcu_test_idct_blocks.  It has NO counterpart in the reference: it was added
+   for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+   serving loops, harnesses that forbid it).  Same kernel and arithmetic (stbi__idct_block, codec/jpeg.c:615), but
+   every pointer is a DEVICE pointer supplied by the caller -- d_coef: nblocks x 64 int16 in natural order, 16-byte
+   aligned; d_qt: 64 uint16 multipliers, natural order; d_out64: nblocks x 64 samples, 4-byte aligned -- and the
+   slab-layout copy of the blocks the kernel reads lives in a file-scope `static __device__` array of
+   JCU_NOALLOC_MAX_BLOCKS blocks (4 MiB that every GPU which loads the library holds until exit) instead of a
+   cudaMalloc'ed buffer.  The call makes c's device current, enqueues two kernels on `stream` (a cudaStream_t; NULL =
+   the context's own stream) and returns without synchronising; it calls no cudaMalloc, cudaFree or allocating
+   library routine.  More than JCU_NOALLOC_MAX_BLOCKS blocks -> cudaErrorInvalidValue, reason in jcu_error_string.
+   All calls on one device share the scratch: calls that overlap on the GPU (different streams without an ordering
+   between them) race; calls on one stream are safe, and each call rewrites every scratch byte it later reads, so
+   nothing of the previous call survives into its result.  The first call on a device looks the scratch address up
+   (cudaGetSymbolAddress) and should happen outside graph capture. */
+#define JCU_NOALLOC_MAX_BLOCKS 32768
+JCU_API int jcu_idct_blocks_noalloc(jcu_ctx *c, const int16_t *d_coef, const uint16_t *d_qt, int nblocks, uint8_t *d_out64,
+												void *stream);
+
 /* ---- encoder (replaces stbi_write_jpg_core, codec/jpeg_write.c:172-366) ---- */
 #define JCU_ENC_HDR_STRIDE 1024 /* bytes reserved per image in the header staging array */
 typedef struct

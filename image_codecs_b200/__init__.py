@@ -9,6 +9,7 @@ There is no CPU decode path: if the library is missing, or no CUDA device is usa
 """
 from .api import (  # noqa: F401
     BatchDecoder,
+    MultiDecoder,
     LibraryMissing,
     cuda_device_count,
     encode_batch,
@@ -24,6 +25,6 @@ from .api import (  # noqa: F401
 )
 
 __all__ = [
-    "BatchDecoder", "LibraryMissing", "cuda_device_count", "encode_batch", "write_jpg_to_bytes", "failure_reason", "inspect", "lib", "lib_path",
+    "BatchDecoder", "MultiDecoder", "LibraryMissing", "cuda_device_count", "encode_batch", "write_jpg_to_bytes", "failure_reason", "inspect", "lib", "lib_path",
     "set_flip_vertically_on_load", "stbi_info_from_memory", "stbi_load", "stbi_load_from_memory",
 ]

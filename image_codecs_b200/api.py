@@ -24,7 +24,9 @@ def lib_path() -> str:
 
 class Params(C.Structure):
     _fields_ = [("device", C.c_int), ("host_threads", C.c_int), ("chunk_images", C.c_int), ("profile", C.c_int),
-                ("entropy_mode", C.c_int), ("reserved", C.c_int * 7)]
+                ("entropy_mode", C.c_int), ("pipeline_depth", C.c_int), ("device_mem_mb", C.c_int),
+                ("no_download_merge", C.c_int), ("trace", C.c_int), ("force_generic", C.c_int),
+                ("rows_per_band", C.c_int), ("debug_guards", C.c_int)]
 
 
 class Timings(C.Structure):
@@ -108,6 +110,17 @@ def lib() -> C.CDLL:
     L.jcu_read_coefs.argtypes = [C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p]
     L.jcu_error_string.restype = C.c_char_p
     L.jcu_error_string.argtypes = [C.c_void_p]
+    L.stbi_jpeg_multi_create.restype = C.c_void_p
+    L.stbi_jpeg_multi_create.argtypes = [ip, C.c_int, C.POINTER(Params)]
+    L.stbi_jpeg_multi_destroy.argtypes = [C.c_void_p]
+    L.stbi_jpeg_multi_device_count.restype = C.c_int
+    L.stbi_jpeg_multi_device_count.argtypes = [C.c_void_p]
+    L.stbi_jpeg_multi_last_split.restype = C.c_int
+    L.stbi_jpeg_multi_last_split.argtypes = [C.c_void_p, ip, C.c_int]
+    L.stbi_jpeg_decode_batch_multi.restype = C.c_int
+    L.stbi_jpeg_decode_batch_multi.argtypes = [C.c_void_p, pp, ip, C.c_int, C.c_int, pp, C.POINTER(C.c_size_t), ip, ip, ip,
+                                               ip]
+    L.stbi_jpeg_set_default_device.argtypes = [C.c_int]
     _lib = L
     return L
 
@@ -241,10 +254,16 @@ class BatchDecoder:
     """stbi_jpeg_batch_* (include/image_api.h): one object drives one device."""
 
     def __init__(self, device: int = 0, host_threads: int = 0, chunk_images: int = 0, profile: bool = True,
-                 entropy_mode: int = 0):
+                 entropy_mode: int = 0, **tuning):
+        """tuning: pipeline_depth, device_mem_mb, no_download_merge, trace, force_generic, rows_per_band, debug_guards
+        (stbi_jpeg_batch_params in include/image_api.h)."""
         p = Params()
         p.device, p.host_threads, p.chunk_images, p.profile, p.entropy_mode = (device, host_threads, chunk_images,
                                                                                int(profile), entropy_mode)
+        for k, v in tuning.items():
+            if k not in dict(Params._fields_):
+                raise TypeError(f"unknown batch parameter {k}")
+            setattr(p, k, int(v))
         self._h = lib().stbi_jpeg_batch_create(C.byref(p))
         if not self._h:
             raise RuntimeError(f"stbi_jpeg_batch_create failed: {failure_reason()} (no CPU fallback exists)")
@@ -365,3 +384,63 @@ class BatchDecoder:
     def decode_into(self, bufs, lens, n, req_comp, outs, caps, xs=None, ys=None, cs=None, st=None) -> int:
         """Raw pointer form for bench.py: ctypes arrays prepared by the caller (pinned buffers)."""
         return lib().stbi_jpeg_decode_batch(self._h, bufs, lens, n, req_comp, outs, caps, xs, ys, cs, st)
+
+
+class MultiDecoder:
+    """stbi_jpeg_multi_* (include/image_api.h): every listed device behind one call, split and threaded in C."""
+
+    def __init__(self, devices: Optional[Sequence[int]] = None, host_threads: int = 0, chunk_images: int = 0, **tuning):
+        p = Params()
+        p.host_threads, p.chunk_images = host_threads, chunk_images
+        for k, v in tuning.items():
+            setattr(p, k, int(v))
+        if devices is None:
+            self._h = lib().stbi_jpeg_multi_create(None, 0, C.byref(p))
+        else:
+            arr = (C.c_int * len(devices))(*devices)
+            self._h = lib().stbi_jpeg_multi_create(arr, len(devices), C.byref(p))
+        if not self._h:
+            raise RuntimeError(f"stbi_jpeg_multi_create failed: {failure_reason()} (no CPU fallback exists)")
+        self.n_devices = lib().stbi_jpeg_multi_device_count(self._h)
+
+    def close(self):
+        if self._h:
+            lib().stbi_jpeg_multi_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def last_split(self) -> List[int]:
+        first = (C.c_int * (self.n_devices + 1))()
+        lib().stbi_jpeg_multi_last_split(self._h, first, self.n_devices + 1)
+        return list(first)
+
+    def decode(self, streams: Sequence, req_comp: int = 0) -> List[Optional[np.ndarray]]:
+        n = len(streams)
+        bufs, lens, keep = BatchDecoder._inputs(streams)
+        xs, ys, cs, st = ((C.c_int * n)() for _ in range(4))
+        rc = lib().stbi_jpeg_decode_batch_multi(self._h, bufs, lens, n, req_comp, None, None, xs, ys, cs, st)
+        if rc < 0:
+            raise RuntimeError(f"stbi_jpeg_decode_batch_multi (sizing) failed: {failure_reason()}")
+        outs = (C.c_void_p * n)()
+        caps = (C.c_size_t * n)()
+        arrays: List[Optional[np.ndarray]] = []
+        for i in range(n):
+            if st[i] == 1:
+                ch = req_comp if req_comp else cs[i]
+                a = np.empty((ys[i], xs[i], ch), dtype=np.uint8)
+                outs[i], caps[i] = a.ctypes.data, a.nbytes
+                arrays.append(a)
+            else:
+                arrays.append(None)
+        rc = lib().stbi_jpeg_decode_batch_multi(self._h, bufs, lens, n, req_comp, outs, caps, xs, ys, cs, st)
+        if rc < 0:
+            raise RuntimeError(f"stbi_jpeg_decode_batch_multi failed: {failure_reason()}")
+        return [a if st[i] == 1 else None for i, a in enumerate(arrays)]
+
+    def decode_into(self, bufs, lens, n, req_comp, outs, caps, xs=None, ys=None, cs=None, st=None) -> int:
+        return lib().stbi_jpeg_decode_batch_multi(self._h, bufs, lens, n, req_comp, outs, caps, xs, ys, cs, st)

@@ -59,12 +59,29 @@ static double now_ms(void)
 /* ===================================================================================== */
 /* batch object                                                                          */
 /* ===================================================================================== */
+/* persistent marker-parser workers, shared by a batch object and the further objects of its chunk pipeline (one
+   chunk is parsed at a time); created on first use, joined when the owning object is destroyed */
+struct parse_job;
+typedef struct
+{
+	pthread_t th[64];
+	int n;
+	pthread_mutex_t mu;
+	pthread_cond_t cv_work, cv_done;
+	unsigned gen;
+	int pending, stop, active; /* active: workers that take part in the current job (tids 0..active-1) */
+	const struct parse_job *job;
+} parse_pool;
+
 struct stbi_jpeg_batch
 {
 	stbi_jpeg_batch_params params;
 	jcu_ctx *ctx;
 	int nthreads;
-	int force_generic; /* IMAGE_CODECS_B200_FORCE_GENERIC=1: route every image through the two-pass path (tests) */
+	int force_generic; /* params.force_generic: route every image through the two-pass path (tests) */
+	parse_pool *pool;	 /* owned by the root object; pipeline objects point at their root's */
+	int pool_owner;
+	size_t mem_budget; /* device bytes one prepared chunk may need (coefficients + planes + pixels + bitstreams) */
 
 	/* prepared batch */
 	int count, req_comp;
@@ -112,9 +129,11 @@ static const char *dev_reason(int word)
 
 API int stbi_jpeg_cuda_device_count(void) { return jcu_device_count(); }
 
-API stbi_jpeg_batch *stbi_jpeg_batch_create(const stbi_jpeg_batch_params *params)
+static stbi_jpeg_batch *batch_create_with_pool(const stbi_jpeg_batch_params *params, parse_pool *shared)
 {
 	stbi_jpeg_batch *b;
+	jcu_ctx_options o;
+	size_t free_b = 0, total_b = 0;
 	int rc;
 	if (jcu_device_count() < 1)
 		return (stbi_jpeg_batch *)err_null("no cuda device");
@@ -125,18 +144,33 @@ API stbi_jpeg_batch *stbi_jpeg_batch_create(const stbi_jpeg_batch_params *params
 		b->params = *params;
 	b->nthreads = b->params.host_threads > 0 ? b->params.host_threads : online_cpus();
 	if (b->nthreads > 64) b->nthreads = 64;
-	{
-		const char *fg = getenv("IMAGE_CODECS_B200_FORCE_GENERIC");
-		b->force_generic = fg && fg[0] == '1';
-	}
-	rc = jcu_ctx_create(b->params.device, b->params.profile, b->params.entropy_mode, &b->ctx);
+	b->force_generic = b->params.force_generic != 0;
+	b->pool = shared;
+	memset(&o, 0, sizeof(o));
+	o.device = b->params.device;
+	o.profile = b->params.profile;
+	o.entropy_mode = b->params.entropy_mode;
+	o.force_generic = b->force_generic;
+	o.rows_per_band = b->params.rows_per_band;
+	o.guard = b->params.debug_guards;
+	rc = jcu_ctx_create_opts(&o, &b->ctx);
 	if (rc != 0)
 	{
 		free(b);
 		return (stbi_jpeg_batch *)err_null("cuda context");
 	}
+	/* what one prepared chunk may ask of the device: the caller's figure, else most of the device for the staged
+	   calls (stbi_jpeg_decode_batch narrows it to a share per pipeline object) */
+	if (b->params.device_mem_mb > 0)
+		b->mem_budget = (size_t)b->params.device_mem_mb << 20;
+	else if (jcu_mem_info(b->params.device, &free_b, &total_b) == 0 && total_b)
+		b->mem_budget = total_b / 10 * 9;
+	else
+		b->mem_budget = (size_t)16 << 30;
 	return b;
 }
+
+API stbi_jpeg_batch *stbi_jpeg_batch_create(const stbi_jpeg_batch_params *params) { return batch_create_with_pool(params, NULL); }
 
 static void batch_release_results(stbi_jpeg_batch *b)
 {
@@ -145,6 +179,8 @@ static void batch_release_results(stbi_jpeg_batch *b)
 		jp_result_free(&b->res[i]);
 	b->count = 0;
 }
+
+static void pool_destroy(parse_pool *pl);
 
 API void stbi_jpeg_batch_destroy(stbi_jpeg_batch *b)
 {
@@ -156,6 +192,8 @@ API void stbi_jpeg_batch_destroy(stbi_jpeg_batch *b)
 			if (b->pipe[pi])
 				stbi_jpeg_batch_destroy(b->pipe[pi]);
 	}
+	if (b->pool_owner)
+		pool_destroy(b->pool);
 	batch_release_results(b);
 	jcu_ctx_destroy(b->ctx);
 	jcu_host_free(b->slab);
@@ -169,21 +207,20 @@ API void stbi_jpeg_batch_destroy(stbi_jpeg_batch *b)
 }
 
 /* ---- threaded parse: each worker copies its files into the pinned slab and parses them there ---- */
-typedef struct
+typedef struct parse_job
 {
 	stbi_jpeg_batch *b;
 	const stbi_uc *const *bufs;
 	const int *lens;
 	const size_t *offs;
-	int tid, nthreads;
+	int nthreads;
 } parse_job;
 
-static void *parse_worker(void *arg)
+static void parse_share(const parse_job *j, int tid)
 {
-	parse_job *j = (parse_job *)arg;
 	stbi_jpeg_batch *b = j->b;
 	int i;
-	for (i = j->tid; i < b->count; i += j->nthreads)
+	for (i = tid; i < b->count; i += j->nthreads)
 	{
 		jp_result *r = &b->res[i];
 		size_t len = j->lens[i] > 0 ? (size_t)j->lens[i] : 0;
@@ -214,17 +251,113 @@ static void *parse_worker(void *arg)
 				}
 		}
 	}
+}
+
+typedef struct
+{
+	parse_pool *pl;
+	int tid;
+} pool_arg;
+
+static void *pool_main(void *arg)
+{
+	pool_arg a = *(pool_arg *)arg;
+	parse_pool *pl = a.pl;
+	unsigned seen = 0;
+	free(arg);
+	pthread_mutex_lock(&pl->mu);
+	for (;;)
+	{
+		const parse_job *job;
+		while (!pl->stop && pl->gen == seen)
+			pthread_cond_wait(&pl->cv_work, &pl->mu);
+		if (pl->stop)
+			break;
+		seen = pl->gen;
+		if (a.tid >= pl->active)
+			continue;
+		job = pl->job;
+		pthread_mutex_unlock(&pl->mu);
+		parse_share(job, a.tid);
+		pthread_mutex_lock(&pl->mu);
+		if (--pl->pending == 0)
+			pthread_cond_signal(&pl->cv_done);
+	}
+	pthread_mutex_unlock(&pl->mu);
 	return NULL;
 }
 
+static parse_pool *pool_create(int n)
+{
+	parse_pool *pl = (parse_pool *)calloc(1, sizeof(*pl));
+	int i;
+	if (!pl)
+		return NULL;
+	pthread_mutex_init(&pl->mu, NULL);
+	pthread_cond_init(&pl->cv_work, NULL);
+	pthread_cond_init(&pl->cv_done, NULL);
+	for (i = 0; i < n && i < 64; ++i)
+	{
+		pool_arg *a = (pool_arg *)malloc(sizeof(*a));
+		if (!a)
+			break;
+		a->pl = pl;
+		a->tid = i;
+		if (pthread_create(&pl->th[i], NULL, pool_main, a) != 0)
+		{
+			free(a);
+			break;
+		}
+		pl->n = i + 1;
+	}
+	return pl;
+}
+
+static void pool_destroy(parse_pool *pl)
+{
+	int i;
+	if (!pl)
+		return;
+	pthread_mutex_lock(&pl->mu);
+	pl->stop = 1;
+	pthread_cond_broadcast(&pl->cv_work);
+	pthread_mutex_unlock(&pl->mu);
+	for (i = 0; i < pl->n; ++i)
+		pthread_join(pl->th[i], NULL);
+	pthread_cond_destroy(&pl->cv_work);
+	pthread_cond_destroy(&pl->cv_done);
+	pthread_mutex_destroy(&pl->mu);
+	free(pl);
+}
+
+/* run one parse job on `nt` pool workers and wait for it */
+static void pool_run(parse_pool *pl, parse_job *job, int nt)
+{
+	pthread_mutex_lock(&pl->mu);
+	job->nthreads = nt;
+	pl->job = job;
+	pl->active = nt;
+	pl->pending = nt;
+	++pl->gen;
+	pthread_cond_broadcast(&pl->cv_work);
+	while (pl->pending > 0)
+		pthread_cond_wait(&pl->cv_done, &pl->mu);
+	pthread_mutex_unlock(&pl->mu);
+}
+
+/* NULL on allocation failure (the old array is freed by the caller's destroy path) */
 static void *grow_buf(void *p, size_t *cap, size_t need, size_t elem)
 {
 	if (need > *cap)
 	{
 		size_t nc = *cap ? *cap : 64;
+		void *np;
 		while (nc < need)
 			nc *= 2;
-		p = realloc(p, nc * elem);
+		np = realloc(p, nc * elem);
+		if (!np)
+			return NULL;
+		p = np;
 		*cap = nc;
 	}
 	return p;
@@ -232,8 +365,30 @@ static void *grow_buf(void *p, size_t *cap, size_t need, size_t elem)
 
 #define ALIGN_UP(x, a) (((x) + ((a)-1)) & ~((size_t)(a)-1))
 
-/* parse `count` streams into b->res (threaded) and stage them in the pinned slab */
-static int batch_parse(stbi_jpeg_batch *b, const stbi_uc *const *bufs, const int *lens, int count, int req_comp)
+/* device bytes image r asks for: coefficient blocks of all frame components, sample planes on the generic path,
+   packed pixels, and its file twice (bitstream slab + unstuffed copy) */
+static size_t image_device_bytes(const jp_result *r, size_t file_len)
+{
+	const jcu_image *im = &r->img;
+	size_t n = 0;
+	int k;
+	for (k = 0; k < im->ncomp; ++k)
+	{
+		const size_t blocks = (size_t)im->comp[k].bw * (size_t)im->comp[k].bh;
+		n += blocks * 128;
+		if (k < im->decode_n && im->path == JCU_PATH_GENERIC)
+			n += blocks * 64;
+	}
+	n += ALIGN_UP((size_t)im->n_out * (size_t)im->width * (size_t)im->height, 256);
+	return n + 2 * file_len + 4096;
+}
+
+/* Parse `count` streams into b->res (threaded) and stage them in the pinned slab.  The chunk is cut where its
+   images would ask the device for more than b->mem_budget bytes: with allow_defer the images behind the cut are
+   left for the caller's next chunk (b->count says how many were taken, at least one), without it they fail
+   alone with "outofmem"; an image that exceeds the budget all by itself fails alone either way -- the reference
+   fails it through its own malloc (jpeg.c:1643, 2297), the others of the batch decode. */
+static int batch_parse(stbi_jpeg_batch *b, const stbi_uc *const *bufs, const int *lens, int count, int req_comp, int allow_defer)
 {
 	size_t *offs, total = 0;
 	int i, nt;
@@ -241,15 +396,28 @@ static int batch_parse(stbi_jpeg_batch *b, const stbi_uc *const *bufs, const int
 	batch_release_results(b);
 	if (count > b->cap_res)
 	{
-		b->res = (jp_result *)realloc(b->res, sizeof(jp_result) * (size_t)count);
-		b->dev_err = (int *)realloc(b->dev_err, sizeof(int) * (size_t)count);
+		jp_result *nr = (jp_result *)realloc(b->res, sizeof(jp_result) * (size_t)count);
+		int *ne;
+		if (nr)
+			b->res = nr;
+		ne = (int *)realloc(b->dev_err, sizeof(int) * (size_t)count);
+		if (ne)
+			b->dev_err = ne;
+		if (!nr || !ne)
+			return err_zero("outofmem");
 		b->cap_res = count;
 	}
-	memset(b->res, 0, sizeof(jp_result) * (size_t)count);
+	if (count > 0)
+		memset(b->res, 0, sizeof(jp_result) * (size_t)count);
 	b->count = count;
 	b->req_comp = req_comp;
 	b->dev_err_valid = 0;
 	offs = (size_t *)malloc(sizeof(size_t) * (size_t)(count + 1));
+	if (!offs)
+	{
+		b->count = 0;
+		return err_zero("outofmem");
+	}
 	for (i = 0; i < count; ++i)
 	{
 		offs[i] = total;
@@ -273,23 +441,17 @@ static int batch_parse(stbi_jpeg_batch *b, const stbi_uc *const *bufs, const int
 
 	nt = b->nthreads;
 	if (nt > count) nt = count;
-	if (nt <= 1)
 	{
-		parse_job j = {b, bufs, lens, offs, 0, 1};
-		parse_worker(&j);
-	}
-	else
-	{
-		pthread_t th[64];
-		parse_job jobs[64];
-		for (i = 0; i < nt; ++i)
+		parse_job j = {b, bufs, lens, offs, 1};
+		if (nt > 1 && !b->pool)
 		{
-			parse_job j = {b, bufs, lens, offs, i, nt};
-			jobs[i] = j;
-			pthread_create(&th[i], NULL, parse_worker, &jobs[i]);
+			b->pool = pool_create(b->nthreads);
+			b->pool_owner = b->pool != NULL;
 		}
-		for (i = 0; i < nt; ++i)
-			pthread_join(th[i], NULL);
+		if (nt > 1 && b->pool && b->pool->n > 1)
+			pool_run(b->pool, &j, nt < b->pool->n ? nt : b->pool->n);
+		else
+			parse_share(&j, 0);
 	}
 	if (req_comp < 0 || req_comp > 4)
 		for (i = 0; i < count; ++i)
@@ -300,11 +462,46 @@ static int batch_parse(stbi_jpeg_batch *b, const stbi_uc *const *bufs, const int
 				b->res[i].reason = "bad req_comp";
 			}
 
+	/* ---- device memory budget: cut the chunk, or fail the images that do not fit ---- */
+	{
+		size_t used = 0;
+		int taken = 0;
+		for (i = 0; i < count; ++i)
+		{
+			jp_result *r = &b->res[i];
+			size_t need;
+			if (!r->ok)
+				continue;
+			need = image_device_bytes(r, (size_t)(lens[i] > 0 ? lens[i] : 0));
+			if (need > b->mem_budget || (!allow_defer && used + need > b->mem_budget))
+			{
+				jp_result_free(r);
+				r->ok = 0;
+				r->reason = "outofmem";
+				continue;
+			}
+			if (used + need > b->mem_budget && taken > 0)
+				break; /* allow_defer: this image and everything behind it go into the caller's next chunk */
+			used += need;
+			++taken;
+		}
+		if (i < count)
+		{
+			int k;
+			for (k = i; k < count; ++k)
+				jp_result_free(&b->res[k]);
+			count = i;
+			b->count = count;
+			b->slab_bytes = offs[count];
+		}
+	}
+
 	/* ---- merge into batch-wide descriptor arrays ---- */
 	{
 		size_t ns = 0, ng = 0, nh = 0, coef = 0, planes = 0, outb = 0;
 		double bits = 0, cbytes = 0;
 		int waves = 0, clear = 0;
+		void *g0, *g1, *g2, *g3;
 		for (i = 0; i < count; ++i)
 			if (b->res[i].ok)
 			{
@@ -312,10 +509,20 @@ static int batch_parse(stbi_jpeg_batch *b, const stbi_uc *const *bufs, const int
 				ng += (size_t)b->res[i].nsegs;
 				nh += (size_t)b->res[i].nhuff;
 			}
-		b->images = (jcu_image *)grow_buf(b->images, &b->cap_images, (size_t)count + 1, sizeof(jcu_image));
-		b->scans = (jcu_scan *)grow_buf(b->scans, &b->cap_scans, ns + 1, sizeof(jcu_scan));
-		b->segs = (uint32_t *)grow_buf(b->segs, &b->cap_segs, ng + 1, sizeof(uint32_t));
-		b->huff = (jcu_huff_spec *)grow_buf(b->huff, &b->cap_huff, nh + 1, sizeof(jcu_huff_spec));
+		g0 = grow_buf(b->images, &b->cap_images, (size_t)count + 1, sizeof(jcu_image));
+		if (g0) b->images = (jcu_image *)g0;
+		g1 = grow_buf(b->scans, &b->cap_scans, ns + 1, sizeof(jcu_scan));
+		if (g1) b->scans = (jcu_scan *)g1;
+		g2 = grow_buf(b->segs, &b->cap_segs, ng + 1, sizeof(uint32_t));
+		if (g2) b->segs = (uint32_t *)g2;
+		g3 = grow_buf(b->huff, &b->cap_huff, nh + 1, sizeof(jcu_huff_spec));
+		if (g3) b->huff = (jcu_huff_spec *)g3;
+		if (!g0 || !g1 || !g2 || !g3)
+		{
+			free(offs);
+			batch_release_results(b);
+			return err_zero("outofmem");
+		}
 		b->flip = g_flip_on_load != 0;
 		ns = ng = nh = 0;
 		for (i = 0; i < count; ++i)
@@ -369,7 +576,9 @@ static int batch_parse(stbi_jpeg_batch *b, const stbi_uc *const *bufs, const int
 			nh += (size_t)r->nhuff;
 			for (s = 0; s < r->nscans; ++s)
 				if (r->scans[s].wave + 1 > waves) waves = r->scans[s].wave + 1;
-			if (im->progressive) clear = 1;
+			/* the slab is reused from batch to batch: blocks that no scan of this image writes (progressive files
+			   accumulate; baseline files that lost a restart marker or a whole component) must start at zero */
+			if (im->progressive || r->needs_clear) clear = 1;
 			bits += r->entropy_bytes * 8.0;
 			cbytes += 128.0 * (double)r->coef_blocks;
 		}
@@ -407,17 +616,11 @@ static void batch_report(stbi_jpeg_batch *b, int *xs, int *ys, int *comps, int *
 	}
 }
 
-API int stbi_jpeg_batch_prepare(stbi_jpeg_batch *b, const stbi_uc *const *bufs, const int *lens, int count,
-										  int req_comp, int *xs, int *ys, int *comps, int *status)
+static int batch_upload(stbi_jpeg_batch *b)
 {
 	jcu_batch jb;
-	int i, nok = 0;
-	if (!b || count < 0)
-		return -1;
-	if (!batch_parse(b, bufs, lens, count, req_comp))
-		return -1;
 	memset(&jb, 0, sizeof(jb));
-	jb.n_images = count;
+	jb.n_images = b->count;
 	jb.images = b->images;
 	jb.n_scans = b->n_scans;
 	jb.scans = b->scans;
@@ -433,10 +636,20 @@ API int stbi_jpeg_batch_prepare(stbi_jpeg_batch *b, const stbi_uc *const *bufs, 
 	jb.n_waves = b->n_waves;
 	jb.need_coef_clear = b->need_clear;
 	if (jcu_upload(b->ctx, &jb) != 0)
-	{
-		err_zero("outofmem"); /* device allocation or copy failed: see jcu_error_string */
+		return err_zero("outofmem"); /* device allocation or copy failed: see jcu_error_string */
+	return 1;
+}
+
+API int stbi_jpeg_batch_prepare(stbi_jpeg_batch *b, const stbi_uc *const *bufs, const int *lens, int count,
+										  int req_comp, int *xs, int *ys, int *comps, int *status)
+{
+	int i, nok = 0;
+	if (!b || count < 0)
 		return -1;
-	}
+	if (!batch_parse(b, bufs, lens, count, req_comp, 0))
+		return -1;
+	if (!batch_upload(b))
+		return -1;
 	batch_report(b, xs, ys, comps, status);
 	for (i = 0; i < count; ++i)
 		nok += b->res[i].ok;
@@ -533,8 +746,7 @@ static void batch_enqueue_fetch_all(stbi_jpeg_batch *b, int n, stbi_uc *const *o
 	size_t run_src = 0, run_bytes = 0;
 	stbi_uc *run_dst = NULL;
 	int i;
-	const char *mg = getenv("IMAGE_CODECS_B200_DL_MERGE"); /* tuning hook */
-	const int merge = !(mg && mg[0] == '0');
+	const int merge = !b->params.no_download_merge;
 	for (i = 0; i < n; ++i)
 	{
 		const jcu_image *im = &b->images[i];
@@ -645,19 +857,37 @@ static int looks_serial(const stbi_uc *buf, int len)
 	return progressive && dri == 0;
 }
 
+/* a chunk that could not be prepared or launched: its images fail alone, the batch goes on */
+static void report_chunk_failed(int first, int n, int *xs, int *ys, int *comps, int *status)
+{
+	int i;
+	for (i = first; i < first + n; ++i)
+	{
+		if (xs) xs[i] = 0;
+		if (ys) ys[i] = 0;
+		if (comps) comps[i] = 0;
+		if (status) status[i] = STBI_JPEG_FAILED;
+	}
+}
+
 API int stbi_jpeg_decode_batch(stbi_jpeg_batch *b, const stbi_uc *const *bufs, const int *lens, int count,
 										 int req_comp, stbi_uc *const *outs, const size_t *out_caps, int *xs, int *ys,
 										 int *comps, int *status)
 {
-	int done = 0, nok = 0, chunk, depth, k0, serial;
+	int done = 0, nok = 0, chunk, depth, k0, serial, broken = 0;
 	stbi_jpeg_batch_timings acc;
 	if (!b || count < 0)
 		return -1;
 	memset(&acc, 0, sizeof(acc));
 	if (!outs)
 	{
-		/* sizing pass: host parse only */
-		if (!batch_parse(b, bufs, lens, count, req_comp))
+		/* sizing pass: host parse only (no device memory is asked for, so nothing is cut or failed for its size) */
+		const size_t keep = b->mem_budget;
+		int ok;
+		b->mem_budget = (size_t)-1;
+		ok = batch_parse(b, bufs, lens, count, req_comp, 0);
+		b->mem_budget = keep;
+		if (!ok)
 			return -1;
 		batch_report(b, xs, ys, comps, status);
 		for (done = 0; done < count; ++done)
@@ -679,15 +909,18 @@ API int stbi_jpeg_decode_batch(stbi_jpeg_batch *b, const stbi_uc *const *bufs, c
 	depth = 1;
 	if (count > chunk || (count >= 64 && !serial))
 	{
-		const char *dv = getenv("IMAGE_CODECS_B200_PIPE_DEPTH"); /* tuning hook */
-		depth = dv ? atoi(dv) : 3;
-		if (depth < 1) depth = 1;
+		depth = b->params.pipeline_depth > 0 ? b->params.pipeline_depth : 3;
 		if (depth > STBI_JPEG_PIPE_MAX) depth = STBI_JPEG_PIPE_MAX;
 		for (k0 = 0; k0 < depth - 1; ++k0)
 			if (!b->pipe[k0])
 			{
 				stbi_jpeg_batch_params pp = b->params;
-				b->pipe[k0] = stbi_jpeg_batch_create(&pp);
+				if (!b->pool && b->nthreads > 1)
+				{
+					b->pool = pool_create(b->nthreads);
+					b->pool_owner = b->pool != NULL;
+				}
+				b->pipe[k0] = batch_create_with_pool(&pp, b->pool);
 				if (!b->pipe[k0])
 				{
 					depth = k0 + 1;
@@ -697,13 +930,21 @@ API int stbi_jpeg_decode_batch(stbi_jpeg_batch *b, const stbi_uc *const *bufs, c
 	}
 	{
 		stbi_jpeg_batch *obj[STBI_JPEG_PIPE_MAX];
+		size_t keep_budget[STBI_JPEG_PIPE_MAX];
 		int pend_first[STBI_JPEG_PIPE_MAX] = {-1, -1, -1, -1}, pend_n[STBI_JPEG_PIPE_MAX] = {0, 0, 0, 0}, k = 0, pending = 0;
-		const int trace = getenv("IMAGE_CODECS_B200_TRACE") != NULL; /* diagnostic: host timeline of the chunk pipeline on stderr */
+		const int trace = b->params.trace != 0; /* diagnostic: host timeline of the chunk pipeline on stderr */
 		const double tr0 = now_ms();
 		double tr_wait0 = 0, tr_wait1 = 0, tr_prep = 0, tr_run = 0;
 		obj[0] = b;
 		for (k0 = 1; k0 < depth; ++k0)
 			obj[k0] = b->pipe[k0 - 1];
+		/* the objects in flight share the device: each chunk may ask for its share of the budget */
+		for (k0 = 0; k0 < depth; ++k0)
+		{
+			keep_budget[k0] = obj[k0]->mem_budget;
+			if (b->params.device_mem_mb <= 0)
+				obj[k0]->mem_budget = b->mem_budget / (size_t)(depth + 1);
+		}
 		while (done < count || pending > 0)
 		{
 			const int slot = k % depth;
@@ -714,61 +955,315 @@ API int stbi_jpeg_decode_batch(stbi_jpeg_batch *b, const stbi_uc *const *bufs, c
 				const int first = pend_first[slot], n = pend_n[slot];
 				tr_wait0 = now_ms() - tr0;
 				if (!stbi_jpeg_batch_sync(s))
-					return -1;
-				tr_wait1 = now_ms() - tr0;
-				batch_report(s, xs ? xs + first : NULL, ys ? ys + first : NULL, comps ? comps + first : NULL,
-								 status ? status + first : NULL);
-				for (i = 0; i < n; ++i)
-					if (stbi_jpeg_batch_status(s, i) == STBI_JPEG_OK)
-						++nok;
-				acc.parse_ms += s->tm.parse_ms;
-				acc.h2d_ms += s->tm.h2d_ms;
-				acc.entropy_ms += s->tm.entropy_ms;
-				acc.idct_ms += s->tm.idct_ms;
-				acc.d2h_ms += s->tm.d2h_ms;
-				acc.total_ms += s->tm.total_ms;
-				acc.entropy_bits += s->tm.entropy_bits;
-				acc.coef_bytes += s->tm.coef_bytes;
-				acc.out_bytes += s->tm.out_bytes;
-				acc.launches += s->tm.launches;
-				acc.selfsync_scans += s->tm.selfsync_scans;
-				if (s->tm.selfsync_rounds > acc.selfsync_rounds)
-					acc.selfsync_rounds = s->tm.selfsync_rounds;
+				{
+					/* a device fault is sticky: nothing later can succeed.  Wait for the copies of the other objects (they
+					   target the caller's buffers, which the caller may free once this call returns), then give up. */
+					broken = 1;
+					report_chunk_failed(first, n, xs, ys, comps, status);
+				}
+				else
+				{
+					tr_wait1 = now_ms() - tr0;
+					batch_report(s, xs ? xs + first : NULL, ys ? ys + first : NULL, comps ? comps + first : NULL,
+									 status ? status + first : NULL);
+					for (i = 0; i < n; ++i)
+						if (stbi_jpeg_batch_status(s, i) == STBI_JPEG_OK)
+							++nok;
+					acc.parse_ms += s->tm.parse_ms;
+					acc.h2d_ms += s->tm.h2d_ms;
+					acc.entropy_ms += s->tm.entropy_ms;
+					acc.idct_ms += s->tm.idct_ms;
+					acc.d2h_ms += s->tm.d2h_ms;
+					acc.total_ms += s->tm.total_ms;
+					acc.entropy_bits += s->tm.entropy_bits;
+					acc.coef_bytes += s->tm.coef_bytes;
+					acc.out_bytes += s->tm.out_bytes;
+					acc.launches += s->tm.launches;
+					acc.selfsync_scans += s->tm.selfsync_scans;
+					if (s->tm.selfsync_rounds > acc.selfsync_rounds)
+						acc.selfsync_rounds = s->tm.selfsync_rounds;
+				}
 				pend_first[slot] = -1;
 				--pending;
+			}
+			if (done < count && broken)
+			{
+				report_chunk_failed(done, count - done, xs, ys, comps, status);
+				done = count;
 			}
 			if (done < count)
 			{
 				/* ramp the first chunks (16, 32, 64, ...) so the first download starts early */
 				const int want = (!serial && depth > 1 && k < 4 && (16 << k) < chunk) ? (16 << k) : chunk;
-				const int n = count - done < want ? count - done : want;
-				if (stbi_jpeg_batch_prepare(s, bufs + done, lens + done, n, req_comp, NULL, NULL, NULL, NULL) < 0)
-					return -1;
-				tr_prep = now_ms() - tr0;
-				if (!stbi_jpeg_batch_run(s))
-					return -1;
-				tr_run = now_ms() - tr0;
-				batch_enqueue_fetch_all(s, n, outs + done, out_caps + done);
-				if (trace)
-					fprintf(stderr, "chunk %d slot %d n %d: wait %.2f..%.2f prepared %.2f launched %.2f downloads enqueued %.2f\n", k, slot,
-							  n, tr_wait0, tr_wait1, tr_prep, tr_run, now_ms() - tr0);
-				pend_first[slot] = done;
-				pend_n[slot] = n;
-				++pending;
-				done += n;
+				int n = count - done < want ? count - done : want;
+				if (!batch_parse(s, bufs + done, lens + done, n, req_comp, 1))
+				{
+					report_chunk_failed(done, n, xs, ys, comps, status); /* host allocation failure: these images only */
+					done += n;
+				}
+				else
+				{
+					n = s->count; /* the memory budget may have cut the chunk; the rest comes next */
+					tr_prep = now_ms() - tr0;
+					if (!batch_upload(s) || !stbi_jpeg_batch_run(s))
+					{
+						report_chunk_failed(done, n, xs, ys, comps, status);
+						done += n;
+					}
+					else
+					{
+						tr_run = now_ms() - tr0;
+						batch_enqueue_fetch_all(s, n, outs + done, out_caps + done);
+						if (trace)
+							fprintf(stderr, "chunk %d slot %d n %d: wait %.2f..%.2f prepared %.2f launched %.2f downloads enqueued %.2f\n", k,
+									  slot, n, tr_wait0, tr_wait1, tr_prep, tr_run, now_ms() - tr0);
+						pend_first[slot] = done;
+						pend_n[slot] = n;
+						++pending;
+						done += n;
+					}
+				}
 			}
 			++k;
 		}
+		for (k0 = 0; k0 < depth; ++k0)
+			obj[k0]->mem_budget = keep_budget[k0];
 	}
 	b->tm = acc;
+	if (broken)
+	{
+		err_zero("cuda sync");
+		return -1;
+	}
 	return nok;
+}
+
+/* ===================================================================================== */
+/* all devices of the box behind one call                                                */
+/* ===================================================================================== */
+#define STBI_JPEG_MULTI_MAX 16
+struct stbi_jpeg_multi
+{
+	int n;
+	stbi_jpeg_batch *b[STBI_JPEG_MULTI_MAX];
+	int first[STBI_JPEG_MULTI_MAX + 1];
+};
+
+API stbi_jpeg_multi *stbi_jpeg_multi_create(const int *devices, int n_devices, const stbi_jpeg_batch_params *params)
+{
+	stbi_jpeg_multi *m;
+	int d, visible = jcu_device_count();
+	if (visible < 1)
+		return (stbi_jpeg_multi *)err_null("no cuda device");
+	if (n_devices <= 0)
+	{
+		n_devices = visible;
+		devices = NULL;
+	}
+	if (n_devices > STBI_JPEG_MULTI_MAX)
+		n_devices = STBI_JPEG_MULTI_MAX;
+	m = (stbi_jpeg_multi *)calloc(1, sizeof(*m));
+	if (!m)
+		return (stbi_jpeg_multi *)err_null("outofmem");
+	for (d = 0; d < n_devices; ++d)
+	{
+		stbi_jpeg_batch_params p;
+		memset(&p, 0, sizeof(p));
+		if (params)
+			p = *params;
+		p.device = devices ? devices[d] : d;
+		if (p.host_threads <= 0)
+		{
+			/* the devices share the host cores */
+			p.host_threads = online_cpus() / n_devices;
+			if (p.host_threads < 2) p.host_threads = 2;
+		}
+		m->b[d] = stbi_jpeg_batch_create(&p);
+		if (!m->b[d])
+		{
+			stbi_jpeg_multi_destroy(m);
+			return NULL; /* reason set by stbi_jpeg_batch_create */
+		}
+		m->n = d + 1;
+	}
+	return m;
+}
+
+API void stbi_jpeg_multi_destroy(stbi_jpeg_multi *m)
+{
+	int d;
+	if (!m)
+		return;
+	for (d = 0; d < m->n; ++d)
+		stbi_jpeg_batch_destroy(m->b[d]);
+	free(m);
+}
+
+API int stbi_jpeg_multi_device_count(const stbi_jpeg_multi *m) { return m ? m->n : 0; }
+
+API int stbi_jpeg_multi_last_split(const stbi_jpeg_multi *m, int *first, int cap)
+{
+	int d;
+	if (!m)
+		return 0;
+	for (d = 0; d <= m->n && d < cap; ++d)
+		first[d] = m->first[d];
+	return m->n;
+}
+
+typedef struct
+{
+	stbi_jpeg_batch *b;
+	const stbi_uc *const *bufs;
+	const int *lens;
+	int count, req_comp;
+	stbi_uc *const *outs;
+	const size_t *out_caps;
+	int *xs, *ys, *comps, *status;
+	int rc;
+	const char *reason;
+} multi_job;
+
+static void *multi_main(void *arg)
+{
+	multi_job *j = (multi_job *)arg;
+	j->rc = stbi_jpeg_decode_batch(j->b, j->bufs, j->lens, j->count, j->req_comp, j->outs, j->out_caps, j->xs, j->ys, j->comps, j->status);
+	j->reason = j->rc < 0 ? tl_reason : NULL; /* the failure string is thread-local: hand it to the caller's thread */
+	return NULL;
+}
+
+API int stbi_jpeg_decode_batch_multi(stbi_jpeg_multi *m, const stbi_uc *const *bufs, const int *lens, int count, int req_comp,
+												 stbi_uc *const *outs, const size_t *out_caps, int *xs, int *ys, int *comps, int *status)
+{
+	multi_job jobs[STBI_JPEG_MULTI_MAX];
+	pthread_t th[STBI_JPEG_MULTI_MAX];
+	int started[STBI_JPEG_MULTI_MAX];
+	double total = 0, run = 0;
+	int d, i, nok = 0, failed = 0;
+	if (!m || m->n < 1 || count < 0)
+		return -1;
+	/* contiguous ranges, balanced by compressed bytes: range d ends where the running sum passes (d+1)/n of the total */
+	for (i = 0; i < count; ++i)
+		total += lens[i] > 0 ? lens[i] : 0;
+	m->first[0] = 0;
+	d = 1;
+	for (i = 0; i < count && d < m->n; ++i)
+	{
+		run += lens[i] > 0 ? lens[i] : 0;
+		while (d < m->n && run >= total * d / m->n)
+			m->first[d++] = i + 1;
+	}
+	while (d <= m->n)
+		m->first[d++] = count;
+	for (d = 0; d < m->n; ++d)
+	{
+		const int f = m->first[d], n = m->first[d + 1] - f;
+		multi_job *j = &jobs[d];
+		memset(j, 0, sizeof(*j));
+		j->b = m->b[d];
+		j->bufs = bufs + f;
+		j->lens = lens + f;
+		j->count = n;
+		j->req_comp = req_comp;
+		j->outs = outs ? outs + f : NULL;
+		j->out_caps = out_caps ? out_caps + f : NULL;
+		j->xs = xs ? xs + f : NULL;
+		j->ys = ys ? ys + f : NULL;
+		j->comps = comps ? comps + f : NULL;
+		j->status = status ? status + f : NULL;
+		started[d] = 0;
+		if (n <= 0)
+			continue;
+		if (m->n > 1 && pthread_create(&th[d], NULL, multi_main, j) == 0)
+			started[d] = 1;
+		else
+			multi_main(j); /* one device, or no thread to be had: the caller's thread does it */
+	}
+	for (d = 0; d < m->n; ++d)
+	{
+		if (started[d])
+			pthread_join(th[d], NULL);
+		if (jobs[d].count <= 0)
+			continue;
+		if (jobs[d].rc < 0)
+		{
+			failed = 1;
+			err_zero(jobs[d].reason ? jobs[d].reason : "cuda sync");
+		}
+		else
+			nok += jobs[d].rc;
+	}
+	return failed ? -1 : nok;
 }
 
 /* ===================================================================================== */
 /* per-image entry points                                                                */
 /* ===================================================================================== */
-static pthread_mutex_t g_default_lock = PTHREAD_MUTEX_INITIALIZER;
-static stbi_jpeg_batch *g_default;
+/* The reference allocates fresh decoder state per call (jpeg.c:2445-2450) and is re-entrant apart from the failure
+   string; so are these: every call borrows a decoder object (own stream, own device buffers, pre-sized so that an
+   ordinary image meets no cudaMalloc) from a pool that grows with the number of threads inside the library at
+   once, up to PI_POOL_MAX; beyond that callers queue for a free object. */
+#define PI_POOL_MAX 16
+static pthread_mutex_t g_pi_lock = PTHREAD_MUTEX_INITIALIZER;
+static pthread_cond_t g_pi_cv = PTHREAD_COND_INITIALIZER;
+static stbi_jpeg_batch *g_pi_free[PI_POOL_MAX];
+static int g_pi_nfree, g_pi_created;
+static int g_default_device;
+
+API void stbi_jpeg_set_default_device(int device) { g_default_device = device < 0 ? 0 : device; }
+
+static stbi_jpeg_batch *pi_acquire(void)
+{
+	stbi_jpeg_batch *b = NULL;
+	pthread_mutex_lock(&g_pi_lock);
+	for (;;)
+	{
+		if (g_pi_nfree > 0)
+		{
+			b = g_pi_free[--g_pi_nfree];
+			if (b->params.device == g_default_device)
+				break;
+			/* the default device changed since this object was made */
+			--g_pi_created;
+			pthread_mutex_unlock(&g_pi_lock);
+			stbi_jpeg_batch_destroy(b);
+			pthread_mutex_lock(&g_pi_lock);
+			b = NULL;
+			continue;
+		}
+		if (g_pi_created < PI_POOL_MAX)
+		{
+			stbi_jpeg_batch_params p;
+			++g_pi_created;
+			memset(&p, 0, sizeof(p));
+			p.device = g_default_device;
+			p.host_threads = 1;
+			pthread_mutex_unlock(&g_pi_lock);
+			b = stbi_jpeg_batch_create(&p);
+			if (b) /* room for a 2048 x 2048 image in any sampling before the first call needs it */
+				jcu_reserve(b->ctx, (size_t)4 << 20, (size_t)3 * 2048 * 2048, (size_t)4 * 2048 * 2048);
+			else
+			{
+				pthread_mutex_lock(&g_pi_lock);
+				--g_pi_created;
+				pthread_cond_signal(&g_pi_cv);
+				pthread_mutex_unlock(&g_pi_lock);
+			}
+			return b;
+		}
+		pthread_cond_wait(&g_pi_cv, &g_pi_lock);
+	}
+	pthread_mutex_unlock(&g_pi_lock);
+	return b;
+}
+
+static void pi_release(stbi_jpeg_batch *b)
+{
+	pthread_mutex_lock(&g_pi_lock);
+	g_pi_free[g_pi_nfree++] = b;
+	pthread_cond_signal(&g_pi_cv);
+	pthread_mutex_unlock(&g_pi_lock);
+}
 
 /* 16-bit / float variants: state of the reference's setters, convert.c:402-411 */
 static float g_l2h_gamma = 2.2f, g_l2h_scale = 1.0f;
@@ -780,6 +1275,7 @@ static void *load_from_buffer_as(const stbi_uc *buffer, size_t len, int *x, int 
 {
 	jp_result probe;
 	stbi_uc *out = NULL;
+	stbi_jpeg_batch *g_default;
 	int ilen, xs = 0, ys = 0, cs = 0, st = 0;
 	/* stbi__load_main (image_api.c:10-13,55): only JPEG is recognised, by its SOI */
 	if (!jp_parse(buffer, len, req_comp, JP_MODE_TYPE, &probe))
@@ -790,16 +1286,7 @@ static void *load_from_buffer_as(const stbi_uc *buffer, size_t len, int *x, int 
 		return (stbi_uc *)err_null("too large");
 	ilen = (int)len;
 
-	pthread_mutex_lock(&g_default_lock);
-	if (!g_default)
-	{
-		stbi_jpeg_batch_params p;
-		const char *dev = getenv("IMAGE_CODECS_B200_DEVICE");
-		memset(&p, 0, sizeof(p));
-		p.device = dev ? atoi(dev) : 0;
-		p.host_threads = 1;
-		g_default = stbi_jpeg_batch_create(&p);
-	}
+	g_default = pi_acquire();
 	if (g_default)
 	{
 		const stbi_uc *bufs[1];
@@ -854,7 +1341,8 @@ static void *load_from_buffer_as(const stbi_uc *buffer, size_t len, int *x, int 
 		else if (g_default->count == 1 && !g_default->res[0].ok)
 			err_null(g_default->res[0].reason); /* NULL reason: the reference left it unchanged too */
 	}
-	pthread_mutex_unlock(&g_default_lock);
+	if (g_default)
+		pi_release(g_default);
 	if (!out)
 		return NULL;
 	if (x) *x = xs;
@@ -1313,11 +1801,10 @@ API int stbi_write_jpg_to_func(stbi_write_func *func, void *context, int x, int 
 	const stbi_uc *px[1];
 	stbi_uc *out[1] = {NULL};
 	int len[1] = {0};
-	const char *dev = getenv("IMAGE_CODECS_B200_DEVICE");
 	if (!data || !x || !y || comp > 4 || comp < 1 || !func)
 		return 0;
 	px[0] = (const stbi_uc *)data;
-	if (stbi_jpeg_encode_batch(dev ? atoi(dev) : 0, px, &x, &y, &comp, 1, quality, out, len, NULL) != 1)
+	if (stbi_jpeg_encode_batch(g_default_device, px, &x, &y, &comp, 1, quality, out, len, NULL) != 1)
 		return 0;
 	func(context, out[0], len[0]);
 	free(out[0]);

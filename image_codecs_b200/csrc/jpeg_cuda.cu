@@ -30,15 +30,16 @@ struct DevBuf
 	size_t guard_at = 0; /* guard mode: offset of the JCU_GUARD_BYTES canary behind the logical size */
 };
 #define JCU_GUARD_BYTES 4096
-/* IMAGE_CODECS_B200_GUARD=1 (test hook; compute-sanitizer is not available on every box): every device buffer
-   is allocated at exactly the size asked for plus a canary that jcu_debug_guards_ok() verifies */
-static bool g_guard_mode = false;
+/* jcu_ctx_options.guard (test hook; compute-sanitizer is not available on every box): every device buffer of the
+   context is allocated at exactly the size asked for plus a canary that jcu_debug_guards_ok() verifies */
 
 struct jcu_ctx
 {
 	int device = 0;
 	int profile = 0;
 	int entropy_mode = 0;
+	bool guard = false;
+	int rows_per_band_forced = 0;
 	cudaStream_t stream = nullptr;
 	/* downloads run on their own stream, behind an event of the compute stream */
 	cudaStream_t dl_own = nullptr, dl_use = nullptr;
@@ -95,9 +96,10 @@ static int set_err(jcu_ctx *c, cudaError_t e, const char *where)
 			return set_err(c, e__, #call);            \
 	} while (0)
 
-static cudaError_t ensure(DevBuf &b, size_t bytes)
+#define ensure(buf, bytes) ensure_impl(c->guard, buf, bytes) /* every caller has its context in `c` */
+static cudaError_t ensure_impl(bool guard_mode, DevBuf &b, size_t bytes)
 {
-	if (g_guard_mode)
+	if (guard_mode)
 	{
 		if (b.p)
 			cudaFree(b.p);
@@ -137,18 +139,27 @@ extern "C" int jcu_device_count(void)
 
 extern "C" int jcu_ctx_create(int device, int profile, int entropy_mode, jcu_ctx **out)
 {
+	jcu_ctx_options o;
+	memset(&o, 0, sizeof(o));
+	o.device = device;
+	o.profile = profile;
+	o.entropy_mode = entropy_mode;
+	return jcu_ctx_create_opts(&o, out);
+}
+
+extern "C" int jcu_ctx_create_opts(const jcu_ctx_options *o, jcu_ctx **out)
+{
 	*out = nullptr;
-	cudaError_t e = cudaSetDevice(device);
+	cudaError_t e = cudaSetDevice(o->device);
 	if (e != cudaSuccess)
 		return (int)e;
 	jcu_ctx *c = new jcu_ctx();
-	c->device = device;
-	c->profile = profile;
-	c->entropy_mode = entropy_mode;
-	const char *gm = getenv("IMAGE_CODECS_B200_GUARD");
-	g_guard_mode = gm && gm[0] == '1';
-	const char *fg = getenv("IMAGE_CODECS_B200_FORCE_GENERIC");
-	c->force_generic = fg && fg[0] == '1';
+	c->device = o->device;
+	c->profile = o->profile;
+	c->entropy_mode = o->entropy_mode;
+	c->guard = o->guard != 0;
+	c->force_generic = o->force_generic != 0;
+	c->rows_per_band_forced = o->rows_per_band > 0 ? o->rows_per_band : 0;
 	e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
 	if (e != cudaSuccess)
 	{
@@ -206,7 +217,7 @@ extern "C" void jcu_ctx_destroy(jcu_ctx *c)
 
 extern "C" int jcu_debug_guards_ok(jcu_ctx *c)
 {
-	if (!c || !g_guard_mode)
+	if (!c || !c->guard)
 		return -1;
 	cudaSetDevice(c->device);
 	if (cudaStreamSynchronize(c->stream) != cudaSuccess)
@@ -231,6 +242,21 @@ extern "C" int jcu_debug_guards_ok(jcu_ctx *c)
 			}
 	}
 	return 1;
+}
+
+extern "C" int jcu_mem_info(int device, size_t *free_bytes, size_t *total_bytes)
+{
+	size_t f = 0, t = 0;
+	cudaError_t e = cudaSetDevice(device);
+	if (e == cudaSuccess)
+		e = cudaMemGetInfo(&f, &t);
+	if (e != cudaSuccess)
+		cudaGetLastError();
+	if (free_bytes)
+		*free_bytes = f;
+	if (total_bytes)
+		*total_bytes = t;
+	return (int)e;
 }
 
 extern "C" const char *jcu_error_string(jcu_ctx *c) { return c ? c->errstr : "no context"; }
@@ -277,9 +303,8 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 				strip_rows += (long long)((imgs[i].mcu_x + S420_MS - 1) / S420_MS) * imgs[i].mcu_y;
 		long long rb = strip_rows / (148 * (512 / S420_THREADS) * 8);
 		c->rows_per_band = (int)std::min<long long>(std::max<long long>(rb, 2), 24);
-		const char *ov = getenv("IMAGE_CODECS_B200_ROWS_PER_BAND"); /* test hook: force the band height */
-		if (ov && atoi(ov) > 0)
-			c->rows_per_band = atoi(ov);
+		if (c->rows_per_band_forced) /* jcu_ctx_options.rows_per_band: tests force the band height */
+			c->rows_per_band = c->rows_per_band_forced;
 	}
 	for (int i = 0; i < b->n_images; ++i)
 	{
@@ -338,6 +363,19 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 		const jcu_scan &sc = b->scans[s];
 		if (!imgs[sc.image].ok || sc.kind != JCU_SCAN_BASELINE || sc.restart_interval != 0 || sc.nseg != 1 || c->entropy_mode == 1)
 			continue;
+		{
+			/* The self-synchronising scans all run behind the last wave, whatever their own wave: a scan that shares a
+			   component with another scan of its image (legal in T.81: the later scan wins, jpeg.c:1716) must keep its
+			   place in the wave order, so it stays on the serial path.  Scans of one image are contiguous. */
+			bool shared = false;
+			for (int dir = -1; dir <= 1 && !shared; dir += 2)
+				for (int o = s + dir; o >= 0 && o < b->n_scans && b->scans[o].image == sc.image && !shared; o += dir)
+					for (int a = 0; a < sc.ncomp; ++a)
+						for (int q = 0; q < b->scans[o].ncomp; ++q)
+							shared = shared || sc.comp[a] == b->scans[o].comp[q];
+			if (shared)
+				continue;
+		}
 		const uint32_t start = b->seg_start[sc.seg_first];
 		const uint32_t bytes = sc.data_end > start ? sc.data_end - start : 0u;
 		if (bytes < (c->entropy_mode == 2 ? 1u : 4u * SS_SUB_BYTES))
@@ -488,6 +526,25 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 	if (c->profile)
 		CK(cudaEventRecord(c->ev_h2d1, c->stream));
 	/* the staging vector `imgs` is pageable: cudaMemcpyAsync has consumed it before returning */
+	return 0;
+}
+
+/* grow the big device buffers ahead of time so that a later jcu_upload of at most this size meets no cudaMalloc */
+extern "C" int jcu_reserve(jcu_ctx *c, size_t bitstream_bytes, size_t coef_elems, size_t out_bytes)
+{
+	CK(cudaSetDevice(c->device));
+	CK(ensure(c->bits, bitstream_bytes + 64));
+	CK(ensure(c->uslab, bitstream_bytes + 32 * (bitstream_bytes / 64 + 4)));
+	CK(ensure(c->useg_len, sizeof(uint32_t) * (bitstream_bytes / 64 + 1)));
+	CK(ensure(c->segs, sizeof(uint32_t) * (bitstream_bytes / 64 + 1)));
+	CK(ensure(c->coef, sizeof(int16_t) * coef_elems + 256));
+	CK(ensure(c->out, out_bytes + 256));
+	CK(ensure(c->images, sizeof(jcu_image) * 4));
+	CK(ensure(c->scans, sizeof(jcu_scan) * 64));
+	CK(ensure(c->huff, sizeof(jcu_huff_spec) * 64));
+	CK(ensure(c->work, sizeof(EntWork) * 4096));
+	CK(ensure(c->err, sizeof(int32_t) * 4));
+	CK(ensure(c->lists, sizeof(int32_t) * 16));
 	return 0;
 }
 

@@ -66,24 +66,33 @@ static int fail(parser *p, const char *why)
 	return 0;
 }
 
-/* ---- growable arrays ---- */
-static void *grow(void *ptr, int *cap, int need, size_t elem)
+/* ---- growable arrays: on allocation failure the old array (and capacity) stay and 0 is returned ---- */
+static int grow(void **ptr, int *cap, int need, size_t elem)
 {
 	if (need > *cap)
 	{
 		int nc = *cap ? *cap * 2 : 16;
+		void *np;
 		while (nc < need)
 			nc *= 2;
-		ptr = realloc(ptr, (size_t)nc * elem);
+		np = realloc(*ptr, (size_t)nc * elem);
+		if (!np)
+			return 0;
+		*ptr = np;
 		*cap = nc;
 	}
-	return ptr;
+	return 1;
 }
 
+/* index of the new entry, or -1 (with the result marked "outofmem") */
 static int push_huff(parser *p, const jcu_huff_spec *s)
 {
 	jp_result *r = p->r;
-	r->huff = (jcu_huff_spec *)grow(r->huff, &r->cap_huff, r->nhuff + 1, sizeof(jcu_huff_spec));
+	if (!grow((void **)&r->huff, &r->cap_huff, r->nhuff + 1, sizeof(jcu_huff_spec)))
+	{
+		fail(p, "outofmem");
+		return -1;
+	}
 	r->huff[r->nhuff] = *s;
 	return r->nhuff++;
 }
@@ -318,6 +327,10 @@ static int frame_header(parser *p, int mode)
 		/* stbi__malloc_mad2(w2, h2, 15), jpeg.c:1641 */
 		if ((unsigned long long)k->bw * 8ull * (unsigned long long)k->bh * 8ull + 15ull > (unsigned long long)INT_MAX)
 			return fail(p, "outofmem");
+		/* progressive: the coefficient plane, stbi__malloc_mad3(w2, h2, sizeof(short), 15), jpeg.c:1651 */
+		if (p->progressive &&
+			 (unsigned long long)k->bw * 8ull * (unsigned long long)k->bh * 8ull * 2ull + 15ull > (unsigned long long)INT_MAX)
+			return fail(p, "outofmem");
 	}
 	return 1;
 }
@@ -384,7 +397,7 @@ static int scan_header(parser *p, jcu_scan *sc, int hd[4], int ha[4])
  * Reaching the end of the file leaves no pending marker (the reference then fails with
  * "expected marker", jpeg.c:1722-1735 + 1355).
  */
-static void walk_entropy_segments(parser *p, jcu_scan *sc)
+static int walk_entropy_segments(parser *p, jcu_scan *sc)
 {
 	jp_result *r = p->r;
 	const unsigned char *buf = p->cur.buf;
@@ -395,7 +408,8 @@ static void walk_entropy_segments(parser *p, jcu_scan *sc)
 
 	sc->seg_first = (uint32_t)r->nsegs;
 	sc->nseg = 1;
-	r->segs = (uint32_t *)grow(r->segs, &r->cap_segs, r->nsegs + 1, sizeof(uint32_t));
+	if (!grow((void **)&r->segs, &r->cap_segs, r->nsegs + 1, sizeof(uint32_t)))
+		return fail(p, "outofmem");
 	r->segs[r->nsegs++] = (uint32_t)(pos < len ? pos : len);
 	p->pending = MARKER_NONE;
 
@@ -428,7 +442,8 @@ static void walk_entropy_segments(parser *p, jcu_scan *sc)
 		}
 		if (ri && code >= 0xd0 && code <= 0xd7 && sc->nseg < expected)
 		{
-			r->segs = (uint32_t *)grow(r->segs, &r->cap_segs, r->nsegs + 1, sizeof(uint32_t));
+			if (!grow((void **)&r->segs, &r->cap_segs, r->nsegs + 1, sizeof(uint32_t)))
+				return fail(p, "outofmem");
 			r->segs[r->nsegs++] = (uint32_t)(q + 1);
 			sc->nseg++;
 			marker_bytes += (q + 1) - at;
@@ -460,6 +475,12 @@ static void walk_entropy_segments(parser *p, jcu_scan *sc)
 	}
 	p->cur.pos = pos;
 	r->entropy_bytes += (double)(sc->data_end - scan_begin) - (double)marker_bytes;
+	/* fewer restart intervals than the scan needs (a lost RSTn followed by a marker): the reference's scan ends
+	   "successfully" and the blocks behind it keep what malloc left there (jpeg.c:1184-1187); here they must not
+	   keep what an EARLIER BATCH left in the reused coefficient slab, so the batch builder clears it */
+	if (sc->nseg < expected)
+		r->needs_clear = 1;
+	return 1;
 }
 
 static int pool_index(parser *p, int is_ac, int t)
@@ -513,13 +534,13 @@ static int one_scan(parser *p)
 		{
 			sc.dc_spec[i] = pool_index(p, 0, hd[i]);
 			if (sc.dc_spec[i] < 0)
-				return fail(p, "bad huffman code"); /* table never defined: undefined in the reference */
+				return p->r->ok ? fail(p, "bad huffman code") : 0; /* table never defined: undefined in the reference */
 		}
 		if (needs_ac)
 		{
 			sc.ac_spec[i] = pool_index(p, 1, ha[i]);
 			if (sc.ac_spec[i] < 0)
-				return fail(p, "bad huffman code");
+				return p->r->ok ? fail(p, "bad huffman code") : 0;
 		}
 	}
 	sc.restart_interval = p->restart_interval;
@@ -565,9 +586,11 @@ static int one_scan(parser *p)
 		for (i = 0; i < sc.ncomp; ++i)
 			memcpy(im->qt[sc.comp[i]], p->dequant[p->tq[sc.comp[i]]], sizeof(im->qt[0]));
 
-	walk_entropy_segments(p, &sc);
+	if (!walk_entropy_segments(p, &sc))
+		return 0;
 
-	r->scans = (jcu_scan *)grow(r->scans, &r->cap_scans, r->nscans + 1, sizeof(jcu_scan));
+	if (!grow((void **)&r->scans, &r->cap_scans, r->nscans + 1, sizeof(jcu_scan)))
+		return fail(p, "outofmem");
 	r->scans[r->nscans++] = sc;
 	return 1;
 }
@@ -703,6 +726,18 @@ int jp_parse(const unsigned char *buf, size_t len, int req_comp, int mode, jp_re
 	if (p->progressive)
 		for (i = 0; i < p->ncomp; ++i)
 			memcpy(r->img.qt[i], p->dequant[p->tq[i]], sizeof(r->img.qt[0]));
+
+	/* a frame component that no scan carried: its blocks are never written by the entropy stage (the reference
+	   shows uninitialised heap there); the builder clears the slab so the result is deterministic */
+	for (i = 0; i < p->ncomp; ++i)
+	{
+		int s_, k_, seen = 0;
+		for (s_ = 0; s_ < r->nscans; ++s_)
+			for (k_ = 0; k_ < r->scans[s_].ncomp; ++k_)
+				seen |= r->scans[s_].comp[k_] == i;
+		if (!seen)
+			r->needs_clear = 1;
+	}
 
 	choose_output(p, req_comp);
 	r->consumed = p->cur.pos < p->cur.len ? p->cur.pos : p->cur.len;

@@ -42,6 +42,7 @@ typedef struct
 	size_t consumed; /* bytes of the file the reference has read when it returns: up to and including the EOI marker */
 	double entropy_bytes; /* entropy-coded bytes over all scans (incl. stuffing, excl. markers) */
 	long long coef_blocks; /* blocks the output stage reads (MCU-padded, decode_n components) */
+	int needs_clear; /* some block of the image is written by no scan (lost RSTn, component without a scan): zero the slab first */
 } jp_result;
 
 /* Parse one JPEG held in memory.  Returns r->ok.  r must be zero-initialised or previously freed. */

@@ -73,8 +73,9 @@ STBIDEF int stbi_info_from_file(FILE *f, int *x, int *y, int *comp);
 STBIDEF int stbi_info_from_memory(stbi_uc const *buffer, int len, int *x, int *y, int *comp);
 STBIDEF int stbi_info_from_callbacks(stbi_io_callbacks const *clbk, void *user, int *x, int *y, int *comp);
 
-/* ---- 16-bit and float variants (reference convert.c:213-252, 286-337): the 8-bit GPU decode widened on the host
- *      exactly as the reference widens its own 8-bit result (v * 257; pow(v / 255, gamma) * scale) ---- */
+/* ---- 16-bit and float variants (reference convert.c:213-252, 286-337): the 8-bit GPU decode is widened ON THE
+ *      DEVICE by a store epilogue (v * 257; a 512-entry table of the reference's pow(v / 255, gamma) * scale built by
+ *      the host's pow()), so the wide samples are what crosses the bus; same values as the reference's host loop ---- */
 STBIDEF stbi_us *stbi_load_16(char const *filename, int *x, int *y, int *comp, int req_comp);
 STBIDEF stbi_us *stbi_load_from_file_16(FILE *f, int *x, int *y, int *comp, int req_comp);
 STBIDEF stbi_us *stbi_load_16_from_memory(stbi_uc const *buffer, int len, int *x, int *y, int *comp, int req_comp);
@@ -132,7 +133,17 @@ typedef struct
 	int chunk_images;		 /* images per pipeline chunk for the host-buffer call; 0 = auto */
 	int profile;			 /* 1 = record CUDA events around each stage (stbi_jpeg_batch_timings) */
 	int entropy_mode;		 /* 0 = auto, 1 = one thread per restart segment, 2 = self-synchronising */
-	int reserved[7];
+	/* tuning (0 = default) */
+	int pipeline_depth;	 /* chunk objects in flight in stbi_jpeg_decode_batch: 0 = 3, 1..4 */
+	int device_mem_mb;	 /* device memory ONE prepared chunk may ask for; 0 = auto (a share of the device).  A chunk
+									 that would need more is cut and continued; an image that needs more by itself fails
+									 alone with "outofmem" */
+	int no_download_merge; /* 1 = one device->host copy per image instead of merged copies of up to 64 MB */
+	int trace;				 /* 1 = host timeline of the chunk pipeline on stderr */
+	/* test switches (0 in production) */
+	int force_generic;	 /* every image takes the generic two-pass output path */
+	int rows_per_band;	 /* > 0: MCU rows per band of the 4:2:0 strip kernel */
+	int debug_guards;		 /* canaries behind every device buffer, see stbi_jpeg_batch_debug_guards */
 } stbi_jpeg_batch_params;
 
 /* per-image status values written by the batch calls */
@@ -196,9 +207,31 @@ STBIDEF void *stbi_jpeg_batch_device_pixels(stbi_jpeg_batch *b, int image, size_
 STBIDEF int stbi_jpeg_batch_status(stbi_jpeg_batch *b, int image);
 STBIDEF const char *stbi_jpeg_batch_reason(stbi_jpeg_batch *b, int image);
 STBIDEF int stbi_jpeg_batch_timings_get(stbi_jpeg_batch *b, stbi_jpeg_batch_timings *t);
-/* test hook: with IMAGE_CODECS_B200_GUARD=1 set before stbi_jpeg_batch_create, every device buffer carries a
-   canary behind its logical size; 1 = all intact, 0 = one was overwritten, -1 = guard mode off */
+/* test hook: a batch created with params.debug_guards = 1 carries a canary behind the logical size of every device
+   buffer; 1 = all intact, 0 = one was overwritten, -1 = guard mode off */
 STBIDEF int stbi_jpeg_batch_debug_guards(stbi_jpeg_batch *b);
+
+/*
+ * All GPUs of the box behind one call (BASELINE.json north_star: "independent image batches are sharded across the 8
+ * GPUs of one box with no collective").  The object owns one stbi_jpeg_batch per device; stbi_jpeg_decode_batch_multi
+ * splits the images into one contiguous range per device, balanced by compressed bytes (entropy-decode time follows
+ * the bits), and runs stbi_jpeg_decode_batch on every range at once, each on its own host worker thread with its own
+ * pinned staging, streams and parser threads (params.host_threads is per device; 0 = online cores / devices).
+ * Arguments, results and per-image semantics are those of stbi_jpeg_decode_batch.  devices == NULL: devices
+ * 0 .. n_devices-1 (n_devices <= 0: every visible device).
+ */
+typedef struct stbi_jpeg_multi stbi_jpeg_multi;
+STBIDEF stbi_jpeg_multi *stbi_jpeg_multi_create(const int *devices, int n_devices, const stbi_jpeg_batch_params *params);
+STBIDEF void stbi_jpeg_multi_destroy(stbi_jpeg_multi *m);
+STBIDEF int stbi_jpeg_multi_device_count(const stbi_jpeg_multi *m);
+STBIDEF int stbi_jpeg_decode_batch_multi(stbi_jpeg_multi *m, const stbi_uc *const *bufs, const int *lens, int count, int req_comp,
+													  stbi_uc *const *outs, const size_t *out_caps, int *xs, int *ys, int *comps, int *status);
+/* images [first[d], first[d+1]) went to device d in the last call (n_devices + 1 entries); returns n_devices */
+STBIDEF int stbi_jpeg_multi_last_split(const stbi_jpeg_multi *m, int *first, int cap);
+
+/* Device used by the per-image entry points (stbi_load*, stbi_write_jpg*); default 0.  Takes effect for contexts
+   created afterwards. */
+STBIDEF void stbi_jpeg_set_default_device(int device);
 
 /*
  * Host-only full marker parse of one stream (no GPU): what the batch loader would hand to the

@@ -150,12 +150,24 @@ typedef struct jcu_ctx jcu_ctx;
 JCU_API int jcu_device_count(void);
 /* all functions below return 0 on success, else a CUDA error code; text via jcu_error_string */
 JCU_API int jcu_ctx_create(int device, int profile, int entropy_mode, jcu_ctx **out);
+/* same, with the tuning / test switches (all zero = the defaults of jcu_ctx_create) */
+typedef struct
+{
+	int32_t device, profile, entropy_mode;
+	int32_t force_generic; /* 1 = every image takes the generic two-pass output path (parity tests of that path) */
+	int32_t rows_per_band; /* > 0 = MCU rows per band of the 4:2:0 strip kernel instead of the batch-size heuristic */
+	int32_t guard;			  /* 1 = every device buffer carries a canary behind its logical size (jcu_debug_guards_ok) */
+	int32_t reserved[2];
+} jcu_ctx_options;
+JCU_API int jcu_ctx_create_opts(const jcu_ctx_options *o, jcu_ctx **out);
 JCU_API void jcu_ctx_destroy(jcu_ctx *c);
 JCU_API const char *jcu_error_string(jcu_ctx *c);
 
+JCU_API int jcu_mem_info(int device, size_t *free_bytes, size_t *total_bytes); /* cudaMemGetInfo: the batch loader budgets its chunks with it */
 JCU_API void *jcu_host_alloc(size_t bytes); /* pinned host memory */
 JCU_API void jcu_host_free(void *p);
 
+JCU_API int jcu_reserve(jcu_ctx *c, size_t bitstream_bytes, size_t coef_elems, size_t out_bytes); /* pre-size the device buffers */
 JCU_API int jcu_upload(jcu_ctx *c, const jcu_batch *b);								  /* H2D, asynchronous on the ctx stream */
 JCU_API int jcu_run(jcu_ctx *c);															  /* entropy waves + output stage, asynchronous */
 JCU_API int jcu_sync(jcu_ctx *c);
@@ -180,9 +192,9 @@ JCU_API void *jcu_device_wide(jcu_ctx *c);
 
 /* stage-level entry points for the parity tests (host pointers in, host pointers out) */
 JCU_API int jcu_test_idct_blocks(jcu_ctx *c, const int16_t *coef, const uint16_t *qt, int nblocks, uint8_t *out64);
-/* test hook: with IMAGE_CODECS_B200_GUARD=1 in the environment every device buffer carries a 4 KB canary behind
-   its logical size; returns 1 if all canaries are intact, 0 if one was overwritten (jcu_error_string says
-   which), -1 if guard mode is off */
+/* test hook: a context created with jcu_ctx_options.guard carries a 4 KB canary behind the logical size of every
+   device buffer; returns 1 if all canaries are intact, 0 if one was overwritten (jcu_error_string says which),
+   -1 if guard mode is off */
 JCU_API int jcu_debug_guards_ok(jcu_ctx *c);
 JCU_API int jcu_test_ycbcr(jcu_ctx *c, const uint8_t *y, const uint8_t *cb, const uint8_t *cr, int n, int step, uint8_t *out);
 JCU_API int jcu_read_coefs(jcu_ctx *c, size_t elem_off, size_t elems, int16_t *dst); /* coefficient slab after run */

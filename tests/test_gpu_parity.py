@@ -82,11 +82,7 @@ def test_batch_req_comp_variants(oracle, decoder, req_comp):
 
 def test_generic_path_matches_too(oracle):
     """The two-pass generic path must agree with the fused kernels' formats as well."""
-    os.environ["IMAGE_CODECS_B200_FORCE_GENERIC"] = "1"
-    try:
-        d = ic.BatchDecoder(device=0)
-    finally:
-        del os.environ["IMAGE_CODECS_B200_FORCE_GENERIC"]
+    d = ic.BatchDecoder(device=0, force_generic=1)
     cases = [c for c in S.small_matrix() if c[0] in ("420", "444", "gray", "420_rst16", "420_prog")]
     datas = [S.stream(f, w, h, k) for f, w, h, k in cases]
     for rc in (0, 4):
@@ -141,20 +137,16 @@ def test_fused_420_strips_and_bands(oracle, rows_per_band):
     """4:2:0 strip kernel: images wider than one 640-pixel strip (2 and 3 strips, a 1-MCU last strip,
     widths that are not multiples of 16 or 8), bands of 1 / 5 / all MCU rows, RGB and RGBA, baseline and
     progressive (decode-time vs output-time dequantisation)."""
-    if rows_per_band:
-        os.environ["IMAGE_CODECS_B200_ROWS_PER_BAND"] = str(rows_per_band)
-    try:
+    if True:
         cases = [("420_rst16", 1300, 100, 0), ("420", 650, 50, 1), ("420", 641, 33, 2), ("420_rst1", 1924, 70, 0),
                  ("420_prog", 1283, 47, 1), ("420_opt", 656, 129, 2), ("420", 1280, 16, 0), ("420", 1288, 200, 1)]
         datas = [S.stream(f, w, h, k) for f, w, h, k in cases]
-        d = ic.BatchDecoder(device=0)
+        d = ic.BatchDecoder(device=0, rows_per_band=rows_per_band)
         for rc in (3, 4):
             outs = d.decode(datas, rc)
             for (f, w, h, k), data, got in zip(cases, datas, outs):
                 _check(oracle, got, data, rc, f"strip {f} {w}x{h} req{rc} rpb{rows_per_band}")
         d.close()
-    finally:
-        os.environ.pop("IMAGE_CODECS_B200_ROWS_PER_BAND", None)
 
 
 def test_full_size_1080p_420_rst16(oracle, decoder):
@@ -165,6 +157,36 @@ def test_full_size_1080p_420_rst16(oracle, decoder):
     outs = decoder.decode(datas, 3)
     for i, (data, got) in enumerate(zip(datas, outs)):
         _check(oracle, got, data, 3, f"1080p #{i}")
+
+
+def test_full_size_2160p_config_c5(oracle, decoder):
+    """BASELINE.json configs[4] geometry: 3840x2160 4:2:0 q90 (12 strips x 135 MCU rows, 194 400 blocks per image,
+    reference driver jpeg.c:2224-2440) with restart interval 16 AND without restart markers (self-synchronising
+    path), an odd size one pixel past the MCU grid (3841x2161: a 1-MCU last strip, clamped chroma edges on both
+    axes), a progressive file, and RGBA output -- every pixel against the compiled reference."""
+    from tools import testenc as te
+
+    datas, tags = [], []
+    for i, d in enumerate(te.encode_many(2, 3840, 2160, kind=-1, base_seed=5150, quality=90, subsampling="420", restart_interval=16)):
+        datas.append(d)
+        tags.append(f"2160p rst16 #{i}")
+    for i, d in enumerate(te.encode_many(2, 3840, 2160, kind=-1, base_seed=5152, quality=90, subsampling="420")):
+        datas.append(d)
+        tags.append(f"2160p no-rst #{i}")
+    datas.append(te.encode(te.synth_rgb(3841, 2161, 1, 5154), quality=90, subsampling="420", restart_interval=16))
+    tags.append("3841x2161 rst16")
+    datas.append(te.encode(te.synth_rgb(3841, 2161, 0, 5155), quality=90, subsampling="420"))
+    tags.append("3841x2161 no-rst")
+    datas.append(te.encode(te.synth_rgb(3840, 2160, 1, 5156), quality=90, subsampling="420", progressive=1, restart_interval=16))
+    tags.append("2160p progressive rst16")
+    datas.append(te.encode(te.synth_rgb(3840, 2160, 0, 5157), quality=90, subsampling="420", progressive=1))
+    tags.append("2160p progressive no-rst")
+    for rc in (3, 4):
+        outs = decoder.decode(datas, rc)
+        for tag, data, got in zip(tags, datas, outs):
+            _check(oracle, got, data, rc, f"{tag} req{rc}")
+    tm = decoder.timings()
+    assert tm["selfsync_scans"] >= 3, tm
 
 
 @pytest.mark.parametrize("entropy_mode", [1, 2])
@@ -538,9 +560,8 @@ def test_no_kernel_writes_past_a_device_buffer(oracle, entropy_mode):
     the size the host asked for plus a 4 KB canary; after decoding the whole format matrix (all entropy paths:
     restart segments, progressive, serial and self-synchronising restart-less scans; all output kernels) and a
     set of corrupted streams, every canary must be intact and the pixels still bit-exact."""
-    os.environ["IMAGE_CODECS_B200_GUARD"] = "1"  # read whenever a context is created; decode() creates its pipeline objects lazily
-    try:
-        d = ic.BatchDecoder(device=0, entropy_mode=entropy_mode)
+    if True:
+        d = ic.BatchDecoder(device=0, entropy_mode=entropy_mode, debug_guards=1)  # the pipeline objects inherit the switch
         cases = S.small_matrix()
         datas = [S.stream(f, w, h, k) for f, w, h, k in cases]
         for rc in (0, 3, 4):
@@ -560,5 +581,126 @@ def test_no_kernel_writes_past_a_device_buffer(oracle, entropy_mode):
         d.decode(bad, 3)
         assert d.guards_ok() == 1, "corrupted streams"
         d.close()
-    finally:
-        del os.environ["IMAGE_CODECS_B200_GUARD"]
+
+
+def _forge_sof_size(raw: bytes, w: int, h: int) -> bytes:
+    b = bytearray(raw)
+    sof = b.index(b"\xff\xc0")
+    b[sof + 5 : sof + 9] = bytes([h >> 8, h & 255, w >> 8, w & 255])
+    return bytes(b)
+
+
+def test_oversized_image_fails_alone_and_chunks_follow_the_memory_budget(oracle):
+    """a ~300-byte file may declare any size, and each forged image asks the device for that much memory
+    (the real attack: 20000x30000, gigabytes).  It must not take the batch down.  Scaled to a 48 MB chunk budget:
+    2000x1500 forgeries (18 MB each) decode -- the budget cuts the chunk after two of them and the rest follows in
+    the next chunk -- a 4000x3000 forgery (73 MB) exceeds the budget by itself and fails alone, and every ordinary
+    image of the batch decodes bit-exactly."""
+    good = [S.stream(f, w, h, 0) for f, w, h in (("420", 233, 177), ("444", 64, 48), ("gray", 129, 65), ("420_rst16", 256, 128))]
+    big = _forge_sof_size(S.stream("420", 17, 9, 0), 2000, 1500)
+    huge = _forge_sof_size(S.stream("420", 17, 9, 0), 4000, 3000)
+    batch = [good[0], big, good[1], huge, good[2], big, big, good[3], big]
+    d = ic.BatchDecoder(device=0, device_mem_mb=48, chunk_images=16)
+    outs = d.decode(batch, 3)
+    for i, (data, got) in enumerate(zip(batch, outs)):
+        if data is huge:
+            assert got is None, i
+        else:  # the forgeries decode in the reference too (zero bits past the end of the scan)
+            _check(oracle, got, data, 3, f"image {i} of a batch with oversized neighbours")
+    # staged form: what does not fit the budget of the one chunk fails alone with "outofmem", the rest decodes
+    n = d.prepare(batch, 3)
+    assert 6 <= n < len(batch) - 1, n
+    d.run()
+    d.sync()
+    for i, data in enumerate(batch):
+        if d.status(i):
+            _check(oracle, d.fetch(i), data, 3, f"staged image {i}")
+        else:
+            assert data in (big, huge) and d.reason(i) == "outofmem", i
+    d.close()
+
+
+def test_blocks_no_scan_writes_are_zero_not_stale(oracle):
+    """a baseline file that lost a restart marker (the scan ends early, jpeg.c:1184-1187) or a whole
+    component leaves blocks that no scan writes.  The reference shows uninitialised heap there; here they must be
+    ZERO coefficients -- never what an earlier batch left in the reused slab -- so the result is deterministic and
+    equals the decode on a fresh object."""
+    noise = [S.stream("420_rst16", 256, 128, 0), S.stream("444", 256, 128, 2)] * 4
+    raw = bytearray(S.stream("420_rst1", 256, 128, 1))
+    rst = [i for i in range(len(raw) - 1) if raw[i] == 0xFF and 0xD0 <= raw[i + 1] <= 0xD7]
+    cut = rst[len(rst) // 2]
+    eoi = raw.rindex(b"\xff\xd9")
+    lost = bytes(raw[:cut]) + bytes(raw[eoi:])  # half the restart intervals, then EOI
+    fresh = ic.BatchDecoder(device=0)
+    want = fresh.decode([lost], 3)[0]
+    fresh.close()
+    assert want is not None
+    d = ic.BatchDecoder(device=0)
+    for _ in range(2):
+        d.decode(noise, 3)  # fill the slab with other images' coefficients
+        got = d.decode([lost], 3)[0]
+        assert got is not None and np.array_equal(got, want)
+    d.close()
+    # rows the scan did reach equal the reference's; the rest is the IDCT of zero blocks (grey 128 luma, neutral chroma)
+    ref, *_ = oracle.load_from_memory(lost, 3)
+    assert ref is not None and np.array_equal(got[:48], ref[:48])
+    assert np.all(got[-16:] == got[-1, -1])
+
+
+def test_per_image_calls_are_reentrant(oracle):
+    """The reference is re-entrant (fresh state per call, jpeg.c:2445-2450): 8 threads x 100 stbi_load_from_memory
+    calls on different files must all be bit-exact, whatever interleaving the context pool gives them."""
+    import threading
+
+    cases = [("420", 233, 177), ("444", 129, 65), ("gray", 256, 128), ("420_rst16", 256, 128), ("420_prog", 129, 65),
+             ("422", 64, 48), ("420_opt", 233, 177), ("cmyk", 64, 48)]
+    datas = [S.stream(f, w, h, i % 3) for i, (f, w, h) in enumerate(cases)]
+    wants = [oracle.load_from_memory(s_, 3)[0] for s_ in datas]
+    errors = []
+
+    def worker(t):
+        try:
+            for k in range(100):
+                i = (t + k) % len(datas)
+                got, x, y, c = ic.stbi_load_from_memory(datas[i], 3)
+                if got is None or not np.array_equal(got, wants[i]):
+                    errors.append((t, k, cases[i]))
+                    return
+            if ic.stbi_load_from_memory(b"junk", 3)[0] is not None or ic.failure_reason() != "unknown image type":
+                errors.append((t, "failure reason is not thread-local"))
+        except Exception as e:  # pragma: no cover
+            errors.append((t, repr(e)))
+
+    ths = [threading.Thread(target=worker, args=(t,)) for t in range(8)]
+    for th in ths:
+        th.start()
+    for th in ths:
+        th.join()
+    assert not errors, errors[:3]
+
+
+def test_multi_device_entry_point_in_c(oracle):
+    """stbi_jpeg_decode_batch_multi: the split (contiguous, byte-balanced), one host thread + pipeline per device and
+    the join all happen in C.  Two 'devices' are always driven -- the same GPU twice where the box has one, two
+    different GPUs where it has more -- and every image must come back bit-exact and in place."""
+    cases = S.small_matrix()[:48]
+    datas = [S.stream(f, w, h, k) for f, w, h, k in cases]
+    datas += [b"not a jpeg", datas[0][:50]]
+    ngpu = ic.cuda_device_count()
+    for devices in ([0, 0], [0, 1] if ngpu >= 2 else [0, 0, 0], None):
+        m = ic.MultiDecoder(devices=devices, chunk_images=8)
+        for rc in (3, 0):
+            outs = m.decode(datas, rc)
+            split = m.last_split()
+            assert split[0] == 0 and split[-1] == len(datas) and split == sorted(split), split
+            for i, (data, got) in enumerate(zip(datas, outs)):
+                want, *_ = oracle.load_from_memory(data, rc)
+                if want is None:
+                    assert got is None, i
+                else:
+                    assert got is not None and np.array_equal(got, want), (devices, rc, i)
+        if m.n_devices > 1:
+            sizes = [sum(len(s_) for s_ in datas[a:b]) for a, b in zip(split, split[1:])]
+            assert max(sizes) - min(sizes) <= 2 * max(len(s_) for s_ in datas), sizes
+        assert m.decode([], 3) == []
+        m.close()

@@ -746,7 +746,7 @@ static void batch_enqueue_fetch_all(stbi_jpeg_batch *b, int n, stbi_uc *const *o
 	size_t run_src = 0, run_bytes = 0;
 	stbi_uc *run_dst = NULL;
 	int i;
-	const int merge = !b->params.no_download_merge;
+	const int merge = !(b->params.no_download_merge & 1);
 	for (i = 0; i < n; ++i)
 	{
 		const jcu_image *im = &b->images[i];
@@ -926,6 +926,8 @@ API int stbi_jpeg_decode_batch(stbi_jpeg_batch *b, const stbi_uc *const *bufs, c
 					depth = k0 + 1;
 					break;
 				}
+				if (b->params.no_download_merge & 2) /* tuning: one FIFO download stream for the whole pipeline */
+					jcu_share_download_stream(b->pipe[k0]->ctx, b->ctx);
 			}
 	}
 	{

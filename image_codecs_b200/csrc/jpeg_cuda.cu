@@ -57,7 +57,8 @@ struct jcu_ctx
 	std::vector<SsWork> ss_work_h; /* self-synchronising decode: CTA work items over all waves */
 	std::vector<SsScan> ss_scan_h;
 	uint32_t ss_nsub_total = 0, ss_max_nsub = 0;
-	int ss_rounds = 0; /* refine rounds the last run needed */
+	int ss_rounds = 0; /* refine rounds the last run needed (read back with the per-image errors) */
+	int ss_coop_ctas = 0; /* CTAs of k_ss_refine_loop that are resident at once on this device */
 	/* batch metadata kept on the host */
 	int n_images = 0, n_waves = 0;
 	size_t coef_elems = 0, out_bytes = 0;
@@ -79,6 +80,15 @@ struct jcu_ctx
 	int launches = 0;
 	int force_generic = 0;
 	int rows_per_band = 8; /* 4:2:0 strip kernel: MCU rows per CTA, chosen per batch */
+	/* pinned staging of the descriptor arrays: a cudaMemcpyAsync from pageable memory blocks the host until the stream
+	   has reached it (behind the bitstream upload: 4-8 ms per 512-image chunk), which starves the chunk pipeline */
+	unsigned char *pin_desc = nullptr;
+	size_t pin_desc_cap = 0;
+	/* per-image failure words + the self-sync round count, published by a last tiny kernel into MAPPED pinned memory:
+	   a device-to-host copy of a few bytes would queue behind the bulk pixel downloads of the other pipeline
+	   objects on the copy engine (measured: 7-12 ms per chunk) */
+	int32_t *err_host = nullptr, *err_host_dev = nullptr;
+	size_t err_host_cap = 0; /* int32 words incl. the 2 trailing self-sync words */
 	char errstr[256] = {0};
 };
 
@@ -182,6 +192,12 @@ extern "C" int jcu_ctx_create_opts(const jcu_ctx_options *o, jcu_ctx **out)
 	/* tables (static) + slots and rings (dynamic) exceed the 48 KB default */
 	cudaFuncSetAttribute(k_entropy_baseline<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ENTB_DYN_SMEM);
 	cudaFuncSetAttribute(k_entropy_baseline<4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ENTB_DYN_SMEM);
+	{
+		int per_sm = 0, sms = 0;
+		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ss_refine_loop, SS_THREADS, 0);
+		cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+		c->ss_coop_ctas = std::max(1, per_sm * sms);
+	}
 	*out = c;
 	return 0;
 }
@@ -207,6 +223,10 @@ extern "C" void jcu_ctx_destroy(jcu_ctx *c)
 		if (ev)
 			cudaEventDestroy(ev);
 	cudaStreamSynchronize(c->dl_use);
+	if (c->pin_desc)
+		cudaFreeHost(c->pin_desc);
+	if (c->err_host)
+		cudaFreeHost(c->err_host);
 	cudaEventDestroy(c->ev_ready);
 	cudaEventDestroy(c->ev_dl);
 	cudaStreamDestroy(c->dl_own);
@@ -502,30 +522,65 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 		CK(ensure(c->ss_changed, 256));
 	}
 
+	if ((size_t)b->n_images + 2 > c->err_host_cap)
+	{
+		if (c->err_host)
+			cudaFreeHost(c->err_host);
+		c->err_host = nullptr;
+		c->err_host_cap = 0;
+		const size_t want = (size_t)b->n_images + 2 + 64;
+		CK(cudaHostAlloc((void **)&c->err_host, want * sizeof(int32_t), cudaHostAllocMapped));
+		CK(cudaHostGetDevicePointer((void **)&c->err_host_dev, c->err_host, 0));
+		c->err_host_cap = want;
+	}
+	/* ---- descriptors go through one pinned staging block, so that no copy below blocks the host ---- */
+	struct Part
+	{
+		const void *src;
+		size_t bytes;
+		void *dst;
+	};
+	const Part parts[] = {
+		{imgs.data(), sizeof(jcu_image) * (size_t)b->n_images, c->images.p},
+		{b->scans, sizeof(jcu_scan) * (size_t)b->n_scans, c->scans.p},
+		{b->seg_start, sizeof(uint32_t) * (size_t)b->n_segs, c->segs.p},
+		{b->huff, sizeof(jcu_huff_spec) * (size_t)b->n_huff, c->huff.p},
+		{c->work_h.data(), sizeof(EntWork) * c->work_h.size(), c->work.p},
+		{c->ss_work_h.data(), sizeof(SsWork) * c->ss_work_h.size(), c->ss_work.p},
+		{c->ss_scan_h.data(), sizeof(SsScan) * c->ss_scan_h.size(), c->ss_scans.p},
+		{c->list_h.data(), sizeof(int32_t) * c->list_h.size(), c->lists.p},
+	};
+	size_t desc_bytes = 0;
+	for (const Part &pt : parts)
+		desc_bytes += (pt.bytes + 255) & ~(size_t)255;
+	if (desc_bytes > c->pin_desc_cap)
+	{
+		/* the previous batch of this context has been waited for (jcu_sync) before its buffers are prepared again */
+		if (c->pin_desc)
+			cudaFreeHost(c->pin_desc);
+		c->pin_desc = nullptr;
+		c->pin_desc_cap = 0;
+		const size_t want = desc_bytes + desc_bytes / 4 + 4096;
+		CK(cudaHostAlloc((void **)&c->pin_desc, want, cudaHostAllocDefault));
+		c->pin_desc_cap = want;
+	}
 	if (c->profile)
 		CK(cudaEventRecord(c->ev_h2d0, c->stream));
+	{
+		size_t off = 0;
+		for (const Part &pt : parts)
+		{
+			if (!pt.bytes)
+				continue;
+			memcpy(c->pin_desc + off, pt.src, pt.bytes);
+			CK(cudaMemcpyAsync(pt.dst, c->pin_desc + off, pt.bytes, cudaMemcpyHostToDevice, c->stream));
+			off += (pt.bytes + 255) & ~(size_t)255;
+		}
+	}
 	if (b->bitstream_bytes)
 		CK(cudaMemcpyAsync(c->bits.p, b->bitstream, b->bitstream_bytes, cudaMemcpyHostToDevice, c->stream));
-	if (b->n_images)
-		CK(cudaMemcpyAsync(c->images.p, imgs.data(), sizeof(jcu_image) * b->n_images, cudaMemcpyHostToDevice, c->stream));
-	if (b->n_scans)
-		CK(cudaMemcpyAsync(c->scans.p, b->scans, sizeof(jcu_scan) * b->n_scans, cudaMemcpyHostToDevice, c->stream));
-	if (b->n_segs)
-		CK(cudaMemcpyAsync(c->segs.p, b->seg_start, sizeof(uint32_t) * b->n_segs, cudaMemcpyHostToDevice, c->stream));
-	if (b->n_huff)
-		CK(cudaMemcpyAsync(c->huff.p, b->huff, sizeof(jcu_huff_spec) * b->n_huff, cudaMemcpyHostToDevice, c->stream));
-	if (!c->work_h.empty())
-		CK(cudaMemcpyAsync(c->work.p, c->work_h.data(), sizeof(EntWork) * c->work_h.size(), cudaMemcpyHostToDevice, c->stream));
-	if (!c->ss_scan_h.empty())
-	{
-		CK(cudaMemcpyAsync(c->ss_work.p, c->ss_work_h.data(), sizeof(SsWork) * c->ss_work_h.size(), cudaMemcpyHostToDevice, c->stream));
-		CK(cudaMemcpyAsync(c->ss_scans.p, c->ss_scan_h.data(), sizeof(SsScan) * c->ss_scan_h.size(), cudaMemcpyHostToDevice, c->stream));
-	}
-	if (!c->list_h.empty())
-		CK(cudaMemcpyAsync(c->lists.p, c->list_h.data(), sizeof(int32_t) * c->list_h.size(), cudaMemcpyHostToDevice, c->stream));
 	if (c->profile)
 		CK(cudaEventRecord(c->ev_h2d1, c->stream));
-	/* the staging vector `imgs` is pageable: cudaMemcpyAsync has consumed it before returning */
 	return 0;
 }
 
@@ -546,6 +601,15 @@ extern "C" int jcu_reserve(jcu_ctx *c, size_t bitstream_bytes, size_t coef_elems
 	CK(ensure(c->err, sizeof(int32_t) * 4));
 	CK(ensure(c->lists, sizeof(int32_t) * 16));
 	return 0;
+}
+
+__global__ void k_publish_status(const int32_t *__restrict__ err, int n, const int32_t *__restrict__ ss_result, int32_t *__restrict__ host)
+{
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n)
+		host[i] = err[i];
+	if (i < 2)
+		host[n + i] = ss_result ? ss_result[i] : 0;
 }
 
 extern "C" int jcu_run(jcu_ctx *c)
@@ -616,30 +680,31 @@ extern "C" int jcu_run(jcu_ctx *c)
 		sb.nblk = (uint32_t *)c->ss_nblk.p;
 		sb.first_blk = (uint32_t *)c->ss_first.p;
 		sb.changed = (int32_t *)c->ss_changed.p;
+		sb.sync = (uint32_t *)c->ss_changed.p + 4;
+		sb.result = (int32_t *)c->ss_changed.p + 8;
 		const unsigned nw = (unsigned)c->ss_work_h.size(), ns = (unsigned)c->ss_scan_h.size();
 		const SsWork *wk = (const SsWork *)c->ss_work.p;
 #define SS_ARGS wk, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p, (const jcu_huff_spec *)c->huff.p, \
 					 (const uint8_t *)c->bits.p, (int16_t *)c->coef.p, (int32_t *)c->err.p, sb
 		k_ss_decode<SS_GUESS><<<nw, SS_THREADS, 0, st>>>(SS_ARGS, 0);
 		c->launches++;
-		int parity = 0;
-		c->ss_rounds = 0;
-		for (uint32_t round = 0; round < c->ss_max_nsub + 2; ++round)
+		/* the Jacobi rounds run to convergence inside ONE cooperative launch (grid barrier per round, jpeg_selfsync.cuh):
+		   no flag copy, no stream synchronisation, the host never learns the round count before jcu_image_errors */
+		CK(cudaMemsetAsync(c->ss_changed.p, 0, 64, st));
 		{
-			int32_t changed = 0;
-			CK(cudaMemsetAsync(sb.changed, 0, sizeof(int32_t), st));
-			k_ss_refine<<<nw, SS_THREADS, 0, st>>>(wk, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p,
-																(const jcu_huff_spec *)c->huff.p, (const uint8_t *)c->bits.p, sb, parity);
-			c->launches++;
-			parity ^= 1;
-			c->ss_rounds++;
-			CK(cudaMemcpyAsync(&changed, sb.changed, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-			CK(cudaStreamSynchronize(st)); /* the round count is data dependent */
-			if (!changed)
-				break;
+			const SsWork *a_work = wk;
+			unsigned a_nw = nw, a_max = c->ss_max_nsub + 2u;
+			const jcu_scan *a_scans = (const jcu_scan *)c->scans.p;
+			const uint32_t *a_segs = (const uint32_t *)c->segs.p;
+			const jcu_huff_spec *a_huff = (const jcu_huff_spec *)c->huff.p;
+			const uint8_t *a_bits = (const uint8_t *)c->bits.p;
+			void *args[] = {&a_work, &a_nw, &a_scans, &d_img, &a_segs, &a_huff, &a_bits, &sb, &a_max};
+			const unsigned grid = std::min<unsigned>(nw, (unsigned)std::max(1, c->ss_coop_ctas));
+			CK(cudaLaunchCooperativeKernel((const void *)k_ss_refine_loop, dim3(grid), dim3(SS_THREADS), args, 0, st));
 		}
+		c->launches++;
 		k_ss_scan<<<ns, 256, 0, st>>>((const SsScan *)c->ss_scans.p, sb.nblk, sb.first_blk);
-		k_ss_decode<SS_WRITE><<<nw, SS_THREADS, 0, st>>>(SS_ARGS, parity);
+		k_ss_decode<SS_WRITE><<<nw, SS_THREADS, 0, st>>>(SS_ARGS, -1); /* parity: read from sb.result[0] */
 		k_ss_dc<<<dim3(ns, 4), SS_DC_THREADS, 0, st>>>((const SsScan *)c->ss_scans.p, (const jcu_scan *)c->scans.p, d_img, (int16_t *)c->coef.p);
 		c->launches += 3;
 #undef SS_ARGS
@@ -678,6 +743,13 @@ extern "C" int jcu_run(jcu_ctx *c)
 	CK(cudaGetLastError());
 	if (c->profile)
 		CK(cudaEventRecord(c->ev_out1, st));
+	if (c->err_host_dev)
+	{
+		const int n = std::max(0, c->n_images);
+		k_publish_status<<<(n + 2 + 255) / 256, 256, 0, st>>>((const int32_t *)c->err.p, n,
+																				c->ss_scan_h.empty() ? nullptr : (const int32_t *)c->ss_changed.p + 8, c->err_host_dev);
+		CK(cudaGetLastError());
+	}
 	return 0;
 }
 
@@ -697,6 +769,13 @@ extern "C" int jcu_sync(jcu_ctx *c)
 		c->dl_open = false;
 	}
 	return 0;
+}
+
+/* tuning: downloads of `c` are queued on `owner`'s download stream (one FIFO for a whole chunk pipeline) */
+extern "C" void jcu_share_download_stream(jcu_ctx *c, jcu_ctx *owner)
+{
+	if (c && owner)
+		c->dl_use = owner->dl_own;
 }
 
 extern "C" int jcu_download(jcu_ctx *c, size_t off, size_t bytes, void *dst)
@@ -752,8 +831,11 @@ extern "C" void *jcu_device_wide(jcu_ctx *c) { return c->wide.p; }
 extern "C" int jcu_image_errors(jcu_ctx *c, int32_t *errs, int n)
 {
 	CK(cudaSetDevice(c->device));
-	CK(cudaMemcpyAsync(errs, c->err.p, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, c->stream));
-	CK(cudaStreamSynchronize(c->stream));
+	CK(cudaStreamSynchronize(c->stream)); /* the last kernel of jcu_run has written the mapped host words */
+	if (!c->err_host || n > c->n_images)
+		return set_err(c, cudaErrorInvalidValue, "jcu_image_errors: no run to report");
+	memcpy(errs, c->err_host, sizeof(int32_t) * (size_t)n);
+	c->ss_rounds = c->ss_scan_h.empty() ? 0 : c->err_host[c->n_images + 1];
 	return 0;
 }
 

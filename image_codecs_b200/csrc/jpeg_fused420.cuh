@@ -40,7 +40,7 @@
 #include "jpeg_output.cuh"
 
 #ifndef S420_MIN_CTAS
-#define S420_MIN_CTAS (512 / S420_THREADS) /* resident CTAs per SM asked of the register allocator (5 and 6 measured: +1 %) */
+#define S420_MIN_CTAS (640 / S420_THREADS) /* resident CTAs per SM asked of the register allocator: 5 x 128 threads = 96 registers, no spills, 45 KB of shared memory each */
 #endif
 #ifndef S420_THREADS
 #define S420_THREADS 128
@@ -51,11 +51,11 @@
 #define S420_YW (S420_MS * 16)					  /* luma sample row, bytes */
 #define S420_CW (8 * S420_MC + 4)								  /* chroma ring row stride in words (>= 8 * S420_MC, == 20 mod 32) */
 #define S420_OFF_Y (S420_SLOTS * 128)
-#define S420_OFF_C (S420_OFF_Y + 16 * S420_YW)
-#define S420_OFF_P (S420_OFF_C + 2 * 8 * S420_CW * 4)
-#define S420_OFF_Q (S420_OFF_P + 2 * S420_CW * 4)
-#define S420_OFF_BAR (S420_OFF_Q + 3 * 64 * 2)
-#define S420_SMEM_BYTES (S420_OFF_BAR + 16)
+#define S420_OFF_C (S420_OFF_Y + 2 * 16 * S420_YW)			/* two luma planes: IDCT of row r+1 may start while row r is still read */
+#define S420_OFF_P (S420_OFF_C + 3 * 8 * S420_CW * 4) /* three chroma slots: MCU rows r, r+1 (bottom halo), r+2 (being written) */
+#define S420_OFF_Q (S420_OFF_P + 2 * S420_CW * 4)		/* two line buffers: last chroma row of MCU row r-1 (top halo) */
+#define S420_OFF_BAR(DEQ) (S420_OFF_Q + ((DEQ) ? 3 * 64 * 2 : 0)) /* the quantiser tables are staged for progressive files only */
+#define S420_SMEM_BYTES(DEQ) (S420_OFF_BAR(DEQ) + 16)
 
 /* ---- mbarrier + bulk async copy (TMA, non-tensor form) ---- */
 __device__ __forceinline__ uint32_t s420_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -135,36 +135,100 @@ __device__ __forceinline__ void s420_load_block(const uint4 *__restrict__ slot, 
 #ifndef S420_FMA_ROW
 #define S420_FMA_ROW false
 #endif
+#ifndef S420_COL_MODE
+#define S420_COL_MODE 0 /* idct_1d MODE of the column pass */
+#endif
+#ifndef S420_ROW_MODE
+#define S420_ROW_MODE 0
+#endif
+#ifndef S420_SPLIT
+#define S420_SPLIT 0 /* 1 = the column pass writes a second register array instead of updating v[] in place */
+#endif
 __device__ __forceinline__ void s420_idct(int (&v)[64], uint32_t (&rows)[16])
 {
 	int o[8];
+#if S420_SPLIT
+	int u[64];
+#else
+	int(&u)[64] = v;
+#endif
 #pragma unroll
 	for (int c = 0; c < 8; ++c)
 	{
-		idct_1d<S420_FMA_COL>(v[c], v[c + 8], v[c + 16], v[c + 24], v[c + 32], v[c + 40], v[c + 48], v[c + 56], 512, o);
+		idct_1d<S420_FMA_COL, S420_COL_MODE>(v[c], v[c + 8], v[c + 16], v[c + 24], v[c + 32], v[c + 40], v[c + 48], v[c + 56], 512, o);
 #pragma unroll
 		for (int r = 0; r < 8; ++r)
-			v[c + 8 * r] = o[r] >> 10;
+			u[c + 8 * r] = o[r] >> 10;
 	}
 #pragma unroll
 	for (int r = 0; r < 8; ++r)
 	{
-		idct_1d<S420_FMA_ROW>(v[8 * r], v[8 * r + 1], v[8 * r + 2], v[8 * r + 3], v[8 * r + 4], v[8 * r + 5], v[8 * r + 6], v[8 * r + 7],
+		idct_1d<S420_FMA_ROW, S420_ROW_MODE>(u[8 * r], u[8 * r + 1], u[8 * r + 2], u[8 * r + 3], u[8 * r + 4], u[8 * r + 5], u[8 * r + 6], u[8 * r + 7],
 				  65536 + (128 << 17), o);
 		rows[2 * r] = s420_pack4(o[0] >> 17, o[1] >> 17, o[2] >> 17, o[3] >> 17);
 		rows[2 * r + 1] = s420_pack4(o[4] >> 17, o[5] >> 17, o[6] >> 17, o[7] >> 17);
 	}
 }
 
-/* four chroma samples (bytes of cbw / crw) -> four ring words 16*Cb+8 | (16*(Cr-128)+8) << 16 */
+#ifdef S420_STREAM_TEST
+/* EXPERIMENT (layout not yet matched): chunk 2j+h holds rows 4h..4h+3 of columns 2j, 2j+1 */
+template <bool DEQ>
+__device__ __forceinline__ void s420_idct_stream(const uint4 *__restrict__ slot, unsigned key, const uint16_t *__restrict__ q, uint32_t (&rows)[16])
+{
+	int u[64];
+	int o[8];
+#pragma unroll
+	for (int j = 0; j < 4; ++j)
+	{
+		const uint4 a = slot[(2 * j) ^ key], b = slot[(2 * j + 1) ^ key];
+		const uint32_t ws[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+		int lo[8], hi[8];
+#pragma unroll
+		for (int r = 0; r < 8; ++r)
+		{
+			lo[r] = (int)(int16_t)(ws[r] & 0xffffu);
+			hi[r] = ((int)ws[r]) >> 16;
+		}
+		idct_1d<S420_FMA_COL, S420_COL_MODE>(lo[0], lo[1], lo[2], lo[3], lo[4], lo[5], lo[6], lo[7], 512, o);
+#pragma unroll
+		for (int r = 0; r < 8; ++r)
+			u[2 * j + 8 * r] = o[r] >> 10;
+		idct_1d<S420_FMA_COL, S420_COL_MODE>(hi[0], hi[1], hi[2], hi[3], hi[4], hi[5], hi[6], hi[7], 512, o);
+#pragma unroll
+		for (int r = 0; r < 8; ++r)
+			u[2 * j + 1 + 8 * r] = o[r] >> 10;
+	}
+#pragma unroll
+	for (int r = 0; r < 8; ++r)
+	{
+		idct_1d<S420_FMA_ROW, S420_ROW_MODE>(u[8 * r], u[8 * r + 1], u[8 * r + 2], u[8 * r + 3], u[8 * r + 4], u[8 * r + 5], u[8 * r + 6], u[8 * r + 7],
+				  65536 + (128 << 17), o);
+		rows[2 * r] = s420_pack4(o[0] >> 17, o[1] >> 17, o[2] >> 17, o[3] >> 17);
+		rows[2 * r + 1] = s420_pack4(o[4] >> 17, o[5] >> 17, o[6] >> 17, o[7] >> 17);
+	}
+}
+#endif
+
+/* four chroma samples (bytes of cbw / crw) -> four ring words 16*Cb+8 | (16*(Cr-128)+8) << 16.
+   Two byte permutes interleave the even / odd samples of both planes, one more per sample spreads a (Cb, Cr) pair
+   over the two 16-bit fields with zeros above (the zero register is the second source), one multiply-add scales and
+   biases both fields: 2.5 instructions per sample. */
+__device__ __forceinline__ uint32_t s420_spread(uint32_t pairs, uint32_t sel)
+{
+	uint32_t d;
+	asm("prmt.b32 %0, %1, 0, %2;" : "=r"(d) : "r"(pairs), "r"(sel));
+	return d;
+}
 __device__ __forceinline__ uint4 s420_chroma_words(uint32_t cbw, uint32_t crw)
 {
 	const uint32_t K = 0xF8080008u; /* 8 | (8 - 16*128) << 16 */
+	const uint32_t ev = __byte_perm(cbw, crw, 0x6240); /* Cb0 Cr0 Cb2 Cr2 */
+	const uint32_t od = __byte_perm(cbw, crw, 0x7351); /* Cb1 Cr1 Cb3 Cr3 */
 	uint4 r;
-	r.x = (__byte_perm(cbw, crw, 0x0400) & 0x00ff00ffu) * 16u + K;
-	r.y = (__byte_perm(cbw, crw, 0x0501) & 0x00ff00ffu) * 16u + K;
-	r.z = (__byte_perm(cbw, crw, 0x0602) & 0x00ff00ffu) * 16u + K;
-	r.w = (__byte_perm(cbw, crw, 0x0703) & 0x00ff00ffu) * 16u + K;
+	r.x = s420_spread(ev, 0x4140u) * 16u + K;
+	r.y = s420_spread(od, 0x4140u) * 16u + K;
+	r.z = s420_spread(ev, 0x4342u) * 16u + K;
+	r.w = s420_spread(od, 0x4342u) * 16u + K;
 	return r;
 }
 
@@ -210,12 +274,12 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 {
 	extern __shared__ __align__(128) unsigned char s420_smem[];
 	uint4 *sCoef = reinterpret_cast<uint4 *>(s420_smem);
-	uint8_t *sY = s420_smem + S420_OFF_Y;											  /* [16][S420_YW] */
-	uint32_t *sC = reinterpret_cast<uint32_t *>(s420_smem + S420_OFF_C);	  /* [2][8][S420_CW] */
-	uint32_t *sP = reinterpret_cast<uint32_t *>(s420_smem + S420_OFF_P);	  /* [2][S420_CW] */
+	uint8_t *sY = s420_smem + S420_OFF_Y;											  /* [2][16][S420_YW] */
+	uint32_t *sC = reinterpret_cast<uint32_t *>(s420_smem + S420_OFF_C);	  /* [3][8][S420_CW]: chroma of MCU row c lives in slot c % 3 */
+	uint32_t *sP = reinterpret_cast<uint32_t *>(s420_smem + S420_OFF_P);	  /* [2][S420_CW], directly behind sC */
 	uint16_t(*sQ)[64] = reinterpret_cast<uint16_t(*)[64]>(s420_smem + S420_OFF_Q);
-	uint64_t *bar = reinterpret_cast<uint64_t *>(s420_smem + S420_OFF_BAR);
-	__shared__ int2 sRow[16]; /* per pixel row of the current MCU row: word offsets (from sC) of its near / far chroma rows */
+	uint64_t *bar = reinterpret_cast<uint64_t *>(s420_smem + S420_OFF_BAR(DEQ));
+	__shared__ int2 sRow[2][16]; /* per pixel row of MCU row r (buffer r & 1): word offsets (from sC) of its near / far chroma rows */
 
 	const jcu_image *im = &images[list[blockIdx.y]];
 	const int strips = im->tiles_x;
@@ -274,6 +338,7 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 	const int cbx = m0 - 1 + cpos;
 	const bool cvalid = !isY && ct < 2 * Mc && cbx >= 0 && cbx < cbw;
 	const int slot = isY ? tid : (nY + ci * Mc + cpos);
+	const int slot_safe = min(slot, S420_SLOTS - 1); /* lanes beyond the strip's blocks read a valid slot and discard the result */
 	const int yrow = (isY && tid >= 2 * Ms) ? 1 : 0, lbx = tid - yrow * 2 * Ms;
 	const bool chroma_warp = (tid | 31) >= nY; /* warp-uniform: this warp holds chroma lanes */
 
@@ -294,38 +359,52 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 		s420_mbar_wait(bar, parity);
 		parity ^= 1u;
 
+		/* chroma slots of MCU rows r-1, r, r+1 (r >= -1) */
+		const int sl_prev = (r + 2) % 3, sl_cur = (r + 3) % 3, sl_next = (r + 4) % 3;
+		/* The slot of row r-1 is the one the IDCT of iteration r+1 overwrites (with row r+2) while slower warps may
+		   still be in the pixel phase of row r: its last row, the top halo of row r, moves to a line buffer first.
+		   Row r-1 has been complete since the barrier of iteration r-2. */
+		if (doY && r > 0)
+			for (int c = tid; c < S420_CW; c += S420_THREADS)
+				sP[(r & 1) * S420_CW + c] = sC[(sl_prev * 8 + 7) * S420_CW + c];
 		/* row selection of the h2v2 resampler (jpeg.c:2301-2318) for the 16 pixel rows of MCU row r */
 		if (tid < 16 && doY)
 		{
 			const int ly = tid, lk = ly >> 1, k = r * 8 + lk;
-			const int nr = ((r & 1) * 8 + lk) * S420_CW;
+			const int nr = (sl_cur * 8 + lk) * S420_CW;
 			int fr;
 			if (ly & 1)
-				fr = (k + 1 > cy - 1) ? nr : (lk < 7 ? nr + S420_CW : (((r + 1) & 1) * 8) * S420_CW);
+				fr = (k + 1 > cy - 1) ? nr : (lk < 7 ? nr + S420_CW : (sl_next * 8) * S420_CW);
 			else
-				fr = (lk > 0) ? nr - S420_CW : (r == 0 ? nr : (16 + (r & 1)) * S420_CW); /* line buffer sP follows sC */
-			sRow[ly] = make_int2(nr, (r * 16 + ly < H) ? fr : -1);
+				fr = (lk > 0) ? nr - S420_CW : (r == 0 ? nr : (24 + (r & 1)) * S420_CW); /* line buffer sP follows sC */
+			sRow[r & 1][ly] = make_int2(nr, (r * 16 + ly < H) ? fr : -1);
 		}
 		/* ---- IDCT phase: luma of MCU row r, chroma of MCU row r+1 ---- */
 		{
 			int v[64];
 			uint32_t rows[16];
-			if ((isY && doY) || (cvalid && doC))
+			/* warp-uniform: a warp none of whose lanes has a block this iteration (luma warps in the chroma-only
+			   prologue) skips the phase; inside, lanes without a block transform whatever their slot holds and store
+			   nothing, so no value has to be merged from a second path */
+			if (!__any_sync(0xffffffffu, (isY && doY) || (cvalid && doC)))
+				goto idct_done;
+#ifdef S420_SKIP_IDCT /* timing experiment only */
+			if (r != 12345)
+				goto idct_done;
+#endif
 			{
 				const int16_t *g = isY ? baseY + ((size_t)(2 * r + yrow) * ybw + 2 * m0 + lbx) * 64
 											  : (ci ? baseCr : baseCb) + ((size_t)(r + 1) * cbw + cbx) * 64;
-				s420_load_block<DEQ>(&sCoef[slot * 8], coef_key(g), sQ[isY ? 0 : 1 + ci], v);
+#ifdef S420_STREAM_TEST
+				s420_idct_stream<DEQ>(&sCoef[slot_safe * 8], coef_key(g), sQ[isY ? 0 : 1 + ci], rows);
+#else
+				s420_load_block<DEQ>(&sCoef[slot_safe * 8], coef_key(g), sQ[isY ? 0 : 1 + ci], v);
 				s420_idct(v, rows);
-			}
-			else
-			{
-#pragma unroll
-				for (int i = 0; i < 16; ++i)
-					rows[i] = 0u;
+#endif
 			}
 			if (isY && doY)
 			{
-				uint8_t *d = sY + (yrow * 8) * S420_YW + lbx * 8;
+				uint8_t *d = sY + ((r & 1) * 16 + yrow * 8) * S420_YW + lbx * 8;
 #pragma unroll
 				for (int rr = 0; rr < 8; ++rr)
 					*reinterpret_cast<uint2 *>(d + rr * S420_YW) = make_uint2(rows[2 * rr], rows[2 * rr + 1]);
@@ -334,7 +413,7 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 			{
 				/* lanes (2p, 2p+1) = (Cb, Cr) of one position: the Cb lane keeps rows 0-3, the Cr lane rows 4-7 */
 				const bool store = cvalid && doC;
-				uint32_t *dbase = sC + (((r + 1) & 1) * 8 + (ci ? 4 : 0)) * S420_CW + cpos * 8;
+				uint32_t *dbase = sC + (sl_next * 8 + (ci ? 4 : 0)) * S420_CW + cpos * 8;
 #pragma unroll
 				for (int rr = 0; rr < 4; ++rr)
 				{
@@ -368,19 +447,24 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 				}
 			}
 		}
+	idct_done:
 		__syncthreads();
 		if (tid == 0 && r + 1 < r1)
 			issue(r + 1);
 
 		/* ---- pixel phase: MCU row r, one task = 8 pixels of one row ---- */
+#ifdef S420_SKIP_PIXEL /* timing experiment only */
+		if (doY && r == 12345)
+#else
 		if (doY)
+#endif
 		{
 			uint8_t *orow0 = obase + (long long)(r * 16) * pitch + m0 * 16 * N;
 			int ly = ly_first, g = g_first;
 #pragma unroll 1
 			while (ly < 16)
 			{
-				const int2 rw = sRow[ly]; /* word offsets of the near / far chroma rows; far < 0: row beyond the image */
+				const int2 rw = sRow[r & 1][ly]; /* word offsets of the near / far chroma rows; far < 0: row beyond the image */
 				const int gx0 = m0 * 16 + g * 8;
 				if (rw.y >= 0 && (full_w || gx0 < W))
 				{
@@ -395,7 +479,7 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 						t[4] = 3u * n4.w + f4.w;
 						t[5] = 3u * np[4] + fp[4];
 					}
-					const uint2 yv = *reinterpret_cast<const uint2 *>(sY + ly * S420_YW + g * 8);
+					const uint2 yv = *reinterpret_cast<const uint2 *>(sY + ((r & 1) * 16 + ly) * S420_YW + g * 8);
 					int R[8], Gc[8], B[8];
 					/* (3*t[i] + t[i-1 or i+1] + 8) >> 4 (jpeg.c:1832-1833) on both chroma fields at once */
 					s420_colour<0>(3u * t[1] + t[0], yv.x, R[0], Gc[0], B[0]);
@@ -459,11 +543,11 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 				}
 			}
 		}
-		/* keep the last chroma row of MCU row r for the top halo of row r+1 */
-		if (r >= 0 && r + 1 < r1)
-			for (int c = tid; c < S420_CW; c += S420_THREADS)
-				sP[((r + 1) & 1) * S420_CW + c] = sC[((r & 1) * 8 + 7) * S420_CW + c];
-		__syncthreads();
+		/* ONE barrier per iteration.  The luma plane, the row table and the top-halo line are double buffered and the
+		   chroma ring has three slots, so a warp that is done with the pixels of row r goes straight on to the IDCT of
+		   row r+1 (it writes plane (r+1)&1 and chroma slot (r+2)%3, neither of which the pixel phase of row r reads)
+		   and only waits, at the barrier above, for everybody's IDCT of row r+1 -- which also proves that nobody still
+		   reads row r-1. */
 	}
 }
 
@@ -476,9 +560,10 @@ static inline cudaError_t fused420_launch(int max_tiles, const int32_t *list, in
 	void (*k)(const int32_t *, const jcu_image *, const int16_t *, uint8_t *, int) =
 		 n_out == 4 ? (deq ? k_fused420_strip<4, true> : k_fused420_strip<4, false>)
 						: (deq ? k_fused420_strip<3, true> : k_fused420_strip<3, false>);
-	cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, S420_SMEM_BYTES);
+	const int smem = deq ? S420_SMEM_BYTES(1) : S420_SMEM_BYTES(0);
+	cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
 	if (e != cudaSuccess)
 		return e;
-	k<<<dim3((unsigned)max_tiles, (unsigned)nlist), S420_THREADS, S420_SMEM_BYTES, st>>>(list, images, coef, out, rows_per_band);
+	k<<<dim3((unsigned)max_tiles, (unsigned)nlist), S420_THREADS, smem, st>>>(list, images, coef, out, rows_per_band);
 	return cudaGetLastError();
 }

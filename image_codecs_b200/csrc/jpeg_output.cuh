@@ -27,16 +27,51 @@
 /* FMA_A: the two shift-adds a0, a1 as multiply-adds whose multiplier comes from constant memory (ptxas cannot turn
    them back into LEA): the fused kernels are bound by the ALU pipe, the FMA pipe has room */
 __constant__ int c_idct_4096 = 4096;
-template <bool FMA_A = false>
+__device__ __forceinline__ int idct_mad(int a, int b, int c) /* pinned multiply-add: one IMAD on the FMA pipe */
+{
+	int d;
+	asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+	return d;
+}
+/* MODE selects how the additions are split between the two math pipes (the fused kernels are bound by the ALU
+   pipe: IADD3 / SHF / PRMT / LEA / I2IP; IMAD runs on the FMA pipe).  All modes give the same 32-bit values.
+     0  even part factored (3 adds + 5 multiply-adds), outputs as eight IADD3
+     1  every addition of the even part rides on a multiply-add (8 IMAD, no ALU op)
+     2  MODE 1 and the output butterfly folded into the odd part's chains: o[i] = x_i + d_i is the chain's addend,
+        o[7-i] = 2 x_i - o[i] (26 IMAD + 6 ALU instead of 21 + 11) */
+template <bool FMA_A = false, int MODE = 0>
 __device__ __forceinline__ void idct_1d(int s0, int s1, int s2, int s3, int s4, int s5, int s6, int s7, int bias,
 													 int (&o)[8])
 {
+	if (MODE == 2)
+	{
+		const int zb = idct_mad(s2, 2217, idct_mad(s6, 2217, bias));	/* z + bias */
+		const int zn = idct_mad(s2, -2217, idct_mad(s6, -2217, bias)); /* -z + bias */
+		const int e3b = idct_mad(s2, 3135, zb), e3n = idct_mad(s2, -3135, zn);
+		const int e2b = idct_mad(s6, -7567, zb), e2n = idct_mad(s6, 7567, zn);
+		const int p = s0 + s4, m = s0 - s4;
+		const int x0 = idct_mad(p, 4096, e3b), x3 = idct_mad(p, 4096, e3n);
+		const int x1 = idct_mad(m, 4096, e2b), x2 = idct_mad(m, 4096, e2n);
+		o[0] = idct_mad(s1, 5683, idct_mad(s3, 4816, idct_mad(s5, 3219, idct_mad(s7, 1131, x0))));
+		o[1] = idct_mad(s1, 4816, idct_mad(s3, -1129, idct_mad(s5, -5681, idct_mad(s7, -3218, x1))));
+		o[2] = idct_mad(s1, 3219, idct_mad(s3, -5681, idct_mad(s5, 1132, idct_mad(s7, 4816, x2))));
+		o[3] = idct_mad(s1, 1131, idct_mad(s3, -3218, idct_mad(s5, 4816, idct_mad(s7, -5680, x3))));
+		o[7] = x0 + x0 - o[0];
+		o[6] = x1 + x1 - o[1];
+		o[5] = x2 + x2 - o[2];
+		o[4] = x3 + x3 - o[3];
+		return;
+	}
 	/* even part (jpeg.c:580-591): p1 = (s2+s6)*f2f(0.5411961); t2 = p1 - s6*f2f(1.847759065); t3 = p1 + s2*f2f(0.765366865) */
-	const int z = (s2 + s6) * 2217;
-	const int e2 = z + s6 * -7567;
-	const int e3 = z + s2 * 3135;
-	const int a0 = FMA_A ? (s0 + s4) * c_idct_4096 + bias : (s0 + s4) * 4096 + bias;
-	const int a1 = FMA_A ? (s0 - s4) * c_idct_4096 + bias : (s0 - s4) * 4096 + bias;
+	const int z = MODE == 1 ? idct_mad(s2, 2217, s6 * 2217) : (s2 + s6) * 2217;
+	const int e2 = MODE == 1 ? idct_mad(s6, -7567, z) : z + s6 * -7567;
+	const int e3 = MODE == 1 ? idct_mad(s2, 3135, z) : z + s2 * 3135;
+	const int a0 = MODE == 1	? idct_mad(s0, 4096, idct_mad(s4, 4096, bias))
+						: FMA_A	? (s0 + s4) * c_idct_4096 + bias
+									: (s0 + s4) * 4096 + bias;
+	const int a1 = MODE == 1	? idct_mad(s0, 4096, idct_mad(s4, -4096, bias))
+						: FMA_A	? (s0 - s4) * c_idct_4096 + bias
+									: (s0 - s4) * 4096 + bias;
 	/* odd part (jpeg.c:592-612) multiplied out: in the ring Z/2^32 the reference's factored butterfly
 	   (p5 = (p3+p4)*f2f(1.175875602), t0..t3 *= ..., t3 += p1+p4, ...) equals this 4x4 integer matrix,
 	   e.g. d3 = s1*(6149+4816-3685-1597) + s3*4816 + s5*(4816-1597) + s7*(4816-3685); 16 multiply-adds, no adds */

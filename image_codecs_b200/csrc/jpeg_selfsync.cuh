@@ -64,7 +64,9 @@ struct SsBuffers
 	SsState *entry_used;		  /* entry state the current exit state was computed from */
 	uint32_t *nblk;			  /* blocks completed inside each subsequence */
 	uint32_t *first_blk;		  /* exclusive prefix of nblk within the scan */
-	int32_t *changed;			  /* any exit state changed in the last round */
+	int32_t *changed;			  /* [3] rotating flags: round t sets changed[t % 3] when an exit state changed */
+	uint32_t *sync;			  /* [0] arrivals at the grid barrier of k_ss_refine_loop, [1] its generation */
+	int32_t *result;			  /* [0] ping-pong side that holds the final exit states, [1] refine launches-worth of rounds run */
 };
 
 struct SBR
@@ -187,6 +189,8 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 	const uint32_t scan_start = seg_start[sc->seg_first], end = sc->data_end;
 	const bool last = i + 1 == w.scan_nsub;
 	const uint32_t limit = last ? end : scan_start + (i + 1) * SS_SUB_BYTES;
+	if (parity < 0)
+		parity = sb.result[0]; /* left there by k_ss_refine_loop */
 	const SsState *cur = parity ? sb.exit_b : sb.exit_a;
 	SsState *nxt = parity ? sb.exit_a : sb.exit_b;
 	const int nblk_mcu = sh.nblk;
@@ -351,15 +355,12 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
  * A thread whose entry state did not change does not decode again.
  */
 #define SS_INNER 8
-__global__ void __launch_bounds__(SS_THREADS)
-k_ss_refine(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans, const jcu_image *__restrict__ images,
-				const uint32_t *__restrict__ seg_start, const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ bitstream,
-				SsBuffers sb, int parity)
+__device__ __forceinline__ void ss_refine_item(EntbShared &sh, SsState *s_exit, const SsWork w, const jcu_scan *__restrict__ scans,
+															  const jcu_image *__restrict__ images, const uint32_t *__restrict__ seg_start,
+															  const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ bitstream, const SsBuffers &sb,
+															  int parity, int32_t *changed_flag)
 {
-	__shared__ EntbShared sh;
-	__shared__ SsState s_exit[SS_THREADS];
 	const int tid = threadIdx.x;
-	const SsWork w = work[blockIdx.x];
 	const jcu_scan *sc = &scans[w.scan];
 	const jcu_image *im = &images[sc->image];
 	entb_setup(sh, sc, im, huff, tid, SS_THREADS);
@@ -443,7 +444,71 @@ k_ss_refine(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 		sb.entry_used[gi] = used;
 		nxt[gi] = mine;
 		if (!ss_same(mine, first))
-			atomicOr(sb.changed, 1);
+			atomicOr(changed_flag, 1);
+	}
+	__syncthreads(); /* the next work item of this CTA rebuilds the tables and reuses s_exit */
+}
+
+/* barrier over all CTAs of a cooperative launch (they are co-resident): arrivals counter + generation */
+__device__ __forceinline__ void ss_grid_barrier(uint32_t *sync, unsigned nctas)
+{
+	__syncthreads();
+	if (threadIdx.x == 0)
+	{
+		volatile uint32_t *gen = sync + 1;
+		const uint32_t g = *gen;
+		__threadfence(); /* this CTA's exit states before its arrival */
+		if (atomicAdd(sync, 1u) == nctas - 1u)
+		{
+			sync[0] = 0u;
+			__threadfence();
+			atomicAdd(sync + 1, 1u);
+		}
+		else
+			while (*gen == g)
+				__nanosleep(40);
+		__threadfence();
+	}
+	__syncthreads();
+}
+
+/*
+ * Phase 2 WITHOUT the host: one cooperative launch runs the Jacobi rounds to convergence.  Every round the CTAs share
+ * out the work items (each item = SS_INNER in-CTA iterations as above), meet at a grid barrier and read the round's
+ * "anything changed" flag; the side of the ping-pong that holds the final exit states goes to sb.result[0] for the
+ * write pass.  The reference has no counterpart (its decoder is serial, jpeg.c:1198-1232); what this replaces is
+ * one kernel launch + one device-to-host flag copy + one stream synchronisation per round.
+ */
+__global__ void __launch_bounds__(SS_THREADS)
+k_ss_refine_loop(const SsWork *__restrict__ work, unsigned nwork, const jcu_scan *__restrict__ scans, const jcu_image *__restrict__ images,
+					  const uint32_t *__restrict__ seg_start, const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ bitstream,
+					  SsBuffers sb, unsigned max_rounds)
+{
+	__shared__ EntbShared sh;
+	__shared__ SsState s_exit[SS_THREADS];
+	int parity = 0;
+	unsigned round = 0;
+	for (; round < max_rounds; ++round)
+	{
+		int32_t *flag = sb.changed + round % 3u;
+		for (unsigned it = blockIdx.x; it < nwork; it += gridDim.x)
+			ss_refine_item(sh, s_exit, work[it], scans, images, seg_start, huff, bitstream, sb, parity, flag);
+		parity ^= 1;
+		ss_grid_barrier(sb.sync, gridDim.x);
+		const int32_t any = *reinterpret_cast<volatile int32_t *>(flag);
+		/* the flag of round + 2 was last read behind the barrier of round - 1, which everybody has left */
+		if (blockIdx.x == 0 && threadIdx.x == 0)
+			sb.changed[(round + 2u) % 3u] = 0;
+		if (!any)
+		{
+			++round;
+			break;
+		}
+	}
+	if (blockIdx.x == 0 && threadIdx.x == 0)
+	{
+		sb.result[0] = parity;
+		sb.result[1] = (int32_t)round;
 	}
 }
 

@@ -138,7 +138,8 @@ typedef struct
 	int device_mem_mb;	 /* device memory ONE prepared chunk may ask for; 0 = auto (a share of the device).  A chunk
 									 that would need more is cut and continued; an image that needs more by itself fails
 									 alone with "outofmem" */
-	int no_download_merge; /* 1 = one device->host copy per image instead of merged copies of up to 64 MB */
+	int no_download_merge; /* bit 0: one device->host copy per image instead of merged copies of up to 64 MB; bit 1: all
+									 pipeline objects queue their copies on ONE stream (FIFO) instead of one stream each */
 	int trace;				 /* 1 = host timeline of the chunk pipeline on stderr */
 	/* test switches (0 in production) */
 	int force_generic;	 /* every image takes the generic two-pass output path */

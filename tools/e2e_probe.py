@@ -35,7 +35,8 @@ for i in range(n):
     caps[i] = per
 st = (C.c_int * n)()
 for prof in ((False,) if os.environ.get('QUICK') else (True, False)):
-    d = ic.BatchDecoder(device=0, profile=prof, chunk_images=chunk, host_threads=int(os.environ.get('HT', '0')))
+    d = ic.BatchDecoder(device=0, profile=prof, chunk_images=chunk, host_threads=int(os.environ.get('HT', '0')),
+                        trace=int(os.environ.get('TRACE', '0')), pipeline_depth=int(os.environ.get('DEPTH', '0')), no_download_merge=int(os.environ.get('DLMODE', '0')))
     d.decode_into(bufs, lens, n, 3, outs, caps, None, None, None, st)
     t0 = time.perf_counter()
     rc = d.decode_into(bufs, lens, n, 3, outs, caps, None, None, None, st)

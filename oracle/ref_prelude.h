@@ -37,14 +37,21 @@ static int stbi__sse2_available(void) { return 1; }
 #define STBI_SIMD_ALIGN(type, name) type name
 #endif
 
+#ifndef ORACLE_PUBLIC_TYPES_FROM_PRODUCT_HEADER /* ref_stub_unity.c takes the public types from include/image_api.h */
 typedef unsigned char stbi_uc;
 typedef unsigned short stbi_us;
+#endif
 typedef uint16_t stbi__uint16;
 typedef int16_t stbi__int16;
 typedef uint32_t stbi__uint32;
 typedef int32_t stbi__int32;
 
+#ifdef ORACLE_PUBLIC_TYPES_FROM_PRODUCT_HEADER
+#undef STBIDEF
+#define STBIDEF /* the reference's own definitions of stbi_load* stay inside the library (-fvisibility=hidden) */
+#else
 #define STBIDEF extern __attribute__((visibility("default")))
+#endif
 #define STBIWDEF extern __attribute__((visibility("default")))
 #define stbi_inline inline
 #define STBI_ASSERT(x) assert(x)
@@ -57,15 +64,19 @@ typedef int32_t stbi__int32;
 #define stbi_lrot(x, y) (((x) << (y)) | ((x) >> (-(y)&31)))
 #define STBIW_UCHAR(x) (unsigned char)((x)&0xff)
 
+#ifndef ORACLE_PUBLIC_TYPES_FROM_PRODUCT_HEADER
 enum { STBI_default = 0, STBI_grey = 1, STBI_grey_alpha = 2, STBI_rgb = 3, STBI_rgb_alpha = 4 };
+#endif
 enum { STBI_ORDER_RGB, STBI_ORDER_BGR };
 
+#ifndef ORACLE_PUBLIC_TYPES_FROM_PRODUCT_HEADER
 typedef struct
 {
 	int (*read)(void *user, char *data, int size);
 	void (*skip)(void *user, int n);
 	int (*eof)(void *user);
 } stbi_io_callbacks;
+#endif
 
 typedef struct
 {

@@ -22,6 +22,7 @@
 #include "jpeg_output.cuh"
 #include "jpeg_fused420.cuh"
 #include "jpeg_fused1x1.cuh"
+#include "jpeg_fused422.cuh"
 
 struct DevBuf
 {
@@ -70,11 +71,11 @@ struct jcu_ctx
 	std::vector<int> wave_ncoop;	  /* per wave: trailing work items that are single-segment progressive AC scans (jpeg_entropy_prog.cuh) */
 	std::vector<int> wave_nsmall;	  /* per wave: work items after the baseline ones that are progressive scans of <= 32 segments */
 	std::vector<int32_t> list_h; /* image lists per path, concatenated */
-	int list_off[4] = {0, 0, 0, 0}, list_n[4] = {0, 0, 0, 0};
-	int tiles[4] = {0, 0, 0, 0};
-	int path_n[4] = {3, 3, 3, 3};
-	int path_deq[4] = {0, 0, 0, 0};
-	int path_maxtiles[4] = {0, 0, 0, 0};
+	int list_off[JCU_PATH_COUNT] = {0, 0, 0, 0, 0}, list_n[JCU_PATH_COUNT] = {0, 0, 0, 0, 0};
+	int tiles[JCU_PATH_COUNT] = {0, 0, 0, 0, 0};
+	int path_n[JCU_PATH_COUNT] = {3, 3, 3, 3, 3};
+	int path_deq[JCU_PATH_COUNT] = {0, 0, 0, 0, 0};
+	int path_maxtiles[JCU_PATH_COUNT] = {0, 0, 0, 0, 0};
 	int max_blocks_generic = 0;
 	long long max_pixels_generic = 0;
 	int launches = 0;
@@ -309,10 +310,10 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 
 	/* ---- per-path image lists and tile numbering ---- */
 	std::vector<jcu_image> imgs(b->images, b->images + b->n_images);
-	std::vector<int32_t> lists[4];
+	std::vector<int32_t> lists[JCU_PATH_COUNT];
 	c->max_blocks_generic = 0;
 	c->max_pixels_generic = 0;
-	for (int p = 0; p < 4; ++p)
+	for (int p = 0; p < JCU_PATH_COUNT; ++p)
 		c->tiles[p] = c->path_deq[p] = c->path_maxtiles[p] = 0;
 	{
 		/* band height of the 4:2:0 strip kernel: tall bands amortise the two-row chroma prologue, but the
@@ -350,6 +351,11 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 				im.tiles_x = (im.mcu_x + S420_MS - 1) / S420_MS;						/* strips */
 				im.tiles_y = (im.mcu_y + c->rows_per_band - 1) / c->rows_per_band; /* bands */
 			}
+			else if (p == JCU_PATH_FUSED_422)
+			{
+				im.tiles_x = (im.mcu_x + F2_MS - 1) / F2_MS;
+				im.tiles_y = (im.mcu_y + F2_ROWS_PER_BAND - 1) / F2_ROWS_PER_BAND;
+			}
 			else
 			{
 				const int bs = p == JCU_PATH_FUSED_444 ? F1_BS(3) : F1_BS(1);
@@ -362,7 +368,7 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 		}
 	}
 	c->list_h.clear();
-	for (int p = 0; p < 4; ++p)
+	for (int p = 0; p < JCU_PATH_COUNT; ++p)
 	{
 		c->list_off[p] = (int)c->list_h.size();
 		c->list_n[p] = (int)lists[p].size();
@@ -724,11 +730,14 @@ extern "C" int jcu_run(jcu_ctx *c)
 		k_generic_color<<<g2, 256, 0, st>>>(lst, d_img, (const uint8_t *)c->planes.p, (uint8_t *)c->out.p);
 		c->launches += 2;
 	}
-	for (int p = 1; p < 4; ++p)
+	for (int p = 1; p < JCU_PATH_COUNT; ++p)
 		if (c->list_n[p] > 0)
 		{
 			const int32_t *lst = (const int32_t *)c->lists.p + c->list_off[p];
-			cudaError_t e = p == JCU_PATH_FUSED_420
+			cudaError_t e = p == JCU_PATH_FUSED_422
+									  ? fused422_launch(c->path_maxtiles[p], lst, c->list_n[p], d_img, d_coef, (uint8_t *)c->out.p, st,
+															  c->path_n[p], c->path_deq[p])
+								  : p == JCU_PATH_FUSED_420
 									  ? fused420_launch(c->path_maxtiles[p], lst, c->list_n[p], d_img, d_coef, (uint8_t *)c->out.p, st,
 															  c->path_n[p], c->path_deq[p], c->rows_per_band)
 								  : p == JCU_PATH_FUSED_444

@@ -636,6 +636,8 @@ static void choose_output(parser *p, int req_comp)
 			im->path = JCU_PATH_FUSED_420;
 		else if (c[0].h == 1 && c[0].v == 1 && c[1].h == 1 && c[1].v == 1 && c[2].h == 1 && c[2].v == 1)
 			im->path = JCU_PATH_FUSED_444;
+		else if (c[0].h == 2 && c[0].v == 1 && c[1].h == 1 && c[1].v == 1 && c[2].h == 1 && c[2].v == 1)
+			im->path = JCU_PATH_FUSED_422;
 	}
 	p->r->coef_blocks = 0;
 	for (i = 0; i < im->decode_n; ++i)

@@ -46,6 +46,18 @@ struct SsState
 	uint64_t buf; /* the buffered bits themselves (implied by pos/aux; kept so a successor can resume) */
 };
 __device__ __forceinline__ bool ss_same(const SsState &a, const SsState &b) { return a.pos == b.pos && a.aux == b.aux; }
+/* exit states cross CTA boundaries INSIDE one launch of k_ss_refine_loop: read them from L2, never from an L1 line that
+   an earlier round left behind */
+static_assert(sizeof(SsState) == 16, "SsState is read as one 16-byte word");
+__device__ __forceinline__ SsState ss_load_l2(const SsState *p)
+{
+	const uint4 v = __ldcg(reinterpret_cast<const uint4 *>(p));
+	SsState s;
+	s.pos = v.x;
+	s.aux = v.y;
+	s.buf = (uint64_t)v.z | ((uint64_t)v.w << 32);
+	return s;
+}
 
 /* one CTA work item: up to SS_THREADS consecutive subsequences of one scan */
 struct SsWork
@@ -380,8 +392,8 @@ __device__ __forceinline__ void ss_refine_item(EntbShared &sh, SsState *s_exit, 
 	used = mine;
 	if (valid)
 	{
-		mine = cur[gi];
-		used = sb.entry_used[gi];
+		mine = ss_load_l2(&cur[gi]);
+		used = ss_load_l2(&sb.entry_used[gi]);
 	}
 	const SsState first = mine;
 	for (int it = 0; it < SS_INNER; ++it)
@@ -389,7 +401,7 @@ __device__ __forceinline__ void ss_refine_item(EntbShared &sh, SsState *s_exit, 
 		bool changed = false;
 		if (valid && i > 0 && (it == 0 || tid > 0))
 		{
-			const SsState en = it == 0 ? cur[gi - 1] : s_exit[tid - 1];
+			const SsState en = it == 0 ? ss_load_l2(&cur[gi - 1]) : s_exit[tid - 1];
 			if (!ss_same(en, used))
 			{
 				used = en;

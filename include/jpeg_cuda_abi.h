@@ -50,7 +50,9 @@ enum
 	JCU_PATH_GENERIC = 0, /* two-pass: IDCT to planes, then resample+colour (any H,V, any mode) */
 	JCU_PATH_FUSED_420 = 1, /* fused tile kernel, 3 comps 2x2/1x1/1x1, YCbCr -> RGB/RGBA */
 	JCU_PATH_FUSED_444 = 2, /* fused tile kernel, 3 comps 1x1, YCbCr -> RGB/RGBA */
-	JCU_PATH_FUSED_GRAY = 3 /* fused tile kernel, component 0 only -> 1..4 channels */
+	JCU_PATH_FUSED_GRAY = 3, /* fused tile kernel, component 0 only -> 1..4 channels */
+	JCU_PATH_FUSED_422 = 4,	 /* fused strip kernel, 3 comps 2x1/1x1/1x1 (h_2 upsampling, jpeg.c:1784), YCbCr -> RGB/RGBA */
+	JCU_PATH_COUNT = 5
 };
 
 /* raw DHT contents (jpeg.c:1381-1416): the device builds its own lookup tables from these */

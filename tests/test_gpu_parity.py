@@ -149,6 +149,36 @@ def test_fused_420_strips_and_bands(oracle, rows_per_band):
         d.close()
 
 
+def test_fused_422_strips_and_edges(oracle):
+    """4:2:2 strip kernel (jpeg_fused422.cuh; stbi__resample_row_h_2, jpeg.c:1784-1812): images wider than one
+    480-pixel strip (2, 3 and 5 strips, a 1-MCU last strip), every residue of the width modulo 16 around a strip
+    boundary -- the asymmetric out[2w-2] sample (jpeg.c:1805) then falls on every position of a pixel group, in the
+    halo block and in the strip's first block --, w_lores 1 and 2, more MCU rows than one band, RGB and RGBA, baseline,
+    progressive (output-time dequantisation), restart markers, and the flipped store order."""
+    from tools import testenc as te
+
+    cases = []
+    for w in list(range(465, 500)) + [1, 2, 3, 4, 15, 16, 17, 31, 32, 33, 959, 960, 961, 1443, 2400]:
+        cases.append((w, 37 if w < 600 else 19, dict()))
+    cases += [(1000, 300, dict()), (523, 140, dict(progressive=1)), (700, 90, dict(restart_interval=3)),
+              (481, 129, dict(progressive=1, restart_interval=7)), (1920, 1080, dict(restart_interval=16))]
+    datas = [te.encode(te.synth_rgb(w, h, i % 3, 600 + i), quality=90, subsampling="422", **kw) for i, (w, h, kw) in enumerate(cases)]
+    d = ic.BatchDecoder(device=0)
+    for rc in (3, 4, 0):
+        outs = d.decode(datas, rc)
+        for (w, h, kw), data, got in zip(cases, datas, outs):
+            _check(oracle, got, data, rc, f"422 {w}x{h} {kw} req{rc}")
+    ic.set_flip_vertically_on_load(True)
+    try:
+        outs = d.decode(datas[:40], 3)
+        for (w, h, kw), data, got in zip(cases, datas, outs):
+            want, *_ = oracle.load_from_memory(data, 3)
+            assert got is not None and np.array_equal(got, want[::-1]), f"flipped 422 {w}x{h}"
+    finally:
+        ic.set_flip_vertically_on_load(False)
+    d.close()
+
+
 def test_full_size_1080p_420_rst16(oracle, decoder):
     """BASELINE.json configs[1] geometry: 1920x1080 4:2:0 q90 restart interval 16 (two distinct images)."""
     from tools import testenc as te

@@ -281,7 +281,7 @@ def run_c1(args, ic, distinct, ncores, local_rank):
                     "d2h_bytes_per_step": args.width * args.height * 3, "ms_per_step": float(lat.mean()),
                     "buffers": "pageable (malloc'ed result, as the reference returns)"},
             "gpu_launches": per_load * n, "roofline": None, "cpu_baseline": cpu}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def bind_to_gpu_numa(local_rank):
@@ -312,8 +312,26 @@ def bind_to_gpu_numa(local_rank):
         return {"bound": False, "why": str(e)[:80]}
 
 
+_REAL_STDOUT = None
+
+
+def emit(line: dict) -> None:
+    """The ONE JSON line goes to the real stdout; everything else this process (NCCL, torch, the libraries) prints on
+    fd 1 was pointed at stderr at start-up."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    global _REAL_STDOUT
     args = parse_args()
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)  # e.g. "NCCL version ..." is written to fd 1 by the library itself
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -346,7 +364,7 @@ def main():
                 "cpu_baseline": {"value": v, "unit": UNIT, "cores": nthreads, "kind": kind, "sample": desc},
                 "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
-        print(json.dumps(line), flush=True)
+        emit(line)
         return
 
     # ------------------------------------------------------------------ our arm
@@ -563,7 +581,7 @@ def main():
                        "selfsync_scans": tm.get("selfsync_scans"), "selfsync_rounds": tm.get("selfsync_rounds"),
                        "wall_ms_per_step": wall_ms / args.steps},
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 

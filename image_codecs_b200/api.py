@@ -104,8 +104,6 @@ def lib() -> C.CDLL:
     L.jcu_ctx_destroy.argtypes = [C.c_void_p]
     L.jcu_test_idct_blocks.restype = C.c_int
     L.jcu_test_idct_blocks.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
-    L.jcu_test_ycbcr.restype = C.c_int
-    L.jcu_test_ycbcr.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
     L.jcu_read_coefs.restype = C.c_int
     L.jcu_read_coefs.argtypes = [C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p]
     L.jcu_error_string.restype = C.c_char_p

@@ -409,7 +409,9 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 		SsScan e;
 		e.scan = s;
 		e.base = c->ss_nsub_total;
-		e.nsub = (bytes + SS_SUB_BYTES - 1) / SS_SUB_BYTES;
+		/* the unstuffing threads cut the scan on 256-byte boundaries of the FILE (aligned 16-byte loads), so a scan that
+		   starts mid-chunk needs one chunk more; the decoding subsequences (unstuffed bytes) never outnumber them */
+		e.nsub = ((start & (SS_SUB_BYTES - 1u)) + bytes + SS_SUB_BYTES - 1) / SS_SUB_BYTES;
 		e.pad = 0;
 		c->ss_scan_h.push_back(e);
 		for (uint32_t f = 0; f < e.nsub; f += SS_THREADS)
@@ -499,7 +501,7 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 		bool any_base = false;
 		for (int w = 0; w < b->n_waves; ++w)
 			any_base = any_base || c->wave_nbase[w] > 0;
-		if (any_base)
+		if (any_base || !c->ss_scan_h.empty()) /* the self-synchronising path unstuffs its scans into the same slab */
 		{
 			CK(ensure(c->uslab, b->bitstream_bytes + 32 * ((size_t)b->n_segs + 4)));
 			CK(ensure(c->useg_len, sizeof(uint32_t) * std::max<size_t>(1, b->n_segs)));
@@ -691,9 +693,16 @@ extern "C" int jcu_run(jcu_ctx *c)
 		const unsigned nw = (unsigned)c->ss_work_h.size(), ns = (unsigned)c->ss_scan_h.size();
 		const SsWork *wk = (const SsWork *)c->ss_work.p;
 #define SS_ARGS wk, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p, (const jcu_huff_spec *)c->huff.p, \
-					 (const uint8_t *)c->bits.p, (int16_t *)c->coef.p, (int32_t *)c->err.p, sb
-		k_ss_decode<SS_GUESS><<<nw, SS_THREADS, 0, st>>>(SS_ARGS, 0);
-		c->launches++;
+					 (const uint8_t *)c->bits.p, (const uint8_t *)c->uslab.p, (const uint32_t *)c->useg_len.p, (int16_t *)c->coef.p, \
+					 (int32_t *)c->err.p, sb
+		/* phase U: count the bytes each 256-byte raw chunk keeps, prefix sum per scan, write the unstuffed stream */
+		k_ss_unstuff<false><<<nw, SS_THREADS, 0, st>>>(wk, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p,
+																	  (const uint8_t *)c->bits.p, (uint8_t *)c->uslab.p, (uint32_t *)c->useg_len.p, sb);
+		k_ss_scan<<<ns, 256, 0, st>>>((const SsScan *)c->ss_scans.p, sb.nblk, sb.first_blk);
+		k_ss_unstuff<true><<<nw, SS_THREADS, 0, st>>>(wk, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p,
+																	 (const uint8_t *)c->bits.p, (uint8_t *)c->uslab.p, (uint32_t *)c->useg_len.p, sb);
+		k_ss_decode<SS_GUESS><<<nw, SS_THREADS, 0, st>>>(SS_ARGS);
+		c->launches += 4;
 		/* the Jacobi rounds run to convergence inside ONE cooperative launch (grid barrier per round, jpeg_selfsync.cuh):
 		   no flag copy, no stream synchronisation, the host never learns the round count before jcu_image_errors */
 		CK(cudaMemsetAsync(c->ss_changed.p, 0, 64, st));
@@ -703,14 +712,15 @@ extern "C" int jcu_run(jcu_ctx *c)
 			const jcu_scan *a_scans = (const jcu_scan *)c->scans.p;
 			const uint32_t *a_segs = (const uint32_t *)c->segs.p;
 			const jcu_huff_spec *a_huff = (const jcu_huff_spec *)c->huff.p;
-			const uint8_t *a_bits = (const uint8_t *)c->bits.p;
-			void *args[] = {&a_work, &a_nw, &a_scans, &d_img, &a_segs, &a_huff, &a_bits, &sb, &a_max};
+			const uint8_t *a_uslab = (const uint8_t *)c->uslab.p;
+			const uint32_t *a_ulen = (const uint32_t *)c->useg_len.p;
+			void *args[] = {&a_work, &a_nw, &a_scans, &d_img, &a_segs, &a_huff, &a_uslab, &a_ulen, &sb, &a_max};
 			const unsigned grid = std::min<unsigned>(nw, (unsigned)std::max(1, c->ss_coop_ctas));
 			CK(cudaLaunchCooperativeKernel((const void *)k_ss_refine_loop, dim3(grid), dim3(SS_THREADS), args, 0, st));
 		}
 		c->launches++;
 		k_ss_scan<<<ns, 256, 0, st>>>((const SsScan *)c->ss_scans.p, sb.nblk, sb.first_blk);
-		k_ss_decode<SS_WRITE><<<nw, SS_THREADS, 0, st>>>(SS_ARGS, -1); /* parity: read from sb.result[0] */
+		k_ss_decode<SS_WRITE><<<nw, SS_THREADS, 0, st>>>(SS_ARGS); /* entry states: side sb.result[0] */
 		k_ss_dc<<<dim3(ns, 4), SS_DC_THREADS, 0, st>>>((const SsScan *)c->ss_scans.p, (const jcu_scan *)c->scans.p, d_img, (int16_t *)c->coef.p);
 		c->launches += 3;
 #undef SS_ARGS
@@ -963,7 +973,7 @@ extern "C" int jcu_encode_sync(jcu_ctx *c)
 
 extern "C" void *jcu_encode_device_out(jcu_ctx *c) { return c->enc_out.p; }
 
-/* ---- stage-level test entry points ---- */
+/* ---- stage-level entry points: the IDCT stage alone (jcu_test_idct_blocks, and its allocation-free twin below) ---- */
 __global__ void k_test_idct(const int16_t *coef, const uint16_t *qt, int n, uint8_t *out)
 {
 	int b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -977,20 +987,6 @@ __global__ void k_test_idct(const int16_t *coef, const uint16_t *qt, int n, uint
 	for (int i = 0; i < 16; ++i)
 		o[i] = rows[i];
 }
-__global__ void k_test_ycbcr(const uint8_t *y, const uint8_t *cb, const uint8_t *cr, int n, int step, uint8_t *out)
-{
-	int i = blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= n)
-		return;
-	int r, g, b;
-	ycbcr_to_rgb(y[i], cb[i], cr[i], r, g, b);
-	out[(size_t)i * step] = (uint8_t)r;
-	out[(size_t)i * step + 1] = (uint8_t)g;
-	out[(size_t)i * step + 2] = (uint8_t)b;
-	if (step == 4)
-		out[(size_t)i * step + 3] = 255;
-}
-
 extern "C" int jcu_test_idct_blocks(jcu_ctx *c, const int16_t *coef, const uint16_t *qt, int nblocks, uint8_t *out64)
 {
 	CK(cudaSetDevice(c->device));
@@ -1017,23 +1013,6 @@ extern "C" int jcu_test_idct_blocks(jcu_ctx *c, const int16_t *coef, const uint1
 	CK(cudaMemcpy(out64, d_o, (size_t)nblocks * 64, cudaMemcpyDeviceToHost));
 	cudaFree(d_c);
 	cudaFree(d_q);
-	cudaFree(d_o);
-	return 0;
-}
-
-extern "C" int jcu_test_ycbcr(jcu_ctx *c, const uint8_t *y, const uint8_t *cb, const uint8_t *cr, int n, int step, uint8_t *out)
-{
-	CK(cudaSetDevice(c->device));
-	uint8_t *d_in, *d_o;
-	CK(cudaMalloc(&d_in, (size_t)n * 3));
-	CK(cudaMalloc(&d_o, (size_t)n * step));
-	CK(cudaMemcpy(d_in, y, n, cudaMemcpyHostToDevice));
-	CK(cudaMemcpy(d_in + n, cb, n, cudaMemcpyHostToDevice));
-	CK(cudaMemcpy(d_in + 2 * (size_t)n, cr, n, cudaMemcpyHostToDevice));
-	k_test_ycbcr<<<(n + 255) / 256, 256, 0, c->stream>>>(d_in, d_in + n, d_in + 2 * (size_t)n, n, step, d_o);
-	CK(cudaStreamSynchronize(c->stream));
-	CK(cudaMemcpy(out, d_o, (size_t)n * step, cudaMemcpyDeviceToHost));
-	cudaFree(d_in);
 	cudaFree(d_o);
 	return 0;
 }

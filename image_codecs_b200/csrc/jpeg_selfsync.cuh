@@ -9,13 +9,16 @@
  * symbols (and, because EOB resets the zig-zag index and the block pattern of an MCU is short, with the
  * true block structure soon after):
  *
- *   1 guess    thread i starts at byte i*SS_SUB_BYTES assuming "start of an MCU" and records its EXIT state
- *              (bit position, block-in-MCU, zig-zag index) at the first symbol start past its boundary.
+ *   U unstuff  the scan's bytes with the stuffing resolved (FF 00 -> FF), written by all threads in parallel into the
+ *              unstuffed slab: per 256-byte raw chunk a count, a prefix sum, a second pass that stores.  Every later
+ *              phase reads bits with a stateless reader (bit position -> two words -> funnel shift).
+ *   1 guess    thread i starts at bit 2048 i of the unstuffed stream assuming "start of an MCU" and records its EXIT
+ *              state (bit position, block-in-MCU, zig-zag index) at the first symbol start past its boundary.
  *   2 refine   every thread re-decodes its subsequence from its predecessor's exit state (Jacobi rounds,
  *              double-buffered); subsequence 0 starts from the true state, so correctness spreads at least
  *              one subsequence per round and, thanks to self-synchronisation, in practice converges in a few
  *              rounds; a thread whose entry state did not change skips the work.  Rounds stop when no exit
- *              state changed.
+ *              state changed -- all inside ONE cooperative launch (grid barrier per round), no host round trip.
  *   3 scan     exclusive prefix sum of the number of blocks each subsequence completes.
  *   4 write    every thread decodes its subsequence once more from its (now true) entry state and writes
  *              (short)(value * dequant) coefficients (jpeg.c:345,365) into the pre-zeroed slab; DC symbols are
@@ -23,10 +26,8 @@
  *   5 dc       per component: prefix sum of the DC differences in decode order = the reference's running
  *              dc_pred (jpeg.c:323-325), stored as (short)(dc * dequant[0]).
  *
- * Exit states must be comparable between decoders with different histories, so this bit reader is
- * canonical: it tops the 64-bit buffer up to more than 56 bits at EVERY symbol start, which makes
- * (read offset, buffered bits) a function of the logical bit position alone.  Byte stuffing (FF 00) is
- * undone inline (jpeg.c:167-187); a scan without restart markers contains no other FF xx.
+ * An exit state is (bit position, zig-zag index, block-in-MCU): a function of where the decoder stands, not of how it
+ * got there, so states of decoders with different histories compare equal once they have fallen into step.
  */
 #pragma once
 #include <cuda_runtime.h>
@@ -37,25 +38,23 @@
 #include "jpeg_entropy_baseline.cuh"
 
 #define SS_THREADS 128
-#define SS_SUB_BYTES 256
+#define SS_SUB_BYTES 256 /* raw bytes per unstuffing thread AND unstuffed bytes per decoding subsequence */
 
+/* entry / exit state of a subsequence: everything a decoder needs to resume, and nothing that depends on its history */
 struct SsState
 {
-	uint32_t pos; /* read offset in the file (next byte to load) */
-	uint32_t aux; /* buffered bits | zig-zag index k << 8 | block-in-MCU << 16 | zero bytes among the buffered bits << 28 */
-	uint64_t buf; /* the buffered bits themselves (implied by pos/aux; kept so a successor can resume) */
+	uint32_t bp;  /* bit position in the unstuffed stream */
+	uint32_t aux; /* zig-zag index k (bits 0-7) | block-in-MCU (bits 8-19) */
 };
-__device__ __forceinline__ bool ss_same(const SsState &a, const SsState &b) { return a.pos == b.pos && a.aux == b.aux; }
+__device__ __forceinline__ bool ss_same(const SsState &a, const SsState &b) { return a.bp == b.bp && a.aux == b.aux; }
 /* exit states cross CTA boundaries INSIDE one launch of k_ss_refine_loop: read them from L2, never from an L1 line that
    an earlier round left behind */
-static_assert(sizeof(SsState) == 16, "SsState is read as one 16-byte word");
 __device__ __forceinline__ SsState ss_load_l2(const SsState *p)
 {
-	const uint4 v = __ldcg(reinterpret_cast<const uint4 *>(p));
+	const uint2 v = __ldcg(reinterpret_cast<const uint2 *>(p));
 	SsState s;
-	s.pos = v.x;
+	s.bp = v.x;
 	s.aux = v.y;
-	s.buf = (uint64_t)v.z | ((uint64_t)v.w << 32);
 	return s;
 }
 
@@ -66,7 +65,7 @@ struct SsWork
 	uint32_t first;	  /* index within the scan of this CTA's first subsequence */
 	uint32_t count;	  /* subsequences handled by this CTA */
 	uint32_t scan_base; /* global index of the scan's subsequence 0 */
-	uint32_t scan_nsub; /* subsequences in the scan */
+	uint32_t scan_nsub; /* subsequences in the scan (by RAW bytes: an upper bound of the unstuffed ones) */
 	uint32_t pad;
 };
 
@@ -74,96 +73,11 @@ struct SsBuffers
 {
 	SsState *exit_a, *exit_b; /* ping-pong exit states */
 	SsState *entry_used;		  /* entry state the current exit state was computed from */
-	uint32_t *nblk;			  /* blocks completed inside each subsequence */
-	uint32_t *first_blk;		  /* exclusive prefix of nblk within the scan */
+	uint32_t *nblk;			  /* blocks completed inside each subsequence (phase U: bytes each raw chunk keeps) */
+	uint32_t *first_blk;		  /* exclusive prefix of nblk within the scan (phase U: output offset of each raw chunk) */
 	int32_t *changed;			  /* [3] rotating flags: round t sets changed[t % 3] when an exit state changed */
 	uint32_t *sync;			  /* [0] arrivals at the grid barrier of k_ss_refine_loop, [1] its generation */
-	int32_t *result;			  /* [0] ping-pong side that holds the final exit states, [1] refine launches-worth of rounds run */
-};
-
-struct SBR
-{
-	uint32_t pos, end;
-	uint64_t buf;
-	int nbits;
-	int pad; /* zero bits appended past the scan's end that are still buffered (bottom of the valid bits); a function of the position */
-};
-
-/* canonical top-up: > 56 valid bits; past the scan's end (or a marker) feeds zero bits */
-__device__ __forceinline__ void sbr_topup(const uint8_t *__restrict__ base, SBR &br)
-{
-	while (br.nbits <= 56)
-	{
-		uint32_t b = 0;
-		bool real = false;
-		if (br.pos < br.end)
-		{
-			real = true;
-			b = base[br.pos++];
-			if (b == 0xff)
-			{
-				uint32_t q = br.pos;
-				uint32_t c = q < br.end ? base[q] : 0u;
-				while (c == 0xff)
-				{
-					++q;
-					c = q < br.end ? base[q] : 0u;
-				}
-				if (c == 0)
-					br.pos = q < br.end ? q + 1 : br.end;
-				else
-				{
-					br.pos = br.end;
-					b = 0;
-					real = false;
-				}
-			}
-		}
-		if (!real)
-			br.pad += 8;
-		br.buf |= (uint64_t)b << (56 - br.nbits);
-		br.nbits += 8;
-	}
-}
-
-/* one symbol + magnitude from a topped-up buffer; false = invalid code */
-template <int BITS, bool IS_DC>
-__device__ __forceinline__ bool ss_symbol(SBR &br, const EntbLutT<BITS> *__restrict__ L, int &value, int &kadv)
-{
-	const uint32_t top = (uint32_t)(br.buf >> 32);
-	uint32_t e = L->fast[top >> (32 - BITS)];
-	if (e == 0)
-	{
-		const uint32_t t16 = top >> 16;
-		int l = BITS + 1;
-		while (t16 >= L->limit[l])
-			++l;
-		if (l > 16)
-		{
-			br.buf <<= 16;
-			br.nbits -= 16;
-			return false;
-		}
-		e = entb_entry(L->vals[(L->base[l] + (int)(t16 >> (16 - l))) & 255], l, IS_DC);
-	}
-	const int len = (int)ENTB_E_LEN(e), size = (int)ENTB_E_SIZE(e);
-	kadv = (int)ENTB_E_KADV(e);
-	const uint32_t after = top << len;
-	const uint32_t s32 = 32u - (uint32_t)size;
-	const uint32_t v = shr_clamp(after, s32), mask = shr_clamp(0xffffffffu, s32);
-	const int t = (int)after >> 31;
-	value = (int)v - (int)(mask & ~(uint32_t)t);
-	const int total = len + size;
-	br.buf <<= total;
-	br.nbits -= total;
-	return true;
-}
-
-enum
-{
-	SS_GUESS = 0,
-	SS_REFINE = 1,
-	SS_WRITE = 2
+	int32_t *result;			  /* [0] ping-pong side that holds the final exit states, [1] rounds run */
 };
 
 /* per self-sync scan */
@@ -175,17 +89,246 @@ struct SsScan
 	uint32_t pad;
 };
 
+/* ------------------------------------------------------------------------------------------------------
+ * Phase U: byte stuffing out of the way, in parallel.  Inside [scan start, data_end) of a scan without restart
+ * markers every run of 0xFF bytes is followed by 0x00 (anything else would be the marker that ends the scan, and
+ * the host parser put data_end there), and stbi__grow_buffer_unsafe (jpeg.c:167-187) turns the whole run + the
+ * zero into ONE data byte 0xFF.  So a raw byte survives unless it is a 0x00 behind an 0xFF or an 0xFF in front of
+ * another 0xFF -- a rule that only looks one byte to each side.  Thread i counts the survivors of raw bytes
+ * [256 i, 256 i + 256), k_ss_scan turns the counts into offsets, and the second pass stores them as big-endian words
+ * (byte j of the stream at j ^ 3) in the segment's area of the unstuffed slab (entb_useg_off), zero padded like
+ * k_unstuff does, with useg_len in the same format.
+ * ------------------------------------------------------------------------------------------------------ */
+/* raw bytes [p0, p0 + 16) of the file as four little-endian words; p0 is 16-byte aligned in the (16-byte aligned, padded)
+   bitstream slab, so the load never leaves it */
+__device__ __forceinline__ uint4 ssu_load16(const uint8_t *__restrict__ base, uint32_t p0)
+{
+	return __ldg(reinterpret_cast<const uint4 *>(base + p0));
+}
+
+template <bool WRITE>
+__global__ void __launch_bounds__(SS_THREADS)
+k_ss_unstuff(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans, const jcu_image *__restrict__ images,
+				 const uint32_t *__restrict__ seg_start, const uint8_t *__restrict__ bitstream, uint8_t *__restrict__ uslab,
+				 uint32_t *__restrict__ useg_len, SsBuffers sb)
+{
+	const SsWork w = work[blockIdx.x];
+	if (threadIdx.x >= w.count)
+		return;
+	const jcu_scan *sc = &scans[w.scan];
+	const jcu_image *im = &images[sc->image];
+	const uint32_t i = w.first + threadIdx.x, gi = w.scan_base + i;
+	const uint8_t *__restrict__ base = bitstream + im->data_off; /* 16-byte aligned */
+	const uint32_t scan_start = seg_start[sc->seg_first], end = sc->data_end;
+	/* chunks are cut on 256-byte boundaries of the FILE (the first one is shorter), so every chunk is 16 aligned loads */
+	const uint32_t a0 = scan_start & ~(SS_SUB_BYTES - 1u);
+	const uint32_t lo = max(scan_start, min(end, a0 + i * SS_SUB_BYTES)), hi = min(end, a0 + (i + 1u) * SS_SUB_BYTES);
+	uint8_t *dst = WRITE ? uslab + entb_useg_off(im->data_off, scan_start, (uint32_t)sc->seg_first) : nullptr;
+	uint32_t j = WRITE ? sb.first_blk[gi] : 0u;
+	uint32_t acc = 0u, nacc = 0u; /* WRITE: bytes collected for the next big-endian word (valid once j is word aligned) */
+	if (lo < hi)
+	{
+		uint32_t prev = lo > scan_start ? (uint32_t)__ldg(base + lo - 1u) : 0u;
+		for (uint32_t p0 = lo & ~15u; p0 < hi; p0 += 16u)
+		{
+			const uint4 v = ssu_load16(base, p0);
+			/* the byte behind this unit decides whether its last 0xFF is a fill byte; behind the scan it reads as 0 */
+			const uint32_t after = p0 + 16u < end ? (uint32_t)__ldg(base + p0 + 16u) : 0u;
+			const uint32_t ws[5] = {v.x, v.y, v.z, v.w, after};
+#pragma unroll
+			for (int q = 0; q < 16; ++q)
+			{
+				const uint32_t p = p0 + (uint32_t)q;
+				const uint32_t cur = (ws[q >> 2] >> (8 * (q & 3))) & 255u;
+				uint32_t nxt = (ws[(q + 1) >> 2] >> (8 * ((q + 1) & 3))) & 255u;
+				if (p + 1u >= end)
+					nxt = 0u;
+				if (p >= lo && p < hi)
+				{
+					const bool drop = (cur == 0u && prev == 0xffu) || (cur == 0xffu && nxt == 0xffu);
+					if (!drop)
+					{
+						if (WRITE)
+						{
+							if ((j & 3u) || nacc) /* inside a word: collect; a word that starts before this chunk's bytes is byte-stored */
+							{
+								if (nacc == 0u) /* leading bytes of a word another chunk began */
+									dst[j ^ 3u] = (uint8_t)cur;
+								else
+								{
+									acc = (acc << 8) | cur;
+									if (++nacc == 4u)
+									{
+										*reinterpret_cast<uint32_t *>(dst + (j & ~3u)) = acc;
+										nacc = 0u;
+									}
+								}
+							}
+							else
+							{
+								acc = cur;
+								nacc = 1u;
+							}
+						}
+						++j;
+					}
+					prev = cur;
+				}
+			}
+		}
+	}
+	if (!WRITE)
+		sb.nblk[gi] = j;
+	/* trailing bytes of a word the next chunk completes */
+	for (uint32_t q = 0; WRITE && q < nacc; ++q)
+		dst[(j - nacc + q) ^ 3u] = (uint8_t)(acc >> (8 * (nacc - 1u - q)));
+	if (WRITE && hi == end && (lo < end || i == 0))
+	{
+		/* the chunk that reaches the end of the scan: pad to 16 bytes, add one all-zero unit, publish the length */
+		const uint32_t exact = j, padded = (exact + 15u) & ~15u;
+		for (uint32_t q = exact; q < padded + 16u; ++q)
+			dst[q ^ 3u] = 0u;
+		useg_len[sc->seg_first] = padded + (padded - exact);
+	}
+}
+
+/* ------------------------------------------------------------------------------------------------------
+ * Stateless bit reader over the unstuffed slab: the next 32 stream bits at bit position bp are one funnel shift
+ * of the two big-endian words around it; words behind the segment read as zero (what the reference feeds behind a
+ * marker or the end of the file, jpeg.c:176-184, common.c:39).
+ * ------------------------------------------------------------------------------------------------------ */
+struct SsReader
+{
+	const uint32_t *src;
+	uint32_t nwords;
+	uint32_t cur, nxt, nx2; /* stream words bp / 32, + 1, + 2 of the position last primed / advanced to */
+};
+__device__ __forceinline__ uint32_t ssr_word(const SsReader &r, uint32_t wi) { return wi < r.nwords ? __ldg(r.src + wi) : 0u; }
+__device__ __forceinline__ void ssr_prime(SsReader &r, uint32_t bp)
+{
+	const uint32_t wi = bp >> 5;
+	r.cur = ssr_word(r, wi);
+	r.nxt = ssr_word(r, wi + 1u);
+	r.nx2 = ssr_word(r, wi + 2u);
+}
+/* a symbol is < 32 bits: at most one word boundary per step.  The word loaded here is not needed before the NEXT
+   boundary, so its latency stays off the symbol-to-symbol chain. */
+__device__ __forceinline__ void ssr_advance(SsReader &r, uint32_t &bp, uint32_t n)
+{
+	const uint32_t nbp = bp + n;
+	if ((nbp ^ bp) & 32u)
+	{
+		r.cur = r.nxt;
+		r.nxt = r.nx2;
+		r.nx2 = ssr_word(r, (nbp >> 5) + 2u);
+	}
+	bp = nbp;
+}
+
+/* one symbol + magnitude at bp; false = invalid code (16 bits are consumed, as jpeg.c:226-230 does) */
+template <int BITS, bool IS_DC>
+__device__ __forceinline__ bool ss_symbol(SsReader &r, uint32_t &bp, const EntbLutT<BITS> *__restrict__ L, int &value, int &kadv)
+{
+	const uint32_t top = __funnelshift_l(r.nxt, r.cur, bp);
+	uint32_t e = L->fast[top >> (32 - BITS)];
+	if (e == 0)
+	{
+		const uint32_t t16 = top >> 16;
+		int l = BITS + 1;
+		while (t16 >= L->limit[l])
+			++l;
+		if (l > 16)
+		{
+			ssr_advance(r, bp, 16u);
+			kadv = 1;
+			value = 0;
+			return false;
+		}
+		e = entb_entry(L->vals[(L->base[l] + (int)(t16 >> (16 - l))) & 255], l, IS_DC);
+	}
+	const uint32_t len = ENTB_E_LEN(e), size = ENTB_E_SIZE(e);
+	kadv = (int)ENTB_E_KADV(e);
+	const uint32_t after = top << len;
+	const uint32_t s32 = 32u - size;
+	const uint32_t v = shr_clamp(after, s32), mask = shr_clamp(0xffffffffu, s32);
+	const int t = (int)after >> 31;
+	value = (int)v - (int)(mask & ~(uint32_t)t);
+	ssr_advance(r, bp, len + size);
+	return true;
+}
+
 /*
- * Phases 1, 2 and 4.  grid = SsWork items; thread t handles subsequence work.first + t of the CTA's scan.
- * parity selects the ping-pong side holding the CURRENT exit states (refine reads it and writes the other;
- * write reads it).
+ * One symbol of the SKELETON decode (guess and refine only need where symbols and blocks end, not what they say):
+ * DC and AC symbols, and the end of a block, take the same instructions -- the table and the prefix width are
+ * selected, the block bookkeeping is arithmetic -- so the 32 subsequences of a warp, which stand at unrelated places of
+ * their blocks, do not serialise on these cases.  Only a code longer than the table's prefix branches.
+ */
+__device__ __forceinline__ void ss_skeleton_step(const EntbShared &sh, uint32_t sh_addr, SsReader &r, uint32_t &bp, int &k, int &b, uint32_t &nb,
+																 int nblk_mcu)
+{
+	const uint32_t ent = sh.blk[b];
+	const bool dc = k == 0;
+	const uint32_t top = __funnelshift_l(r.nxt, r.cur, bp);
+	const uint32_t tdc = (ent >> 12) & 3u, tac = (ent >> 16) & 3u;
+	const uint32_t tab = dc ? (uint32_t)offsetof(EntbShared, dc) + tdc * (uint32_t)sizeof(EntbDc)
+									: (uint32_t)offsetof(EntbShared, ac) + tac * (uint32_t)sizeof(EntbAc);
+	const uint32_t idx = dc ? top >> (32 - ENTB_DC_BITS) : top >> (32 - ENTB_AC_BITS);
+	uint32_t e = lds_u16(sh_addr + tab + (idx << 1));
+	uint32_t adv;
+	int kadv;
+	if (e == 0u)
+	{
+		const uint32_t t16 = top >> 16;
+		const uint32_t *limit = dc ? sh.dc[tdc].limit : sh.ac[tac].limit;
+		const int32_t *basep = dc ? sh.dc[tdc].base : sh.ac[tac].base;
+		const uint8_t *vals = dc ? sh.dc[tdc].vals : sh.ac[tac].vals;
+		int l = (dc ? ENTB_DC_BITS : ENTB_AC_BITS) + 1;
+		while (t16 >= limit[l])
+			++l;
+		if (l > 16)
+		{
+			adv = 16u; /* invalid code: 16 bits are consumed (jpeg.c:226-230), the block goes on */
+			kadv = 1;
+		}
+		else
+		{
+			e = entb_entry(vals[(basep[l] + (int)(t16 >> (16 - l))) & 255], l, dc);
+			adv = ENTB_E_LEN(e) + ENTB_E_SIZE(e);
+			kadv = (int)ENTB_E_KADV(e);
+		}
+	}
+	else
+	{
+		adv = ENTB_E_LEN(e) + ENTB_E_SIZE(e);
+		kadv = (int)ENTB_E_KADV(e);
+	}
+	ssr_advance(r, bp, adv);
+	k = dc ? 1 : k + kadv;
+	const bool done = k >= 64;
+	k = done ? 0 : k;
+	nb += done ? 1u : 0u;
+	const int b1 = b + 1 == nblk_mcu ? 0 : b + 1;
+	b = done ? b1 : b;
+}
+
+enum
+{
+	SS_GUESS = 0,
+	SS_WRITE = 2
+};
+
+/*
+ * Phases 1 and 4.  grid = SsWork items; thread t handles subsequence work.first + t of the CTA's scan: the unstuffed
+ * bits [2048 i, 2048 (i + 1)).  GUESS starts at the subsequence's first bit assuming "start of an MCU" and records
+ * the exit state at the first symbol start past its end.  WRITE decodes from the converged entry state (the exit
+ * state of the predecessor on side sb.result[0]) and stores coefficients.
  */
 template <int MODE>
 __global__ void __launch_bounds__(SS_THREADS)
 k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans, const jcu_image *__restrict__ images,
 				const uint32_t *__restrict__ seg_start, const jcu_huff_spec *__restrict__ huff,
-				const uint8_t *__restrict__ bitstream, int16_t *__restrict__ coef, int32_t *__restrict__ img_err, SsBuffers sb,
-				int parity)
+				const uint8_t *__restrict__ bitstream, const uint8_t *__restrict__ uslab, const uint32_t *__restrict__ useg_len,
+				int16_t *__restrict__ coef, int32_t *__restrict__ img_err, SsBuffers sb)
 {
 	__shared__ EntbShared sh;
 	const int tid = threadIdx.x;
@@ -197,54 +340,45 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 		return;
 
 	const uint32_t i = w.first + (uint32_t)tid, gi = w.scan_base + i;
-	const uint8_t *__restrict__ base = bitstream + im->data_off;
-	const uint32_t scan_start = seg_start[sc->seg_first], end = sc->data_end;
-	const bool last = i + 1 == w.scan_nsub;
-	const uint32_t limit = last ? end : scan_start + (i + 1) * SS_SUB_BYTES;
-	if (parity < 0)
-		parity = sb.result[0]; /* left there by k_ss_refine_loop */
-	const SsState *cur = parity ? sb.exit_b : sb.exit_a;
-	SsState *nxt = parity ? sb.exit_a : sb.exit_b;
+	const uint32_t scan_start = seg_start[sc->seg_first];
+	const uint32_t ul = useg_len[sc->seg_first];
+	const uint32_t exact = (ul & ~15u) - (ul & 15u); /* bytes of the scan once the stuffing is gone */
+	SsReader rd;
+	rd.src = reinterpret_cast<const uint32_t *>(uslab + entb_useg_off(im->data_off, scan_start, (uint32_t)sc->seg_first));
+	rd.nwords = (ul & ~15u) >> 2;
+	const uint32_t nsub_real = max(1u, (exact + SS_SUB_BYTES - 1u) / SS_SUB_BYTES); /* subsequences that hold data */
+	const bool last = i + 1u == nsub_real;
+	const uint32_t limit = (i + 1u) * (SS_SUB_BYTES * 8u);
 	const int nblk_mcu = sh.nblk;
 
-	SBR br;
-	br.end = end;
+	uint32_t bp = i * (SS_SUB_BYTES * 8u);
 	int b = 0, k = 0;
-	if (MODE == SS_GUESS || i == 0)
+	if (MODE == SS_WRITE && i > 0)
 	{
-		if (MODE == SS_REFINE)
-		{
-			nxt[gi] = cur[gi]; /* subsequence 0 was decoded from the true start state in the guess phase */
-			return;
-		}
-		uint32_t pos = scan_start + i * SS_SUB_BYTES;
-		if (i > 0 && base[pos - 1] == 0xff && base[pos] == 0x00)
-			++pos; /* do not start on the second byte of a stuffed pair */
-		br.pos = pos;
-		br.buf = 0;
-		br.nbits = 0;
-		br.pad = 0;
-	}
-	else
-	{
+		const SsState *cur = sb.result[0] ? sb.exit_b : sb.exit_a;
 		const SsState en = cur[gi - 1];
-		if (MODE == SS_REFINE)
+		bp = en.bp;
+		k = (int)(en.aux & 255u);
+		b = (int)((en.aux >> 8) & 0xfffu);
+	}
+	if (i >= nsub_real)
+	{
+		/* behind the data (the raw scan was longer than the unstuffed one): nothing to decode; pass the state on */
+		if (MODE == SS_GUESS)
 		{
-			if (ss_same(en, sb.entry_used[gi]))
-			{
-				nxt[gi] = cur[gi];
-				return;
-			}
-			sb.entry_used[gi] = en;
+			SsState ex;
+			ex.bp = bp;
+			ex.aux = 0u;
+			sb.exit_a[gi] = ex;
+			sb.nblk[gi] = 0u;
+			SsState none;
+			none.bp = none.aux = 0xffffffffu;
+			sb.entry_used[gi] = none;
 		}
-		br.pos = en.pos;
-		br.buf = en.buf;
-		br.nbits = (int)(en.aux & 255u);
-		k = (int)((en.aux >> 8) & 255u);
-		b = (int)((en.aux >> 16) & 0xfffu);
-		br.pad = (int)(en.aux >> 28) << 3;
+		return;
 	}
 
+	ssr_prime(rd, bp);
 	/* write phase: global block counter and the address of the block in progress */
 	const uint32_t total_blocks = (uint32_t)sc->total_units * (uint32_t)nblk_mcu;
 	const int upr = sc->units_per_row;
@@ -266,52 +400,85 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 
 	uint32_t nb = 0;
 	bool failed = false;
-	for (;;)
+	if (MODE == SS_GUESS)
 	{
-		sbr_topup(base, br);
-		if (MODE == SS_WRITE)
+		const uint32_t sh_addr = (uint32_t)__cvta_generic_to_shared(&sh);
+		while (bp < limit)
+			ss_skeleton_step(sh, sh_addr, rd, bp, k, b, nb, nblk_mcu);
+	}
+	else
+	{
+		/* One instruction path for DC and AC symbols (table, prefix width, target position and multiplier are selected),
+		   so the lanes of a warp -- at unrelated places of their blocks -- only diverge at the end of a block, where the
+		   next block's address is formed from counters that are carried along instead of divided out again. */
+		const uint32_t sh_addr = (uint32_t)__cvta_generic_to_shared(&sh);
+		int ux = 0, uy = 0;
+		if (g < total_blocks)
 		{
-			if (g >= total_blocks || (!last && br.pos >= limit))
-				break;
+			const uint32_t m = g / (uint32_t)nblk_mcu;
+			ux = (int)(m % (uint32_t)upr);
+			uy = (int)(m / (uint32_t)upr);
 		}
-		else if (br.pos >= limit)
-			break;
-		const uint32_t ent = sh.blk[b];
-		int val, kadv;
-		if (k == 0)
+		while (g < total_blocks && (last || bp < limit))
 		{
-			const bool ok = ss_symbol<ENTB_DC_BITS, true>(br, &sh.dc[(ent >> 12) & 3u], val, kadv);
-			if (MODE == SS_WRITE)
+			const uint32_t ent = sh.blk[b];
+			const bool dc = k == 0;
+			const uint32_t top = __funnelshift_l(rd.nxt, rd.cur, bp);
+			const uint32_t tdc = (ent >> 12) & 3u, tac = (ent >> 16) & 3u;
+			const uint32_t tab = dc ? (uint32_t)offsetof(EntbShared, dc) + tdc * (uint32_t)sizeof(EntbDc)
+											: (uint32_t)offsetof(EntbShared, ac) + tac * (uint32_t)sizeof(EntbAc);
+			const uint32_t idx = dc ? top >> (32 - ENTB_DC_BITS) : top >> (32 - ENTB_AC_BITS);
+			uint32_t e = lds_u16(sh_addr + tab + (idx << 1));
+			bool ok = true;
+			if (e == 0u)
 			{
-				failed |= !ok;
-				blk[coef_pos(0, key)] = (int16_t)val; /* DC difference; phase 5 turns it into (short)(dc * q) */
+				const uint32_t t16 = top >> 16;
+				const uint32_t *lim = dc ? sh.dc[tdc].limit : sh.ac[tac].limit;
+				const int32_t *basep = dc ? sh.dc[tdc].base : sh.ac[tac].base;
+				const uint8_t *vals = dc ? sh.dc[tdc].vals : sh.ac[tac].vals;
+				int l = (dc ? ENTB_DC_BITS : ENTB_AC_BITS) + 1;
+				while (t16 >= lim[l])
+					++l;
+				ok = l <= 16;
+				/* invalid code: 16 bits are consumed (jpeg.c:226-230) and the block goes on by one position */
+				e = ok ? entb_entry(vals[(basep[l] + (int)(t16 >> (16 - l))) & 255], l, dc) : (1u | (16u << 11));
 			}
-			k = 1;
-		}
-		else
-		{
-			const bool ok = ss_symbol<ENTB_AC_BITS, false>(br, &sh.ac[(ent >> 16) & 3u], val, kadv);
-			if (!ok)
-				kadv = 1;
-			const uint32_t e = sh.zq[ent & 15u][(k + kadv - 1) & 127];
-			k += kadv;
-			if (MODE == SS_WRITE)
+			const uint32_t len = ENTB_E_LEN(e), size = ENTB_E_SIZE(e);
+			const int kadv = (int)ENTB_E_KADV(e);
+			const uint32_t after = top << len;
+			const uint32_t s32 = 32u - size;
+			const uint32_t v = shr_clamp(after, s32), mask = shr_clamp(0xffffffffu, s32);
+			const int t = (int)after >> 31;
+			const int val = (int)v - (int)(mask & ~(uint32_t)t);
+			ssr_advance(rd, bp, len + size);
+			failed |= !ok;
+			/* DC: the raw difference at position 0 (phase 5 turns it into (short)(dc * q)); AC: (short)(value * q) */
+			const uint32_t zqe = sh.zq[ent & 15u][dc ? 0 : ((k + kadv - 1) & 127)];
+			const int mul = dc ? 1 : (int)(zqe >> 16);
+			if (ok && (dc || val))
+				blk[coef_pos(dc ? 0 : (int)ENTB_ZQ_NAT(zqe), key)] = (int16_t)(val * mul);
+			k = dc ? 1 : k + kadv;
+			if (k >= 64)
 			{
-				failed |= !ok;
-				if (ok && val)
-					blk[coef_pos((int)ENTB_ZQ_NAT(e), key)] = (int16_t)(val * (int)(e >> 16));
-			}
-		}
-		if (k >= 64)
-		{
-			k = 0;
-			++nb;
-			b = (b + 1 == nblk_mcu) ? 0 : b + 1;
-			if (MODE == SS_WRITE)
-			{
+				k = 0;
 				++g;
+				if (++b == nblk_mcu)
+				{
+					b = 0;
+					if (++ux == upr)
+					{
+						ux = 0;
+						++uy;
+					}
+				}
 				if (g < total_blocks)
-					locate(g);
+				{
+					const uint32_t en = sh.blk[b];
+					const int sl = (int)(en & 15u);
+					const int bx = ux * sh.hn[sl] + (int)((en >> 4) & 15u), by = uy * sh.vn[sl] + (int)((en >> 8) & 15u);
+					blk = coef + sh.coff[sl] + ((size_t)by * sh.bw[sl] + bx) * 64;
+					key = coef_key(blk);
+				}
 			}
 		}
 	}
@@ -321,127 +488,109 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 			report_failure(img_err, sc, 0u, JCU_ERR_BAD_HUFFMAN);
 		else if (g_entry < total_blocks && g >= total_blocks)
 		{
-			/* this thread finished the scan's last block: the left-over rule of jpeg_entropy.cuh (one segment, the last) */
-			BitReader t;
-			t.p = base + br.pos;
-			t.end = base + end;
-			t.buf = br.buf;
-			t.nbits = br.nbits;
-			t.stopped = br.pos >= end;
-			t.pad = min(br.pad, br.nbits);
-			/* a stuffed 0xFF more than 32 bits behind the end position is certainly unread; one inside the window needs
-			   the exact fill level of the reference's bit buffer: replay its reader over the scan (rare, damaged files) */
-			const int d_ff = br_first_ff_ahead(t);
-			if (d_ff >= 32 || (d_ff >= 0 && entb_replay_trips(sh, base, im->data_len, scan_start, sc->total_units, false, end)))
-				report_failure(img_err, sc, 0u, JCU_ERR_UNKNOWN_MARKER);
+			/* this thread finished the scan's last block: the left-over rule of jpeg_entropy.cuh for a scan that simply runs
+			   out of units, on the unstuffed copy as in k_entropy_baseline.  A stuffed 0xFF (a data byte 0xFF) wholly behind
+			   the end position and beyond anything the reference can have buffered trips its marker loop; one inside the
+			   32-bit window needs the exact fill level of its bit buffer: replay its reader over the scan (damaged files) */
+			const int pos = (int)bp, R = 8 * (int)exact - pos;
+			if (R >= 9)
+			{
+				const uint8_t *ub = reinterpret_cast<const uint8_t *>(rd.src);
+				int f = -1;
+				for (int q = (pos + 7) >> 3; q < (int)exact && f < 0; ++q)
+					if (ub[q ^ 3] == 0xffu)
+						f = q;
+				if (f >= 0 && (8 * f >= pos + 32 ||
+									entb_replay_trips(sh, bitstream + im->data_off, im->data_len, scan_start, sc->total_units, false, sc->data_end)))
+					report_failure(img_err, sc, 0u, JCU_ERR_UNKNOWN_MARKER);
+			}
 		}
 		return;
 	}
 	SsState ex;
-	ex.pos = br.pos;
-	ex.aux = (uint32_t)br.nbits | ((uint32_t)k << 8) | ((uint32_t)b << 16) | ((uint32_t)(min(br.pad, br.nbits) >> 3) << 28);
-	ex.buf = br.buf;
+	ex.bp = bp;
+	ex.aux = (uint32_t)k | ((uint32_t)b << 8);
 	sb.nblk[gi] = nb;
-	if (MODE == SS_GUESS)
-	{
-		sb.exit_a[gi] = ex;
-		SsState none;
-		none.pos = 0xffffffffu;
-		none.aux = 0xffffffffu;
-		none.buf = 0;
-		sb.entry_used[gi] = none;
-	}
-	else
-	{
-		if (!ss_same(ex, cur[gi]))
-			atomicOr(sb.changed, 1);
-		nxt[gi] = ex;
-	}
+	sb.exit_a[gi] = ex;
+	SsState none;
+	none.bp = none.aux = 0xffffffffu;
+	sb.entry_used[gi] = none;
 }
 
 /*
- * Phase 2, several Jacobi iterations per launch.  Same work split as k_ss_decode.  Iteration 0 takes every
- * entry state from the previous round (global memory); the following iterations pass exit states from thread
- * t-1 to thread t of the same CTA through shared memory, so a correction travels up to SS_INNER subsequences
- * per launch instead of one, and the many cheap tail rounds (a launch and a host round trip each) disappear.
- * A thread whose entry state did not change does not decode again.
+ * Phase 2: Jacobi rounds.  One work item = SS_INNER iterations inside a CTA: iteration 0 takes every entry state from
+ * the previous round (global memory), the following ones pass exit states from thread t-1 to thread t through shared
+ * memory, so a correction travels up to SS_INNER subsequences per round.  A thread whose entry state did not
+ * change does not decode again.
  */
-#define SS_INNER 8
-__device__ __forceinline__ void ss_refine_item(EntbShared &sh, SsState *s_exit, const SsWork w, const jcu_scan *__restrict__ scans,
+#ifndef SS_INNER
+#define SS_INNER 16 /* measured on 256 x 1080p 4:4:4: 8 -> 6 rounds 12.06 ms, 16 -> 4 rounds 11.92 ms, 32 -> 3 rounds 11.88 ms */
+#endif
+__device__ __forceinline__ bool ss_refine_item(EntbShared &sh, SsState *s_exit, const SsWork w, const jcu_scan *__restrict__ scans,
 															  const jcu_image *__restrict__ images, const uint32_t *__restrict__ seg_start,
-															  const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ bitstream, const SsBuffers &sb,
-															  int parity, int32_t *changed_flag)
+															  const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ uslab,
+															  const uint32_t *__restrict__ useg_len, const SsBuffers &sb, int parity, int32_t *changed_flag,
+															  bool rebuild)
 {
 	const int tid = threadIdx.x;
 	const jcu_scan *sc = &scans[w.scan];
 	const jcu_image *im = &images[sc->image];
-	entb_setup(sh, sc, im, huff, tid, SS_THREADS);
-	const bool valid = (uint32_t)tid < w.count;
+	const uint32_t sh_addr = (uint32_t)__cvta_generic_to_shared(&sh);
 	const uint32_t i = w.first + (uint32_t)tid, gi = w.scan_base + i;
-	const uint8_t *__restrict__ base = bitstream + im->data_off;
-	const uint32_t scan_start = seg_start[sc->seg_first], end = sc->data_end;
-	const bool last = i + 1 == w.scan_nsub;
-	const uint32_t limit = last ? end : scan_start + (i + 1) * SS_SUB_BYTES;
+	const uint32_t ul = useg_len[sc->seg_first];
+	const uint32_t exact = (ul & ~15u) - (ul & 15u);
+	SsReader rd;
+	rd.src = reinterpret_cast<const uint32_t *>(uslab + entb_useg_off(im->data_off, seg_start[sc->seg_first], (uint32_t)sc->seg_first));
+	rd.nwords = (ul & ~15u) >> 2;
+	const uint32_t nsub_real = max(1u, (exact + SS_SUB_BYTES - 1u) / SS_SUB_BYTES);
+	const bool valid = (uint32_t)tid < w.count;
+	const bool live = valid && i < nsub_real; /* subsequences behind the data only pass their entry state on */
+	const uint32_t limit = (i + 1u) * (SS_SUB_BYTES * 8u);
 	const SsState *cur = parity ? sb.exit_b : sb.exit_a;
 	SsState *nxt = parity ? sb.exit_a : sb.exit_b;
-	const int nblk_mcu = sh.nblk;
 
-	SsState mine, used;
-	mine.pos = mine.aux = 0;
-	mine.buf = 0;
-	used = mine;
+	SsState mine, used, en0;
+	mine.bp = mine.aux = 0;
+	used = en0 = mine;
 	if (valid)
 	{
 		mine = ss_load_l2(&cur[gi]);
 		used = ss_load_l2(&sb.entry_used[gi]);
+		en0 = i > 0 ? ss_load_l2(&cur[gi - 1]) : used;
 	}
+	/* after the first rounds most work items have nothing to do: find that out BEFORE the scan's tables are built */
+	if (!__syncthreads_or(valid && !ss_same(en0, used)))
+	{
+		if (valid)
+			nxt[gi] = mine;
+		return false;
+	}
+	if (rebuild) /* consecutive work items of a CTA often belong to one scan: its tables are built once */
+		entb_setup(sh, sc, im, huff, tid, SS_THREADS);
+	const int nblk_mcu = sh.nblk;
 	const SsState first = mine;
 	for (int it = 0; it < SS_INNER; ++it)
 	{
 		bool changed = false;
 		if (valid && i > 0 && (it == 0 || tid > 0))
 		{
-			const SsState en = it == 0 ? ss_load_l2(&cur[gi - 1]) : s_exit[tid - 1];
+			const SsState en = it == 0 ? en0 : s_exit[tid - 1];
 			if (!ss_same(en, used))
 			{
 				used = en;
-				SBR br;
-				br.end = end;
-				br.pos = en.pos;
-				br.buf = en.buf;
-				br.nbits = (int)(en.aux & 255u);
-				br.pad = (int)(en.aux >> 28) << 3;
-				int k = (int)((en.aux >> 8) & 255u), b = (int)((en.aux >> 16) & 0xfffu);
-				uint32_t nb = 0;
-				for (;;)
+				SsState ex = en;
+				if (live)
 				{
-					sbr_topup(base, br);
-					if (br.pos >= limit)
-						break;
-					const uint32_t ent = sh.blk[b];
-					int val, kadv;
-					if (k == 0)
-					{
-						ss_symbol<ENTB_DC_BITS, true>(br, &sh.dc[(ent >> 12) & 3u], val, kadv);
-						k = 1;
-					}
-					else
-					{
-						const bool ok = ss_symbol<ENTB_AC_BITS, false>(br, &sh.ac[(ent >> 16) & 3u], val, kadv);
-						k += ok ? kadv : 1;
-					}
-					if (k >= 64)
-					{
-						k = 0;
-						++nb;
-						b = (b + 1 == nblk_mcu) ? 0 : b + 1;
-					}
+					uint32_t bp = en.bp;
+					int k = (int)(en.aux & 255u), b = (int)((en.aux >> 8) & 0xfffu);
+					uint32_t nb = 0;
+					ssr_prime(rd, bp);
+					while (bp < limit)
+						ss_skeleton_step(sh, sh_addr, rd, bp, k, b, nb, nblk_mcu);
+					ex.bp = bp;
+					ex.aux = (uint32_t)k | ((uint32_t)b << 8);
+					sb.nblk[gi] = nb;
 				}
-				SsState ex;
-				ex.pos = br.pos;
-				ex.aux = (uint32_t)br.nbits | ((uint32_t)k << 8) | ((uint32_t)b << 16) | ((uint32_t)(min(br.pad, br.nbits) >> 3) << 28);
-				ex.buf = br.buf;
-				sb.nblk[gi] = nb;
 				changed = !ss_same(ex, mine);
 				mine = ex;
 			}
@@ -458,7 +607,8 @@ __device__ __forceinline__ void ss_refine_item(EntbShared &sh, SsState *s_exit, 
 		if (!ss_same(mine, first))
 			atomicOr(changed_flag, 1);
 	}
-	__syncthreads(); /* the next work item of this CTA rebuilds the tables and reuses s_exit */
+	__syncthreads(); /* the next work item of this CTA may rebuild the tables and reuses s_exit */
+	return true; /* the tables in shared memory are this scan's */
 }
 
 /* barrier over all CTAs of a cooperative launch (they are co-resident): arrivals counter + generation */
@@ -486,25 +636,30 @@ __device__ __forceinline__ void ss_grid_barrier(uint32_t *sync, unsigned nctas)
 
 /*
  * Phase 2 WITHOUT the host: one cooperative launch runs the Jacobi rounds to convergence.  Every round the CTAs share
- * out the work items (each item = SS_INNER in-CTA iterations as above), meet at a grid barrier and read the round's
- * "anything changed" flag; the side of the ping-pong that holds the final exit states goes to sb.result[0] for the
- * write pass.  The reference has no counterpart (its decoder is serial, jpeg.c:1198-1232); what this replaces is
- * one kernel launch + one device-to-host flag copy + one stream synchronisation per round.
+ * out the work items, meet at a grid barrier and read the round's "anything changed" flag; the side of the ping-pong
+ * that holds the final exit states goes to sb.result[0] for the write pass.  The reference has no counterpart (its
+ * decoder is serial, jpeg.c:1198-1232); what this replaces is one kernel launch + one device-to-host flag copy + one
+ * stream synchronisation per round.
  */
 __global__ void __launch_bounds__(SS_THREADS)
 k_ss_refine_loop(const SsWork *__restrict__ work, unsigned nwork, const jcu_scan *__restrict__ scans, const jcu_image *__restrict__ images,
-					  const uint32_t *__restrict__ seg_start, const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ bitstream,
-					  SsBuffers sb, unsigned max_rounds)
+					  const uint32_t *__restrict__ seg_start, const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ uslab,
+					  const uint32_t *__restrict__ useg_len, SsBuffers sb, unsigned max_rounds)
 {
 	__shared__ EntbShared sh;
 	__shared__ SsState s_exit[SS_THREADS];
-	int parity = 0;
+	int parity = 0, have_scan = -1;
 	unsigned round = 0;
 	for (; round < max_rounds; ++round)
 	{
 		int32_t *flag = sb.changed + round % 3u;
+		/* work items are dealt out round-robin (neighbouring items, i.e. one image, spread over the SMs) */
 		for (unsigned it = blockIdx.x; it < nwork; it += gridDim.x)
-			ss_refine_item(sh, s_exit, work[it], scans, images, seg_start, huff, bitstream, sb, parity, flag);
+		{
+			const SsWork w = work[it];
+			if (ss_refine_item(sh, s_exit, w, scans, images, seg_start, huff, uslab, useg_len, sb, parity, flag, w.scan != have_scan))
+				have_scan = w.scan;
+		}
 		parity ^= 1;
 		ss_grid_barrier(sb.sync, gridDim.x);
 		const int32_t any = *reinterpret_cast<volatile int32_t *>(flag);
@@ -582,16 +737,45 @@ k_ss_dc(const SsScan *__restrict__ ss, const jcu_scan *__restrict__ scans, const
 	const int tid = threadIdx.x;
 	const uint32_t chunk = (n + SS_DC_THREADS - 1u) / SS_DC_THREADS;
 	const uint32_t lo = min(n, (uint32_t)tid * chunk), hi = min(n, lo + chunk);
-	auto dc_of = [&](uint32_t j) -> int16_t * {
-		const uint32_t m = j / (uint32_t)per, r = j - m * (uint32_t)per;
-		const int y = (int)r / hn, x = (int)r - y * hn;
-		const int ux = (int)(m % (uint32_t)upr), uy = (int)(m / (uint32_t)upr);
-		int16_t *blk = plane + ((size_t)(uy * vn + y) * bw + (ux * hn + x)) * 64;
+	/* walk the blocks of the component in decode order without a division per block: (unit column, unit row, block in unit) */
+	struct Walk
+	{
+		int ux, uy, r;
+	};
+	auto start = [&](uint32_t j) {
+		Walk wk;
+		const uint32_t m = j / (uint32_t)per;
+		wk.r = (int)(j - m * (uint32_t)per);
+		wk.ux = (int)(m % (uint32_t)upr);
+		wk.uy = (int)(m / (uint32_t)upr);
+		return wk;
+	};
+	auto addr = [&](const Walk &wk) -> int16_t * {
+		const int y = wk.r / hn, x = wk.r - y * hn;
+		int16_t *blk = plane + ((size_t)(wk.uy * vn + y) * bw + (wk.ux * hn + x)) * 64;
 		return blk + coef_pos(0, coef_key(blk));
 	};
+	auto step = [&](Walk &wk) {
+		if (++wk.r == per)
+		{
+			wk.r = 0;
+			if (++wk.ux == upr)
+			{
+				wk.ux = 0;
+				++wk.uy;
+			}
+		}
+	};
 	int sum = 0;
-	for (uint32_t j = lo; j < hi; ++j)
-		sum += (int)*dc_of(j);
+	{
+		Walk wk = start(lo);
+#pragma unroll 8
+		for (uint32_t j = lo; j < hi; ++j)
+		{
+			sum += (int)*addr(wk);
+			step(wk);
+		}
+	}
 	s_part[tid] = sum;
 	__syncthreads();
 	if (tid == 0)
@@ -606,10 +790,28 @@ k_ss_dc(const SsScan *__restrict__ ss, const jcu_scan *__restrict__ scans, const
 	}
 	__syncthreads();
 	int pred = s_part[tid];
-	for (uint32_t j = lo; j < hi; ++j)
 	{
-		int16_t *p = dc_of(j);
-		pred += (int)*p;
-		*p = (int16_t)(pred * q0);
+		/* eight blocks at a time: all loads first (nothing else writes these words), then the running sum and the stores --
+		   otherwise every load waits for the store before it, which the compiler must assume to alias */
+		Walk wk = start(lo);
+		for (uint32_t j = lo; j < hi; j += 8u)
+		{
+			int16_t *p[8];
+			int d[8];
+#pragma unroll
+			for (int q = 0; q < 8; ++q)
+			{
+				p[q] = addr(wk);
+				d[q] = j + (uint32_t)q < hi ? (int)*p[q] : 0;
+				step(wk);
+			}
+#pragma unroll
+			for (int q = 0; q < 8; ++q)
+				if (j + (uint32_t)q < hi)
+				{
+					pred += d[q];
+					*p[q] = (int16_t)(pred * q0);
+				}
+		}
 	}
 }

@@ -193,13 +193,13 @@ JCU_API int jcu_widen(jcu_ctx *c, size_t off, size_t count, int elem_bytes, int 
 JCU_API int jcu_download_wide(jcu_ctx *c, size_t bytes, void *dst); /* async D2H of the wide buffer; jcu_sync waits */
 JCU_API void *jcu_device_wide(jcu_ctx *c);
 
-/* stage-level entry points for the parity tests (host pointers in, host pointers out) */
+/* stage-level entry point: the IDCT stage alone (host pointers in, host pointers out).  The colour-conversion test hook
+   lives in the separate test library (csrc/test_hooks.cu -> libimage_codecs_b200_testhooks.so), not in the product. */
 JCU_API int jcu_test_idct_blocks(jcu_ctx *c, const int16_t *coef, const uint16_t *qt, int nblocks, uint8_t *out64);
 /* test hook: a context created with jcu_ctx_options.guard carries a 4 KB canary behind the logical size of every
    device buffer; returns 1 if all canaries are intact, 0 if one was overwritten (jcu_error_string says which),
    -1 if guard mode is off */
 JCU_API int jcu_debug_guards_ok(jcu_ctx *c);
-JCU_API int jcu_test_ycbcr(jcu_ctx *c, const uint8_t *y, const uint8_t *cb, const uint8_t *cr, int n, int step, uint8_t *out);
 JCU_API int jcu_read_coefs(jcu_ctx *c, size_t elem_off, size_t elems, int16_t *dst); /* coefficient slab after run */
 
 /* Allocation-free variant of jcu_test_idct_blocks.  It has NO counterpart in the reference: it was added at the

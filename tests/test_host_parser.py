@@ -103,7 +103,8 @@ def test_geometry_and_path_selection():
     assert (y["decode_n"], y["n_out"], y["comps_in_file"]) == (1, 1, 3)
     p = ic.inspect(S.stream("420_prog", 64, 48, 0), 3)
     assert p["progressive"] == 1 and p["n_scans"] > 1
-    assert ic.inspect(S.stream("422", 64, 48, 0), 3)["path"] == 0  # generic two-pass path
+    assert ic.inspect(S.stream("422", 64, 48, 0), 3)["path"] == 4  # fused 4:2:2 strip kernel
+    assert ic.inspect(S.stream("440", 64, 48, 0), 3)["path"] == 0  # generic two-pass path
     c = ic.inspect(S.stream("cmyk", 17, 9, 0), 0)
     assert (c["comps_in_file"], c["n_out"], c["color_mode"]) == (3, 3, 3)
 

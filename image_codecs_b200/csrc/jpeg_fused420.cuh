@@ -141,17 +141,10 @@ __device__ __forceinline__ void s420_load_block(const uint4 *__restrict__ slot, 
 #ifndef S420_ROW_MODE
 #define S420_ROW_MODE 0
 #endif
-#ifndef S420_SPLIT
-#define S420_SPLIT 0 /* 1 = the column pass writes a second register array instead of updating v[] in place */
-#endif
 __device__ __forceinline__ void s420_idct(int (&v)[64], uint32_t (&rows)[16])
 {
 	int o[8];
-#if S420_SPLIT
-	int u[64];
-#else
-	int(&u)[64] = v;
-#endif
+	int(&u)[64] = v; /* a second register array for the column pass's results compiles to the same code */
 #pragma unroll
 	for (int c = 0; c < 8; ++c)
 	{
@@ -169,45 +162,6 @@ __device__ __forceinline__ void s420_idct(int (&v)[64], uint32_t (&rows)[16])
 		rows[2 * r + 1] = s420_pack4(o[4] >> 17, o[5] >> 17, o[6] >> 17, o[7] >> 17);
 	}
 }
-
-#ifdef S420_STREAM_TEST
-/* EXPERIMENT (layout not yet matched): chunk 2j+h holds rows 4h..4h+3 of columns 2j, 2j+1 */
-template <bool DEQ>
-__device__ __forceinline__ void s420_idct_stream(const uint4 *__restrict__ slot, unsigned key, const uint16_t *__restrict__ q, uint32_t (&rows)[16])
-{
-	int u[64];
-	int o[8];
-#pragma unroll
-	for (int j = 0; j < 4; ++j)
-	{
-		const uint4 a = slot[(2 * j) ^ key], b = slot[(2 * j + 1) ^ key];
-		const uint32_t ws[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-		int lo[8], hi[8];
-#pragma unroll
-		for (int r = 0; r < 8; ++r)
-		{
-			lo[r] = (int)(int16_t)(ws[r] & 0xffffu);
-			hi[r] = ((int)ws[r]) >> 16;
-		}
-		idct_1d<S420_FMA_COL, S420_COL_MODE>(lo[0], lo[1], lo[2], lo[3], lo[4], lo[5], lo[6], lo[7], 512, o);
-#pragma unroll
-		for (int r = 0; r < 8; ++r)
-			u[2 * j + 8 * r] = o[r] >> 10;
-		idct_1d<S420_FMA_COL, S420_COL_MODE>(hi[0], hi[1], hi[2], hi[3], hi[4], hi[5], hi[6], hi[7], 512, o);
-#pragma unroll
-		for (int r = 0; r < 8; ++r)
-			u[2 * j + 1 + 8 * r] = o[r] >> 10;
-	}
-#pragma unroll
-	for (int r = 0; r < 8; ++r)
-	{
-		idct_1d<S420_FMA_ROW, S420_ROW_MODE>(u[8 * r], u[8 * r + 1], u[8 * r + 2], u[8 * r + 3], u[8 * r + 4], u[8 * r + 5], u[8 * r + 6], u[8 * r + 7],
-				  65536 + (128 << 17), o);
-		rows[2 * r] = s420_pack4(o[0] >> 17, o[1] >> 17, o[2] >> 17, o[3] >> 17);
-		rows[2 * r + 1] = s420_pack4(o[4] >> 17, o[5] >> 17, o[6] >> 17, o[7] >> 17);
-	}
-}
-#endif
 
 /* four chroma samples (bytes of cbw / crw) -> four ring words 16*Cb+8 | (16*(Cr-128)+8) << 16.
    Two byte permutes interleave the even / odd samples of both planes, one more per sample spreads a (Cb, Cr) pair
@@ -279,7 +233,8 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 	uint32_t *sP = reinterpret_cast<uint32_t *>(s420_smem + S420_OFF_P);	  /* [2][S420_CW], directly behind sC */
 	uint16_t(*sQ)[64] = reinterpret_cast<uint16_t(*)[64]>(s420_smem + S420_OFF_Q);
 	uint64_t *bar = reinterpret_cast<uint64_t *>(s420_smem + S420_OFF_BAR(DEQ));
-	__shared__ int2 sRow[2][16]; /* per pixel row of MCU row r (buffer r & 1): word offsets (from sC) of its near / far chroma rows */
+	__shared__ int4 sRow[2][16]; /* per pixel row of MCU row r (buffer r & 1): word offsets (from sC) of its near / far chroma
+											 rows, byte offset of its luma row in sY, byte offset of its output row from the image's first */
 
 	const jcu_image *im = &images[list[blockIdx.y]];
 	const int strips = im->tiles_x;
@@ -377,7 +332,7 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 				fr = (k + 1 > cy - 1) ? nr : (lk < 7 ? nr + S420_CW : (sl_next * 8) * S420_CW);
 			else
 				fr = (lk > 0) ? nr - S420_CW : (r == 0 ? nr : (24 + (r & 1)) * S420_CW); /* line buffer sP follows sC */
-			sRow[r & 1][ly] = make_int2(nr, (r * 16 + ly < H) ? fr : -1);
+			sRow[r & 1][ly] = make_int4(nr + 8, (r * 16 + ly < H) ? fr + 8 : -1, ((r & 1) * 16 + ly) * S420_YW, (r * 16 + ly) * pitch);
 		}
 		/* ---- IDCT phase: luma of MCU row r, chroma of MCU row r+1 ---- */
 		{
@@ -395,12 +350,8 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 			{
 				const int16_t *g = isY ? baseY + ((size_t)(2 * r + yrow) * ybw + 2 * m0 + lbx) * 64
 											  : (ci ? baseCr : baseCb) + ((size_t)(r + 1) * cbw + cbx) * 64;
-#ifdef S420_STREAM_TEST
-				s420_idct_stream<DEQ>(&sCoef[slot_safe * 8], coef_key(g), sQ[isY ? 0 : 1 + ci], rows);
-#else
 				s420_load_block<DEQ>(&sCoef[slot_safe * 8], coef_key(g), sQ[isY ? 0 : 1 + ci], v);
 				s420_idct(v, rows);
-#endif
 			}
 			if (isY && doY)
 			{
@@ -459,16 +410,19 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 		if (doY)
 #endif
 		{
-			uint8_t *orow0 = obase + (long long)(r * 16) * pitch + m0 * 16 * N;
+			/* everything that depends on the row alone comes out of the row table with one 16-byte load; the column
+			   terms are three multiples of g */
+			uint8_t *ostrip = obase + m0 * 16 * N;
+			const int4 *rowtab = sRow[r & 1];
 			int ly = ly_first, g = g_first;
 #pragma unroll 1
 			while (ly < 16)
 			{
-				const int2 rw = sRow[r & 1][ly]; /* word offsets of the near / far chroma rows; far < 0: row beyond the image */
+				const int4 rw = rowtab[ly]; /* x, y: word offsets of the near / far chroma rows (+ 8: first column of the strip); y < 0: row beyond the image */
 				const int gx0 = m0 * 16 + g * 8;
 				if (rw.y >= 0 && (full_w || gx0 < W))
 				{
-					const uint32_t *np = sC + rw.x + 8 + g * 4, *fp = sC + rw.y + 8 + g * 4;
+					const uint32_t *np = sC + rw.x + g * 4, *fp = sC + rw.y + g * 4;
 					uint32_t t[6];
 					{
 						const uint4 n4 = *reinterpret_cast<const uint4 *>(np), f4 = *reinterpret_cast<const uint4 *>(fp);
@@ -479,7 +433,7 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 						t[4] = 3u * n4.w + f4.w;
 						t[5] = 3u * np[4] + fp[4];
 					}
-					const uint2 yv = *reinterpret_cast<const uint2 *>(sY + ((r & 1) * 16 + ly) * S420_YW + g * 8);
+					const uint2 yv = *reinterpret_cast<const uint2 *>(sY + rw.z + g * 8);
 					int R[8], Gc[8], B[8];
 					/* (3*t[i] + t[i-1 or i+1] + 8) >> 4 (jpeg.c:1832-1833) on both chroma fields at once */
 					s420_colour<0>(3u * t[1] + t[0], yv.x, R[0], Gc[0], B[0]);
@@ -490,7 +444,7 @@ k_fused420_strip(const int32_t *__restrict__ list, const jcu_image *__restrict__
 					s420_colour<1>(3u * t[3] + t[4], yv.y, R[5], Gc[5], B[5]);
 					s420_colour<2>(3u * t[4] + t[3], yv.y, R[6], Gc[6], B[6]);
 					s420_colour<3>(3u * t[4] + t[5], yv.y, R[7], Gc[7], B[7]);
-					uint8_t *o = orow0 + (ly * pitch + g * 8 * N);
+					uint8_t *o = ostrip + (rw.w + g * 8 * N);
 					if (full_w || (vec_ok && gx0 + 8 <= W))
 					{
 						if (N == 3)

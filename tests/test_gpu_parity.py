@@ -237,6 +237,34 @@ def test_restartless_streams_serial_and_selfsync(oracle, entropy_mode):
     d.close()
 
 
+def test_later_scan_of_a_component_wins(oracle):
+    """T.81 allows a component to appear in several scans of a baseline file; the reference decodes them
+    in file order, so the later one wins (jpeg.c:1716).  Two restart-less Cb scans long enough for the
+    self-synchronising path, in both orders: a scan that shares a component with another scan of its image must keep
+    its place in the wave order (it stays on the serial path), whatever the entropy mode."""
+    from tools import testenc as te
+
+    def split(data):
+        idx = [i for i in range(2, len(data) - 1) if data[i] == 0xFF and data[i + 1] == 0xDA]
+        eoi = data.rindex(b"\xff\xd9")
+        parts = [data[idx[k]:(idx[k + 1] if k + 1 < len(idx) else eoi)] for k in range(len(idx))]
+        return data[:idx[0]], parts, data[eoi:]
+
+    a = te.encode(te.synth_rgb(640, 360, 0, 11), quality=90, subsampling="420", noninterleaved=True)
+    b = te.encode(te.synth_rgb(640, 360, 2, 12), quality=90, subsampling="420", noninterleaved=True)
+    (ha, pa, ea), (_, pb, _) = split(a), split(b)
+    assert len(pa) == 3 and len(pb) == 3 and len(pb[1]) > 4096
+    later_wins = ha + pa[0] + pa[1] + pa[2] + pb[1] + ea   # Cb of image b overwrites Cb of image a
+    earlier_loses = ha + pb[1] + pa[0] + pa[1] + pa[2] + ea  # ... and here it is overwritten: equals image a
+    for mode in (0, 1, 2):
+        d = ic.BatchDecoder(device=0, entropy_mode=mode)
+        outs = d.decode([later_wins, earlier_loses, a], 3)
+        _check(oracle, outs[0], later_wins, 3, f"mode{mode} later Cb scan wins")
+        _check(oracle, outs[1], earlier_loses, 3, f"mode{mode} earlier Cb scan is overwritten")
+        assert np.array_equal(outs[1], outs[2]) and not np.array_equal(outs[0], outs[2])
+        d.close()
+
+
 def test_selfsync_full_size_444_and_gray(oracle, decoder):
     """BASELINE.json configs[2]: 1080p 4:4:4 colour and 8-bit grayscale without restart markers (auto mode picks
     the self-synchronising path for scans this long), plus 4:2:0 and a dense-noise image."""

@@ -60,8 +60,9 @@ struct jcu_ctx
 	uint32_t ss_nsub_total = 0, ss_max_nsub = 0;
 	int ss_rounds = 0; /* refine rounds the last run needed (read back with the per-image errors) */
 	int ss_coop_ctas = 0; /* CTAs of k_ss_refine_loop that are resident at once on this device */
+	int pc_resident = 1024; /* CTAs of k_prog_coop that are resident at once */
 	/* batch metadata kept on the host */
-	int n_images = 0, n_waves = 0;
+	int n_images = 0, n_waves = 0, n_scans = 0;
 	size_t coef_elems = 0, out_bytes = 0;
 	bool need_clear = false;
 	std::vector<EntWork> work_h;
@@ -70,6 +71,10 @@ struct jcu_ctx
 	std::vector<char> wave_two;	  /* per wave: every baseline scan uses <= 2 distinct DC and <= 2 distinct AC tables */
 	std::vector<int> wave_ncoop;	  /* per wave: trailing work items that are single-segment progressive AC scans (jpeg_entropy_prog.cuh) */
 	std::vector<int> wave_nsmall;	  /* per wave: work items after the baseline ones that are progressive scans of <= 32 segments */
+	std::vector<EntWork> pipe_work_h; /* progressive scans without restart markers of images whose scans ALL take the warp decoder:
+													  one pipelined launch for the whole dependency chain (jpeg_entropy_prog.cuh, PcPipe) */
+	std::vector<int32_t> pipe_preds_h; /* per scan: PC_MAX_PREDS predecessor scans, -1 = none */
+	DevBuf pipe_work, pipe_preds, pipe_progress;
 	std::vector<int32_t> list_h; /* image lists per path, concatenated */
 	int list_off[JCU_PATH_COUNT] = {0, 0, 0, 0, 0}, list_n[JCU_PATH_COUNT] = {0, 0, 0, 0, 0};
 	int tiles[JCU_PATH_COUNT] = {0, 0, 0, 0, 0};
@@ -198,6 +203,9 @@ extern "C" int jcu_ctx_create_opts(const jcu_ctx_options *o, jcu_ctx **out)
 		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ss_refine_loop, SS_THREADS, 0);
 		cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
 		c->ss_coop_ctas = std::max(1, per_sm * sms);
+		per_sm = 0;
+		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_prog_coop, PC_THREADS, 0);
+		c->pc_resident = std::max(64, per_sm * sms);
 	}
 	*out = c;
 	return 0;
@@ -211,7 +219,7 @@ extern "C" void jcu_ctx_destroy(jcu_ctx *c)
 	cudaStreamSynchronize(c->stream);
 	DevBuf *bufs[] = {&c->bits, &c->images, &c->scans, &c->segs, &c->huff, &c->work, &c->coef, &c->planes, &c->out, &c->err, &c->lists,
 							&c->ss_work, &c->ss_scans, &c->ss_exit_a, &c->ss_exit_b, &c->ss_entry, &c->ss_nblk, &c->ss_first, &c->ss_changed, &c->uslab, &c->useg_len,
-							&c->enc_pix, &c->enc_img, &c->enc_coef, &c->enc_nbits, &c->enc_bitoff, &c->enc_tot, &c->enc_bitbuf, &c->enc_ffcnt, &c->enc_ffoff, &c->enc_out, &c->enc_len, &c->enc_hdr, &c->wide, &c->wide_lut};
+							&c->pipe_work, &c->pipe_preds, &c->pipe_progress, &c->enc_pix, &c->enc_img, &c->enc_coef, &c->enc_nbits, &c->enc_bitoff, &c->enc_tot, &c->enc_bitbuf, &c->enc_ffcnt, &c->enc_ffoff, &c->enc_out, &c->enc_len, &c->enc_hdr, &c->wide, &c->wide_lut};
 	for (auto b : bufs)
 		if (b->p)
 			cudaFree(b->p);
@@ -303,6 +311,7 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 	CK(cudaSetDevice(c->device));
 	c->n_images = b->n_images;
 	c->n_waves = b->n_waves;
+	c->n_scans = b->n_scans;
 	c->coef_elems = b->coef_elems;
 	c->out_bytes = b->out_bytes;
 	c->need_clear = b->need_coef_clear != 0;
@@ -431,6 +440,81 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 	}
 	if (!c->ss_scan_h.empty())
 		c->need_clear = true; /* phase 4 writes single coefficients into zeroed blocks */
+	/* which scans take the warp decoder (k_prog_coop), and which images consist of such scans only */
+	std::vector<char> is_coop((size_t)std::max(1, b->n_scans), 0), img_piped((size_t)std::max(1, b->n_images), 0);
+	{
+		std::vector<int> n_all((size_t)std::max(1, b->n_images), 0), n_coop((size_t)std::max(1, b->n_images), 0);
+		for (int s = 0; s < b->n_scans; ++s)
+		{
+			const jcu_scan &sc = b->scans[s];
+			if (!imgs[sc.image].ok)
+				continue;
+			const bool ac = sc.kind == JCU_SCAN_PROG_AC_FIRST || sc.kind == JCU_SCAN_PROG_AC_REFINE;
+			/* a first DC pass clears its blocks (jpeg.c:385): only one that nothing precedes may rely on the zeroed slab */
+			const bool dc = sc.kind == JCU_SCAN_PROG_DC_REFINE || (sc.kind == JCU_SCAN_PROG_DC_FIRST && sc.wave == 0 && c->need_clear);
+			int distinct_dc = 0; /* a first DC pass may use one table per component; the warp decoder holds PC_MAX_LUTS */
+			if (sc.kind == JCU_SCAN_PROG_DC_FIRST)
+				for (int i = 0; i < sc.ncomp; ++i)
+				{
+					bool fresh = true;
+					for (int j = 0; j < i; ++j)
+						fresh = fresh && sc.dc_spec[j] != sc.dc_spec[i];
+					distinct_dc += fresh;
+				}
+			is_coop[s] = ((ac && sc.ncomp == 1) || dc) && sc.nseg == 1 && c->entropy_mode != 1 && !is_ss[s] && distinct_dc <= PC_MAX_LUTS;
+			++n_all[sc.image];
+			n_coop[sc.image] += is_coop[s];
+		}
+		for (int i = 0; i < b->n_images; ++i)
+			img_piped[i] = n_all[i] > 1 && n_all[i] == n_coop[i];
+	}
+	c->pipe_work_h.clear();
+	c->pipe_preds_h.assign((size_t)std::max(1, b->n_scans) * PC_MAX_PREDS, -1);
+	std::vector<uint64_t> behind((size_t)std::max(1, b->n_scans), 0); /* scans (bit = ordinal in the image) a scan is known to stay behind */
+	for (int s = 0; s < b->n_scans; ++s)
+	{
+		const jcu_scan &sc = b->scans[s];
+		if (!imgs[sc.image].ok || !img_piped[sc.image])
+			continue;
+		int first = s; /* first scan of the image */
+		while (first > 0 && b->scans[first - 1].image == sc.image)
+			--first;
+		if (s - first >= 64)
+		{
+			img_piped[sc.image] = 2;
+			continue;
+		}
+		/* the predecessors of a scan: earlier scans of its image that share a component and overlap its write set -- the
+		   rule that gives the dependency levels in jpeg_parse.c (one_scan).  The NEAREST ones are kept: they are behind
+		   their own predecessors in turn. */
+		auto lo = [](const jcu_scan &x) { return (x.kind == JCU_SCAN_BASELINE || x.kind == JCU_SCAN_PROG_DC_FIRST) ? 0 : x.ss; };
+		auto hi = [](const jcu_scan &x) {
+			return (x.kind == JCU_SCAN_BASELINE || x.kind == JCU_SCAN_PROG_DC_FIRST) ? 63
+					 : x.kind == JCU_SCAN_PROG_AC_FIRST											  ? std::min(63, x.se + 15)
+																													  : x.se;
+		};
+		int np = 0;
+		for (int j = s - 1; j >= 0 && b->scans[j].image == sc.image; --j)
+		{
+			const jcu_scan &o = b->scans[j];
+			bool shared = false;
+			for (int a = 0; a < sc.ncomp; ++a)
+				for (int q = 0; q < o.ncomp; ++q)
+					shared = shared || sc.comp[a] == o.comp[q];
+			if (!shared || lo(sc) > hi(o) || lo(o) > hi(sc))
+				continue;
+			/* a predecessor of a predecessor needs no wait of its own: the nearer one never overtakes it */
+			if (behind[s] & (1ull << (j - first)))
+				continue;
+			behind[s] |= (1ull << (j - first)) | behind[j];
+			if (np == PC_MAX_PREDS)
+			{
+				img_piped[sc.image] = 2; /* more predecessors than the table holds: this image keeps the level-by-level launches */
+				break;
+			}
+			c->pipe_preds_h[(size_t)s * PC_MAX_PREDS + np++] = j;
+		}
+	}
 	c->wave_off.assign((size_t)b->n_waves + 1, 0);
 	c->wave_nbase.assign((size_t)b->n_waves, 0);
 	c->wave_two.assign((size_t)b->n_waves, 1);
@@ -450,13 +534,20 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 				const jcu_scan &sc = b->scans[s];
 				if (sc.wave != w || !imgs[sc.image].ok || is_ss[s])
 					continue;
-				const bool ac = sc.kind == JCU_SCAN_PROG_AC_FIRST || sc.kind == JCU_SCAN_PROG_AC_REFINE;
-				/* a first DC pass clears its blocks (jpeg.c:385): only one that nothing precedes may rely on the zeroed slab */
-				const bool dc = sc.kind == JCU_SCAN_PROG_DC_REFINE || (sc.kind == JCU_SCAN_PROG_DC_FIRST && sc.wave == 0 && c->need_clear);
-				const bool coop = ((ac && sc.ncomp == 1) || dc) && sc.nseg == 1 && c->entropy_mode != 1;
+				const bool coop = is_coop[s] != 0;
 				const int group = sc.kind == JCU_SCAN_BASELINE ? 0 : coop ? 3 : sc.nseg <= ENT_SMALL_THREADS ? 1 : 2;
 				if (group != pass)
 					continue;
+				if (coop && img_piped[sc.image] == 1)
+				{
+					/* the whole chain of this image goes into the one pipelined launch, in level order */
+					EntWork wk;
+					wk.scan = s;
+					wk.seg_first = 0;
+					wk.nseg = 1;
+					c->pipe_work_h.push_back(wk);
+					continue;
+				}
 				if (pass == 0)
 				{
 					int nd = 0, na = 0;
@@ -494,6 +585,30 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 		c->wave_ncoop[w] = (int)c->work_h.size() - c->wave_ncoop[w];
 	}
 	c->wave_off[b->n_waves] = (int)c->work_h.size();
+	if (!c->pipe_work_h.empty())
+	{
+		/* Ticket order of the pipelined launch.  Level-major order over the whole batch would fill the machine with the
+		   first levels of all images; instead the images go in groups whose scans are all resident at once, level-major
+		   inside a group -- predecessors still come first, and every chain of a group runs as a pipeline. */
+		int max_scans = 1;
+		std::vector<int> per_img((size_t)b->n_images, 0), rank((size_t)b->n_images, -1);
+		for (const EntWork &wk : c->pipe_work_h)
+			max_scans = std::max(max_scans, ++per_img[b->scans[wk.scan].image]);
+		int nrank = 0;
+		for (int i = 0; i < b->n_images; ++i)
+			if (per_img[i])
+				rank[i] = nrank++;
+		const int group = std::max(1, (c->pc_resident * 9 / 10) / max_scans);
+		std::stable_sort(c->pipe_work_h.begin(), c->pipe_work_h.end(), [&](const EntWork &x, const EntWork &y) {
+			const jcu_scan &sx = b->scans[x.scan], &sy = b->scans[y.scan];
+			const int gx = rank[sx.image] / group, gy = rank[sy.image] / group;
+			if (gx != gy)
+				return gx < gy;
+			if (sx.wave != sy.wave)
+				return sx.wave < sy.wave;
+			return x.scan < y.scan;
+		});
+	}
 
 	/* ---- device buffers ---- */
 	CK(ensure(c->bits, b->bitstream_bytes + 64));
@@ -530,6 +645,12 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 		CK(ensure(c->ss_changed, 256));
 	}
 
+	if (!c->pipe_work_h.empty())
+	{
+		CK(ensure(c->pipe_work, sizeof(EntWork) * c->pipe_work_h.size()));
+		CK(ensure(c->pipe_preds, sizeof(int32_t) * c->pipe_preds_h.size()));
+		CK(ensure(c->pipe_progress, sizeof(int32_t) * ((size_t)b->n_scans + 4)));
+	}
 	if ((size_t)b->n_images + 2 > c->err_host_cap)
 	{
 		if (c->err_host)
@@ -557,6 +678,8 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 		{c->ss_work_h.data(), sizeof(SsWork) * c->ss_work_h.size(), c->ss_work.p},
 		{c->ss_scan_h.data(), sizeof(SsScan) * c->ss_scan_h.size(), c->ss_scans.p},
 		{c->list_h.data(), sizeof(int32_t) * c->list_h.size(), c->lists.p},
+		{c->pipe_work_h.data(), sizeof(EntWork) * c->pipe_work_h.size(), c->pipe_work.p},
+		{c->pipe_preds_h.data(), c->pipe_work_h.empty() ? 0 : sizeof(int32_t) * c->pipe_preds_h.size(), c->pipe_preds.p},
 	};
 	size_t desc_bytes = 0;
 	for (const Part &pt : parts)
@@ -633,6 +756,24 @@ extern "C" int jcu_run(jcu_ctx *c)
 
 	const jcu_image *d_img = (const jcu_image *)c->images.p;
 	const int16_t *d_coef = (const int16_t *)c->coef.p;
+	PcPipe no_pipe;
+	no_pipe.preds = nullptr;
+	no_pipe.progress = nullptr;
+	no_pipe.ticket = nullptr;
+	if (!c->pipe_work_h.empty())
+	{
+		/* progressive files without restart markers: every scan of an image at once, each behind its predecessors
+		   (jpeg_entropy_prog.cuh, PcPipe); the word behind the progress array is the work ticket */
+		PcPipe pp;
+		pp.preds = (const int32_t *)c->pipe_preds.p;
+		pp.progress = (int32_t *)c->pipe_progress.p;
+		pp.ticket = (uint32_t *)c->pipe_progress.p + c->n_scans;
+		CK(cudaMemsetAsync(c->pipe_progress.p, 0, sizeof(int32_t) * ((size_t)c->n_scans + 4), st));
+		k_prog_coop<<<(unsigned)c->pipe_work_h.size(), PC_THREADS, 0, st>>>((const EntWork *)c->pipe_work.p, (const jcu_scan *)c->scans.p, d_img,
+																								  (const uint32_t *)c->segs.p, (const jcu_huff_spec *)c->huff.p,
+																								  (const uint8_t *)c->bits.p, (int16_t *)c->coef.p, (int32_t *)c->err.p, pp);
+		c->launches++;
+	}
 	for (int w = 0; w < c->n_waves; ++w)
 	{
 		const int n = c->wave_off[w + 1] - c->wave_off[w], nb = c->wave_nbase[w];
@@ -660,7 +801,7 @@ extern "C" int jcu_run(jcu_ctx *c)
 			const EntWork *wc = wk + (n - nco);
 			k_prog_coop<<<nco, PC_THREADS, 0, st>>>(wc, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p,
 																(const jcu_huff_spec *)c->huff.p, (const uint8_t *)c->bits.p, (int16_t *)c->coef.p,
-																(int32_t *)c->err.p);
+																(int32_t *)c->err.p, no_pipe);
 			c->launches++;
 		}
 		if (nsm > 0)

@@ -51,8 +51,12 @@
 #define ENTB_SLOT_WORDS 32 /* 64 int16; byte o of lane l's block sits at o ^ entb_slot_key(l) */
 #define ENTB_MAX_MCU_BLOCKS 64
 
+#ifndef ENTB_DC_BITS
 #define ENTB_DC_BITS 9
+#endif
+#ifndef ENTB_AC_BITS
 #define ENTB_AC_BITS 11
+#endif
 
 /* 16-bit lookup entry: kadv (7) | size (4) << 7 | len (5) << 11 ; 0 = code longer than the table's prefix */
 #define ENTB_E_KADV(e) ((e) & 127u)

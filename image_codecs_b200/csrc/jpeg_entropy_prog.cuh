@@ -40,6 +40,7 @@
 #include "jpeg_entropy.cuh"
 
 #define PC_THREADS 32
+#define PC_MAX_LUTS 2 /* 8 KB of shared memory per scan instead of 13: every scan of a 256-image batch is resident at once */
 #define PC_RING_BYTES 512
 #define PC_FULL 0xffffffffu
 
@@ -50,7 +51,7 @@
 
 struct PcShared
 {
-	HuffLut lut[4];
+	HuffLut lut[PC_MAX_LUTS]; /* distinct tables of the scan (a DC scan with more goes to the per-segment decoder) */
 	int lut_of[4];
 	uint32_t ring[PC_RING_BYTES / 4];
 	uint32_t tab[64];	 /* DC scans: per block of an MCU: slot | x << 4 | y << 8 | lut << 12 */
@@ -236,18 +237,77 @@ __device__ __forceinline__ int pc_extend(uint32_t top, int len, int s)
 }
 
 /*
+ * Scan pipelining (PcPipe, round 2).  The scans of a progressive file form a dependency chain (first passes before
+ * refinements of the same coefficients), and round 1 ran the chain level by level: one launch per level, each as long
+ * as its slowest scan -- four to five scan durations per image.  But a scan only needs its predecessors to be AHEAD of
+ * it, not finished: in pipelined mode every scan of an image runs at once, publishes how far down the image it is
+ * final (in pixel rows, after every row of units) and waits, before each row of units, until its predecessors have
+ * passed that row.  The chain then costs about its longest scan.  The work items are handed out by a ticket in
+ * (level, scan) order, so a scan's predecessors always started before it and a waiting warp can never keep a
+ * predecessor off the machine.  Coefficients written by another warp are read from L2 (ld.global.cg).
+ */
+#define PC_MAX_PREDS 4
+struct PcPipe
+{
+	const int32_t *preds; /* per scan: PC_MAX_PREDS scan indices it must stay behind, -1 = none; NULL = not pipelined */
+	int32_t *progress;	 /* per scan: pixel rows of the image below which the scan's output is final */
+	uint32_t *ticket;		 /* next work item */
+};
+__device__ __forceinline__ int16_t pc_ld(const int16_t *p, bool l2) { return l2 ? __ldcg(p) : *p; }
+/* before a row of units that covers pixel rows up to y_needed */
+__device__ __forceinline__ void pc_wait(const PcPipe &pp, const int32_t *my_preds, int y_needed, int lane)
+{
+	if (!pp.preds)
+		return;
+	if (lane == 0)
+		for (int i = 0; i < PC_MAX_PREDS; ++i)
+		{
+			const int p = my_preds[i];
+			if (p < 0)
+				continue;
+			const volatile int32_t *f = pp.progress + p;
+			unsigned spins = 0;
+			while (*f < y_needed && ++spins < (1u << 28)) /* the cap only keeps a broken build from hanging the GPU */
+				__nanosleep(200);
+		}
+	__syncwarp();
+	__threadfence();
+}
+/* after a row of units: everything up to pixel row y_done is final */
+__device__ __forceinline__ void pc_publish(const PcPipe &pp, int scan, int y_done, int lane)
+{
+	if (!pp.preds)
+		return;
+	__threadfence();
+	__syncwarp();
+	if (lane == 0)
+		*reinterpret_cast<volatile int32_t *>(pp.progress + scan) = y_done;
+}
+
+/*
  * grid = CTA work items (one single-segment progressive scan each), 32 threads.
  */
 __global__ void __launch_bounds__(PC_THREADS)
 k_prog_coop(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans, const jcu_image *__restrict__ images,
 				const uint32_t *__restrict__ seg_start, const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ bitstream,
-				int16_t *__restrict__ coef, int32_t *__restrict__ img_err)
+				int16_t *__restrict__ coef, int32_t *__restrict__ img_err, PcPipe pp)
 {
 	__shared__ PcShared sh;
+	__shared__ uint32_t s_item;
 	const int lane = threadIdx.x;
-	const EntWork w = work[blockIdx.x];
+	const bool piped = pp.preds != nullptr;
+	if (piped)
+	{
+		if (lane == 0)
+			s_item = atomicAdd(pp.ticket, 1u);
+		__syncwarp();
+	}
+	const EntWork w = work[piped ? s_item : blockIdx.x];
 	const jcu_scan *sc = &scans[w.scan];
 	const jcu_image *im = &images[sc->image];
+	const int32_t *my_preds = piped ? pp.preds + (size_t)w.scan * PC_MAX_PREDS : nullptr;
+	/* pixel rows one row of this scan's units covers */
+	const int rows_px = 8 * (sc->ncomp == 1 ? im->vmax / max(1, im->comp[sc->comp[0]].v) : im->vmax);
 	const int kind = sc->kind, ncs = sc->ncomp;
 	const bool is_dc = kind == JCU_SCAN_PROG_DC_FIRST || kind == JCU_SCAN_PROG_DC_REFINE;
 	for (int i = lane; i < 80; i += PC_THREADS)
@@ -261,16 +321,20 @@ k_prog_coop(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans
 			{
 				if (lane == 0)
 					report_failure(img_err, sc, 0u, JCU_ERR_BAD_HUFFMAN);
+				pc_publish(pp, w.scan, 0x7fffffff, lane);
 				return;
 			}
-			int alias = -1;
+			int alias = -1, distinct = 0;
 			for (int j = 0; j < i; ++j)
+			{
 				if ((is_dc ? sc->dc_spec[j] : sc->ac_spec[j]) == spec)
 					alias = sh.lut_of[j];
+				distinct = max(distinct, sh.lut_of[j] + 1);
+			}
 			if (alias < 0)
 			{
-				hufflut_build(&sh.lut[i], &huff[spec], is_dc, lane, PC_THREADS);
-				alias = i;
+				alias = min(distinct, PC_MAX_LUTS - 1); /* the host sends no scan with more distinct tables here */
+				hufflut_build(&sh.lut[alias], &huff[spec], is_dc, lane, PC_THREADS);
 			}
 			if (lane == 0)
 				sh.lut_of[i] = alias;
@@ -328,8 +392,17 @@ k_prog_coop(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans
 	{
 		/* ---- one bit per block (jpeg.c:395-400): 32 blocks per step ---- */
 		const uint32_t nblocks = (uint32_t)total * (uint32_t)nblk_mcu;
+		const uint32_t per_row = (uint32_t)upr * (uint32_t)nblk_mcu; /* blocks of one row of units */
+		uint32_t waited_to = 0; /* blocks covered by the rows waited for so far */
 		for (uint32_t g0 = 0; g0 < nblocks; g0 += 32u)
 		{
+			if (piped && g0 + 32u > waited_to)
+			{
+				const uint32_t row_hi = (min(g0 + 31u, nblocks - 1u)) / per_row;
+				pc_publish(pp, w.scan, (int)(g0 / per_row) * rows_px, lane); /* rows wholly below g0 are final */
+				pc_wait(pp, my_preds, (int)(row_hi + 1u) * rows_px, lane);
+				waited_to = (row_hi + 1u) * per_row;
+			}
 			pc_need32(st, sh.ring, lane);
 			const uint32_t bits = pc_top(st);
 			const uint32_t g = g0 + (uint32_t)lane;
@@ -341,7 +414,7 @@ k_prog_coop(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans
 				const int by = (int)(m / (uint32_t)upr) * sh.dc_vn[slot] + (int)((t >> 8) & 15u);
 				int16_t *blk = coef + sh.dc_off[slot] + ((size_t)by * sh.dc_bw[slot] + bx) * 64;
 				int16_t *p0 = &blk[coef_pos(0, coef_key(blk))];
-				*p0 = (int16_t)(*p0 + (int16_t)(1 << al));
+				*p0 = (int16_t)(pc_ld(p0, piped) + (int16_t)(1 << al));
 			}
 			pc_drop(st, (int)min(32u, nblocks - g0));
 		}
@@ -353,6 +426,11 @@ k_prog_coop(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans
 		int ux = 0, uy = 0;
 		for (int m = 0; m < total && !failed; ++m)
 		{
+			if (piped && ux == 0)
+			{
+				pc_publish(pp, w.scan, uy * rows_px, lane);
+				pc_wait(pp, my_preds, (uy + 1) * rows_px, lane);
+			}
 			for (int j = 0; j < nblk_mcu; ++j)
 			{
 				const uint32_t t = sh.tab[j];
@@ -417,8 +495,16 @@ k_prog_coop(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans
 		{
 			/* ---- first pass of a band (jpeg.c:412-466): values go straight to the zeroed slab ---- */
 			int u = 0;
+			int row_end = 0; /* first unit behind the rows waited for */
 			while (u < total && !failed)
 			{
+				if (piped && u >= row_end)
+				{
+					const int row = u / upr;
+					pc_publish(pp, w.scan, row * rows_px, lane);
+					pc_wait(pp, my_preds, (row + 1) * rows_px, lane);
+					row_end = (row + 1) * upr;
+				}
 				int16_t *blk = plane + ((size_t)(u / upr) * bw + (u % upr)) * 64;
 				const unsigned key = coef_key(blk);
 				int k = ss, eob_run = 0;
@@ -487,11 +573,13 @@ k_prog_coop(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans
 			int c0n = 0, c1n = 0; /* prefetched coefficients of the next block */
 			int bx = 0;
 			int16_t *row = plane, *blk = plane;
+			int rowi = 0;
 			if (total > 0)
 			{
+				pc_wait(pp, my_preds, rows_px, lane);
 				const unsigned key = coef_key(blk);
-				c0n = blk[coef_pos(nat0, key)];
-				c1n = blk[coef_pos(nat1, key)];
+				c0n = pc_ld(&blk[coef_pos(nat0, key)], piped);
+				c1n = pc_ld(&blk[coef_pos(nat1, key)], piped);
 			}
 			for (int u = 0; u < total && !failed; ++u)
 			{
@@ -503,13 +591,21 @@ k_prog_coop(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans
 				{
 					bx = 0;
 					row += (size_t)bw * 64;
+					++rowi;
+					if (piped && u + 1 < total)
+					{
+						/* the next block opens a new row of units: rows above the current one are final (the current block is
+						   still being worked on), and the predecessors must have passed the new row before it is read */
+						pc_publish(pp, w.scan, (rowi - 1) * rows_px, lane);
+						pc_wait(pp, my_preds, (rowi + 1) * rows_px, lane);
+					}
 				}
 				blk = row + (size_t)bx * 64;
 				if (u + 1 < total)
 				{
 					const unsigned kn = coef_key(blk);
-					c0n = blk[coef_pos(nat0, kn)];
-					c1n = blk[coef_pos(nat1, kn)];
+					c0n = pc_ld(&blk[coef_pos(nat0, kn)], piped);
+					c1n = pc_ld(&blk[coef_pos(nat1, kn)], piped);
 				}
 				/* history masks inside the band, and this lane's ranks among the zeros / non-zeros below its positions */
 				const uint32_t Mlo = __ballot_sync(PC_FULL, c0 != 0) & band_lo, Mhi = __ballot_sync(PC_FULL, c1 != 0) & band_hi;
@@ -635,6 +731,7 @@ k_prog_coop(const EntWork *__restrict__ work, const jcu_scan *__restrict__ scans
 			}
 		}
 	}
+	pc_publish(pp, w.scan, 0x7fffffff, lane); /* finished (or failed): nobody waits for this scan any more */
 	if (failed)
 	{
 		if (lane == 0)

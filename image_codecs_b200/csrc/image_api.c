@@ -393,6 +393,10 @@ static int batch_parse(stbi_jpeg_batch *b, const stbi_uc *const *bufs, const int
 	size_t *offs, total = 0;
 	int i, nt;
 	double t0 = now_ms();
+	/* the staging slab, the descriptor block and the device buffers are about to be reused: whatever the previous batch
+	   of this object still has in flight (a staged caller may not have waited) must be done first */
+	if (b->count > 0)
+		jcu_sync(b->ctx);
 	batch_release_results(b);
 	if (count > b->cap_res)
 	{

@@ -38,6 +38,7 @@
 #include "jpeg_entropy_baseline.cuh"
 
 #define SS_THREADS 128
+#define SS_SLOT_STRIDE 136 /* bytes between the block-assembly slots of neighbouring threads (write pass) */
 #define SS_SUB_BYTES 256 /* raw bytes per unstuffing thread AND unstuffed bytes per decoding subsequence */
 
 /* entry / exit state of a subsequence: everything a decoder needs to resume, and nothing that depends on its history */
@@ -331,6 +332,9 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 				int16_t *__restrict__ coef, int32_t *__restrict__ img_err, SsBuffers sb)
 {
 	__shared__ EntbShared sh;
+	/* WRITE: one block under assembly per thread, natural order; 34 words apart so that the threads of a warp storing
+	   the same coefficient hit 16 different banks */
+	__shared__ __align__(8) unsigned char s_slot[MODE == SS_WRITE ? SS_THREADS * SS_SLOT_STRIDE : 8];
 	const int tid = threadIdx.x;
 	const SsWork w = work[blockIdx.x];
 	const jcu_scan *sc = &scans[w.scan];
@@ -338,6 +342,10 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 	entb_setup(sh, sc, im, huff, tid, SS_THREADS);
 	if ((uint32_t)tid >= w.count)
 		return;
+	const uint32_t slot = (uint32_t)__cvta_generic_to_shared(s_slot) + (uint32_t)tid * SS_SLOT_STRIDE;
+	if (MODE == SS_WRITE)
+		for (int q = 0; q < 16; ++q)
+			asm volatile("st.shared.v2.u32 [%0], {%1, %1};" ::"r"(slot + 8u * (uint32_t)q), "r"(0u) : "memory");
 
 	const uint32_t i = w.first + (uint32_t)tid, gi = w.scan_base + i;
 	const uint32_t scan_start = seg_start[sc->seg_first];
@@ -399,7 +407,7 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 		locate(g);
 
 	uint32_t nb = 0;
-	bool failed = false;
+	bool failed = false, in_slot_at_exit = false;
 	if (MODE == SS_GUESS)
 	{
 		const uint32_t sh_addr = (uint32_t)__cvta_generic_to_shared(&sh);
@@ -419,6 +427,11 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 			ux = (int)(m % (uint32_t)upr);
 			uy = (int)(m / (uint32_t)upr);
 		}
+		/* A block this thread STARTS is assembled in its shared-memory slot and leaves as eight 16-byte stores when it
+		   is complete (whole sectors: no read-modify-write of the zeroed slab, 8 requests instead of one per non-zero
+		   coefficient).  The block it enters in the middle of (the predecessor began it) and the one it leaves
+		   unfinished go coefficient by coefficient into the zeroed slab, as two threads share them. */
+		bool in_slot = k == 0;
 		while (g < total_blocks && (last || bp < limit))
 		{
 			const uint32_t ent = sh.blk[b];
@@ -456,10 +469,32 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 			const uint32_t zqe = sh.zq[ent & 15u][dc ? 0 : ((k + kadv - 1) & 127)];
 			const int mul = dc ? 1 : (int)(zqe >> 16);
 			if (ok && (dc || val))
-				blk[coef_pos(dc ? 0 : (int)ENTB_ZQ_NAT(zqe), key)] = (int16_t)(val * mul);
+			{
+				const int nat = dc ? 0 : (int)ENTB_ZQ_NAT(zqe);
+				if (in_slot)
+					sts_u16(slot + 2u * (uint32_t)nat, (uint32_t)(val * mul));
+				else
+					blk[coef_pos(nat, key)] = (int16_t)(val * mul);
+			}
 			k = dc ? 1 : k + kadv;
 			if (k >= 64)
 			{
+				if (in_slot)
+				{
+					/* flush: chunk r (coefficient row r) goes to chunk position r ^ key of the block (jpeg_coef_layout.cuh) */
+					uint4 *dst = reinterpret_cast<uint4 *>(blk);
+#pragma unroll
+					for (int r = 0; r < 8; ++r)
+					{
+						uint32_t a0, a1, a2, a3;
+						asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(a0), "=r"(a1) : "r"(slot + 16u * (uint32_t)r));
+						asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(a2), "=r"(a3) : "r"(slot + 16u * (uint32_t)r + 8u));
+						dst[r ^ (int)key] = make_uint4(a0, a1, a2, a3);
+						asm volatile("st.shared.v2.u32 [%0], {%1, %1};" ::"r"(slot + 16u * (uint32_t)r), "r"(0u) : "memory");
+						asm volatile("st.shared.v2.u32 [%0], {%1, %1};" ::"r"(slot + 16u * (uint32_t)r + 8u), "r"(0u) : "memory");
+					}
+				}
+				in_slot = true; /* the next block starts here */
 				k = 0;
 				++g;
 				if (++b == nblk_mcu)
@@ -481,9 +516,19 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 				}
 			}
 		}
+		in_slot_at_exit = in_slot;
 	}
 	if (MODE == SS_WRITE)
 	{
+		/* left in the middle of a block (the successor finishes it): if this thread started it, what was assembled so far
+		   goes into the zeroed slab coefficient by coefficient, like the parts two threads share */
+		if (k != 0 && in_slot_at_exit && g < total_blocks)
+			for (int n = 0; n < 64; ++n)
+			{
+				const uint32_t v = lds_u16(slot + 2u * (uint32_t)n);
+				if (v)
+					blk[coef_pos(n, key)] = (int16_t)v;
+			}
 		if (failed)
 			report_failure(img_err, sc, 0u, JCU_ERR_BAD_HUFFMAN);
 		else if (g_entry < total_blocks && g >= total_blocks)

@@ -763,100 +763,82 @@ k_ss_scan(const SsScan *__restrict__ ss, const uint32_t *__restrict__ nblk, uint
  * (jpeg.c:323-325) and the stored value is (short)(dc * dequant[0]).
  */
 #define SS_DC_THREADS 1024
+#define SS_DC_ROUNDS 32 /* blocks per lane and tile: a tile = 32 warps x 32 rounds x 32 lanes = 32 768 blocks */
 __global__ void __launch_bounds__(SS_DC_THREADS)
 k_ss_dc(const SsScan *__restrict__ ss, const jcu_scan *__restrict__ scans, const jcu_image *__restrict__ images,
 		  int16_t *__restrict__ coef)
 {
-	__shared__ int s_part[SS_DC_THREADS];
+	__shared__ int s_warp[SS_DC_THREADS / 32];
+	__shared__ int s_carry;
 	const jcu_scan *sc = &scans[ss[blockIdx.x].scan];
 	const int slot = blockIdx.y;
 	if (slot >= sc->ncomp)
 		return;
 	const jcu_image *im = &images[sc->image];
 	const jcu_comp *cp = &im->comp[sc->comp[slot]];
-	const int hn = sc->ncomp == 1 ? 1 : cp->h, vn = sc->ncomp == 1 ? 1 : cp->v, per = hn * vn;
-	const int upr = sc->units_per_row, bw = cp->bw;
+	const int hn = sc->ncomp == 1 ? 1 : cp->h, vn = sc->ncomp == 1 ? 1 : cp->v;
+	const uint32_t per = (uint32_t)(hn * vn), upr = (uint32_t)sc->units_per_row;
+	const int bw = cp->bw;
 	const int q0 = (int)im->qt[sc->comp[slot]][0];
-	const uint32_t n = (uint32_t)sc->total_units * (uint32_t)per;
+	const uint32_t n = (uint32_t)sc->total_units * per;
 	int16_t *plane = coef + cp->coef_off;
-	const int tid = threadIdx.x;
-	const uint32_t chunk = (n + SS_DC_THREADS - 1u) / SS_DC_THREADS;
-	const uint32_t lo = min(n, (uint32_t)tid * chunk), hi = min(n, lo + chunk);
-	/* walk the blocks of the component in decode order without a division per block: (unit column, unit row, block in unit) */
-	struct Walk
-	{
-		int ux, uy, r;
-	};
-	auto start = [&](uint32_t j) {
-		Walk wk;
-		const uint32_t m = j / (uint32_t)per;
-		wk.r = (int)(j - m * (uint32_t)per);
-		wk.ux = (int)(m % (uint32_t)upr);
-		wk.uy = (int)(m / (uint32_t)upr);
-		return wk;
-	};
-	auto addr = [&](const Walk &wk) -> int16_t * {
-		const int y = wk.r / hn, x = wk.r - y * hn;
-		int16_t *blk = plane + ((size_t)(wk.uy * vn + y) * bw + (wk.ux * hn + x)) * 64;
+	const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+	/* block j of the component in decode order -> its DC word.  A warp reads 32 CONSECUTIVE blocks per round (one
+	   sector each, neighbours in the slab) and keeps the 32 rounds of a tile in registers: the slab is read once and
+	   written once (the first version summed in one sweep and re-read everything in a second). */
+	auto addr = [&](uint32_t j) -> int16_t * {
+		const uint32_t m = j / per, r = j - m * per;
+		const uint32_t uy = m / upr, ux = m - uy * upr;
+		const uint32_t y = r / (uint32_t)hn, x = r - y * (uint32_t)hn;
+		int16_t *blk = plane + ((size_t)(uy * (uint32_t)vn + y) * (size_t)bw + (ux * (uint32_t)hn + x)) * 64;
 		return blk + coef_pos(0, coef_key(blk));
 	};
-	auto step = [&](Walk &wk) {
-		if (++wk.r == per)
-		{
-			wk.r = 0;
-			if (++wk.ux == upr)
-			{
-				wk.ux = 0;
-				++wk.uy;
-			}
-		}
-	};
-	int sum = 0;
-	{
-		Walk wk = start(lo);
-#pragma unroll 8
-		for (uint32_t j = lo; j < hi; ++j)
-		{
-			sum += (int)*addr(wk);
-			step(wk);
-		}
-	}
-	s_part[tid] = sum;
-	__syncthreads();
 	if (tid == 0)
-	{
-		int run = 0;
-		for (int i = 0; i < SS_DC_THREADS; ++i)
-		{
-			const int v = s_part[i];
-			s_part[i] = run;
-			run += v;
-		}
-	}
+		s_carry = 0;
 	__syncthreads();
-	int pred = s_part[tid];
+	const uint32_t tile_blocks = SS_DC_THREADS * SS_DC_ROUNDS;
+	for (uint32_t t0 = 0; t0 < n; t0 += tile_blocks)
 	{
-		/* eight blocks at a time: all loads first (nothing else writes these words), then the running sum and the stores --
-		   otherwise every load waits for the store before it, which the compiler must assume to alias */
-		Walk wk = start(lo);
-		for (uint32_t j = lo; j < hi; j += 8u)
+		const uint32_t wlo = t0 + (uint32_t)wid * (32u * SS_DC_ROUNDS);
+		int d[SS_DC_ROUNDS];
+		int mine = 0;
+#pragma unroll
+		for (int q = 0; q < SS_DC_ROUNDS; ++q)
 		{
-			int16_t *p[8];
-			int d[8];
-#pragma unroll
-			for (int q = 0; q < 8; ++q)
-			{
-				p[q] = addr(wk);
-				d[q] = j + (uint32_t)q < hi ? (int)*p[q] : 0;
-				step(wk);
-			}
-#pragma unroll
-			for (int q = 0; q < 8; ++q)
-				if (j + (uint32_t)q < hi)
-				{
-					pred += d[q];
-					*p[q] = (int16_t)(pred * q0);
-				}
+			const uint32_t j = wlo + 32u * (uint32_t)q + (uint32_t)lane;
+			d[q] = j < n ? (int)*addr(j) : 0;
 		}
+#pragma unroll
+		for (int q = 0; q < SS_DC_ROUNDS; ++q)
+			mine += d[q];
+#pragma unroll
+		for (int o = 16; o > 0; o >>= 1)
+			mine += __shfl_xor_sync(0xffffffffu, mine, o);
+		if (lane == 0)
+			s_warp[wid] = mine;
+		__syncthreads();
+		int pred = s_carry; /* dc_pred (jpeg.c:323) in front of this warp's first block */
+		for (int w2 = 0; w2 < wid; ++w2)
+			pred += s_warp[w2];
+#pragma unroll
+		for (int q = 0; q < SS_DC_ROUNDS; ++q)
+		{
+			int v = d[q];
+#pragma unroll
+			for (int o = 1; o < 32; o <<= 1)
+			{
+				const int u = __shfl_up_sync(0xffffffffu, v, o);
+				if (lane >= o)
+					v += u;
+			}
+			const uint32_t j = wlo + 32u * (uint32_t)q + (uint32_t)lane;
+			if (j < n)
+				*addr(j) = (int16_t)((pred + v) * q0);
+			pred += __shfl_sync(0xffffffffu, v, 31);
+		}
+		__syncthreads();
+		if (tid == SS_DC_THREADS - 1)
+			s_carry = pred; /* the last warp's running value = everything up to the end of the tile */
+		__syncthreads();
 	}
 }

@@ -26,7 +26,7 @@ class Params(C.Structure):
     _fields_ = [("device", C.c_int), ("host_threads", C.c_int), ("chunk_images", C.c_int), ("profile", C.c_int),
                 ("entropy_mode", C.c_int), ("pipeline_depth", C.c_int), ("device_mem_mb", C.c_int),
                 ("no_download_merge", C.c_int), ("trace", C.c_int), ("force_generic", C.c_int),
-                ("rows_per_band", C.c_int), ("debug_guards", C.c_int)]
+                ("rows_per_band", C.c_int), ("debug_guards", C.c_int), ("selfsync_sub_bytes", C.c_int)]
 
 
 class Timings(C.Structure):
@@ -253,8 +253,8 @@ class BatchDecoder:
 
     def __init__(self, device: int = 0, host_threads: int = 0, chunk_images: int = 0, profile: bool = True,
                  entropy_mode: int = 0, **tuning):
-        """tuning: pipeline_depth, device_mem_mb, no_download_merge, trace, force_generic, rows_per_band, debug_guards
-        (stbi_jpeg_batch_params in include/image_api.h)."""
+        """tuning: pipeline_depth, device_mem_mb, no_download_merge, trace, force_generic, rows_per_band, debug_guards,
+        selfsync_sub_bytes (stbi_jpeg_batch_params in include/image_api.h)."""
         p = Params()
         p.device, p.host_threads, p.chunk_images, p.profile, p.entropy_mode = (device, host_threads, chunk_images,
                                                                                int(profile), entropy_mode)

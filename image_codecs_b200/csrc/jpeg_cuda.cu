@@ -41,6 +41,7 @@ struct jcu_ctx
 	int entropy_mode = 0;
 	bool guard = false;
 	int rows_per_band_forced = 0;
+	uint32_t ss_sub_forced = 0;
 	cudaStream_t stream = nullptr;
 	/* downloads run on their own stream, behind an event of the compute stream */
 	cudaStream_t dl_own = nullptr, dl_use = nullptr;
@@ -50,6 +51,7 @@ struct jcu_ctx
 					ev_d2h1 = nullptr;
 	bool d2h_open = false;
 	DevBuf bits, images, scans, segs, huff, work, coef, planes, out, err, lists;
+	DevBuf ss_dwork, ss_dscans; /* the decoding phases' work items / scans (subsequences of ss_sub_bytes) */
 	DevBuf ss_work, ss_scans, ss_exit_a, ss_exit_b, ss_entry, ss_nblk, ss_first, ss_changed;
 	DevBuf wide, wide_lut; /* 16-bit / float copy of one image and its look-up table (jpeg_widen.cuh) */
 	DevBuf uslab, useg_len; /* unstuffed copy of the baseline segments (jpeg_entropy_baseline.cuh) */
@@ -57,7 +59,10 @@ struct jcu_ctx
 	cudaEvent_t ev_enc0 = nullptr, ev_enc1 = nullptr;
 	std::vector<SsWork> ss_work_h; /* self-synchronising decode: CTA work items over all waves */
 	std::vector<SsScan> ss_scan_h;
-	uint32_t ss_nsub_total = 0, ss_max_nsub = 0;
+	std::vector<SsWork> ss_dwork_h; /* the same scans cut into decoding subsequences */
+	std::vector<SsScan> ss_dscan_h;
+	uint32_t ss_nsub_total = 0, ss_max_nsub = 0; /* raw 256-byte chunks (unstuffing) */
+	uint32_t ss_dsub_total = 0, ss_max_dsub = 0, ss_sub_bytes = SS_SUB_BYTES; /* decoding subsequences */
 	int ss_rounds = 0; /* refine rounds the last run needed (read back with the per-image errors) */
 	int ss_coop_ctas = 0; /* CTAs of k_ss_refine_loop that are resident at once on this device */
 	int pc_resident = 1024; /* CTAs of k_prog_coop that are resident at once */
@@ -176,6 +181,8 @@ extern "C" int jcu_ctx_create_opts(const jcu_ctx_options *o, jcu_ctx **out)
 	c->guard = o->guard != 0;
 	c->force_generic = o->force_generic != 0;
 	c->rows_per_band_forced = o->rows_per_band > 0 ? o->rows_per_band : 0;
+	if (o->selfsync_sub_bytes == 32 || o->selfsync_sub_bytes == 64 || o->selfsync_sub_bytes == 128 || o->selfsync_sub_bytes == 256)
+		c->ss_sub_forced = (uint32_t)o->selfsync_sub_bytes;
 	e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
 	if (e != cudaSuccess)
 	{
@@ -218,7 +225,7 @@ extern "C" void jcu_ctx_destroy(jcu_ctx *c)
 	cudaSetDevice(c->device);
 	cudaStreamSynchronize(c->stream);
 	DevBuf *bufs[] = {&c->bits, &c->images, &c->scans, &c->segs, &c->huff, &c->work, &c->coef, &c->planes, &c->out, &c->err, &c->lists,
-							&c->ss_work, &c->ss_scans, &c->ss_exit_a, &c->ss_exit_b, &c->ss_entry, &c->ss_nblk, &c->ss_first, &c->ss_changed, &c->uslab, &c->useg_len,
+							&c->ss_work, &c->ss_scans, &c->ss_dwork, &c->ss_dscans, &c->ss_exit_a, &c->ss_exit_b, &c->ss_entry, &c->ss_nblk, &c->ss_first, &c->ss_changed, &c->uslab, &c->useg_len,
 							&c->pipe_work, &c->pipe_preds, &c->pipe_progress, &c->enc_pix, &c->enc_img, &c->enc_coef, &c->enc_nbits, &c->enc_bitoff, &c->enc_tot, &c->enc_bitbuf, &c->enc_ffcnt, &c->enc_ffoff, &c->enc_out, &c->enc_len, &c->enc_hdr, &c->wide, &c->wide_lut};
 	for (auto b : bufs)
 		if (b->p)
@@ -252,7 +259,7 @@ extern "C" int jcu_debug_guards_ok(jcu_ctx *c)
 	if (cudaStreamSynchronize(c->stream) != cudaSuccess)
 		return 0;
 	DevBuf *bufs[] = {&c->bits, &c->images, &c->scans, &c->segs, &c->huff, &c->work, &c->coef, &c->planes, &c->out, &c->err, &c->lists,
-							&c->ss_work, &c->ss_scans, &c->ss_exit_a, &c->ss_exit_b, &c->ss_entry, &c->ss_nblk, &c->ss_first, &c->ss_changed,
+							&c->ss_work, &c->ss_scans, &c->ss_dwork, &c->ss_dscans, &c->ss_exit_a, &c->ss_exit_b, &c->ss_entry, &c->ss_nblk, &c->ss_first, &c->ss_changed,
 							&c->uslab, &c->useg_len};
 	std::vector<unsigned char> h(JCU_GUARD_BYTES);
 	int which = 0;
@@ -388,8 +395,12 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 	c->work_h.clear();
 	c->ss_work_h.clear();
 	c->ss_scan_h.clear();
+	c->ss_dwork_h.clear();
+	c->ss_dscan_h.clear();
 	c->ss_nsub_total = 0;
 	c->ss_max_nsub = 0;
+	c->ss_dsub_total = 0;
+	c->ss_max_dsub = 0;
 	std::vector<char> is_ss((size_t)std::max(1, b->n_scans), 0);
 	for (int s = 0; s < b->n_scans; ++s)
 	{
@@ -439,7 +450,46 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 		is_ss[s] = 1;
 	}
 	if (!c->ss_scan_h.empty())
+	{
 		c->need_clear = true; /* phase 4 writes single coefficients into zeroed blocks */
+		/* Decoding subsequences: 256 unstuffed bytes when the batch fills the GPU with them; a small batch (the
+		   per-image stbi_load of ONE 512 x 512 file is 409 of them) takes shorter ones, down to 32 bytes -- every phase is
+		   one dependent chain per thread, so its latency is the subsequence length, and idle SMs cost nothing. */
+		unsigned long long total = 0;
+		for (const SsScan &e : c->ss_scan_h)
+		{
+			const jcu_scan &sc = b->scans[e.scan];
+			total += sc.data_end - b->seg_start[sc.seg_first];
+		}
+		uint32_t sub = SS_SUB_BYTES;
+		while (sub > SS_MIN_SUB && total / sub < 131072ull)
+			sub >>= 1;
+		if (c->ss_sub_forced) /* jcu_ctx_options.selfsync_sub_bytes: tests and tuning */
+			sub = c->ss_sub_forced;
+		c->ss_sub_bytes = sub;
+		for (const SsScan &u : c->ss_scan_h)
+		{
+			const jcu_scan &sc = b->scans[u.scan];
+			const uint32_t bytes = sc.data_end - b->seg_start[sc.seg_first];
+			SsScan e = u;
+			e.base = c->ss_dsub_total;
+			e.nsub = std::max(1u, (bytes + sub - 1u) / sub); /* the unstuffed stream is never longer than the raw one */
+			c->ss_dscan_h.push_back(e);
+			for (uint32_t f = 0; f < e.nsub; f += SS_THREADS)
+			{
+				SsWork wk;
+				wk.scan = e.scan;
+				wk.first = f;
+				wk.count = std::min<uint32_t>(SS_THREADS, e.nsub - f);
+				wk.scan_base = e.base;
+				wk.scan_nsub = e.nsub;
+				wk.pad = 0;
+				c->ss_dwork_h.push_back(wk);
+			}
+			c->ss_dsub_total += e.nsub;
+			c->ss_max_dsub = std::max(c->ss_max_dsub, e.nsub);
+		}
+	}
 	/* which scans take the warp decoder (k_prog_coop), and which images consist of such scans only */
 	std::vector<char> is_coop((size_t)std::max(1, b->n_scans), 0), img_piped((size_t)std::max(1, b->n_images), 0);
 	{
@@ -634,9 +684,11 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 	CK(ensure(c->lists, sizeof(int32_t) * std::max<size_t>(1, c->list_h.size())));
 	if (!c->ss_scan_h.empty())
 	{
-		const size_t n = c->ss_nsub_total;
+		const size_t n = std::max(c->ss_nsub_total, c->ss_dsub_total);
 		CK(ensure(c->ss_work, sizeof(SsWork) * c->ss_work_h.size()));
 		CK(ensure(c->ss_scans, sizeof(SsScan) * c->ss_scan_h.size()));
+		CK(ensure(c->ss_dwork, sizeof(SsWork) * c->ss_dwork_h.size()));
+		CK(ensure(c->ss_dscans, sizeof(SsScan) * c->ss_dscan_h.size()));
 		CK(ensure(c->ss_exit_a, sizeof(SsState) * n));
 		CK(ensure(c->ss_exit_b, sizeof(SsState) * n));
 		CK(ensure(c->ss_entry, sizeof(SsState) * n));
@@ -677,6 +729,8 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 		{c->work_h.data(), sizeof(EntWork) * c->work_h.size(), c->work.p},
 		{c->ss_work_h.data(), sizeof(SsWork) * c->ss_work_h.size(), c->ss_work.p},
 		{c->ss_scan_h.data(), sizeof(SsScan) * c->ss_scan_h.size(), c->ss_scans.p},
+		{c->ss_dwork_h.data(), sizeof(SsWork) * c->ss_dwork_h.size(), c->ss_dwork.p},
+		{c->ss_dscan_h.data(), sizeof(SsScan) * c->ss_dscan_h.size(), c->ss_dscans.p},
 		{c->list_h.data(), sizeof(int32_t) * c->list_h.size(), c->lists.p},
 		{c->pipe_work_h.data(), sizeof(EntWork) * c->pipe_work_h.size(), c->pipe_work.p},
 		{c->pipe_preds_h.data(), c->pipe_work_h.empty() ? 0 : sizeof(int32_t) * c->pipe_preds_h.size(), c->pipe_preds.p},
@@ -831,9 +885,12 @@ extern "C" int jcu_run(jcu_ctx *c)
 		sb.changed = (int32_t *)c->ss_changed.p;
 		sb.sync = (uint32_t *)c->ss_changed.p + 4;
 		sb.result = (int32_t *)c->ss_changed.p + 8;
+		sb.sub_bytes = c->ss_sub_bytes;
 		const unsigned nw = (unsigned)c->ss_work_h.size(), ns = (unsigned)c->ss_scan_h.size();
-		const SsWork *wk = (const SsWork *)c->ss_work.p;
-#define SS_ARGS wk, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p, (const jcu_huff_spec *)c->huff.p, \
+		const unsigned ndw = (unsigned)c->ss_dwork_h.size();
+		const SsWork *wk = (const SsWork *)c->ss_work.p, *dwk = (const SsWork *)c->ss_dwork.p;
+		const SsScan *dscans = (const SsScan *)c->ss_dscans.p;
+#define SS_ARGS dwk, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p, (const jcu_huff_spec *)c->huff.p, \
 					 (const uint8_t *)c->bits.p, (const uint8_t *)c->uslab.p, (const uint32_t *)c->useg_len.p, (int16_t *)c->coef.p, \
 					 (int32_t *)c->err.p, sb
 		/* phase U: count the bytes each 256-byte raw chunk keeps, prefix sum per scan, write the unstuffed stream */
@@ -842,26 +899,26 @@ extern "C" int jcu_run(jcu_ctx *c)
 		k_ss_scan<<<ns, 256, 0, st>>>((const SsScan *)c->ss_scans.p, sb.nblk, sb.first_blk);
 		k_ss_unstuff<true><<<nw, SS_THREADS, 0, st>>>(wk, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p,
 																	 (const uint8_t *)c->bits.p, (uint8_t *)c->uslab.p, (uint32_t *)c->useg_len.p, sb);
-		k_ss_decode<SS_GUESS><<<nw, SS_THREADS, 0, st>>>(SS_ARGS);
+		k_ss_decode<SS_GUESS><<<ndw, SS_THREADS, 0, st>>>(SS_ARGS);
 		c->launches += 4;
 		/* the Jacobi rounds run to convergence inside ONE cooperative launch (grid barrier per round, jpeg_selfsync.cuh):
 		   no flag copy, no stream synchronisation, the host never learns the round count before jcu_image_errors */
 		CK(cudaMemsetAsync(c->ss_changed.p, 0, 64, st));
 		{
-			const SsWork *a_work = wk;
-			unsigned a_nw = nw, a_max = c->ss_max_nsub + 2u;
+			const SsWork *a_work = dwk;
+			unsigned a_nw = ndw, a_max = c->ss_max_dsub + 2u;
 			const jcu_scan *a_scans = (const jcu_scan *)c->scans.p;
 			const uint32_t *a_segs = (const uint32_t *)c->segs.p;
 			const jcu_huff_spec *a_huff = (const jcu_huff_spec *)c->huff.p;
 			const uint8_t *a_uslab = (const uint8_t *)c->uslab.p;
 			const uint32_t *a_ulen = (const uint32_t *)c->useg_len.p;
 			void *args[] = {&a_work, &a_nw, &a_scans, &d_img, &a_segs, &a_huff, &a_uslab, &a_ulen, &sb, &a_max};
-			const unsigned grid = std::min<unsigned>(nw, (unsigned)std::max(1, c->ss_coop_ctas));
+			const unsigned grid = std::min<unsigned>(ndw, (unsigned)std::max(1, c->ss_coop_ctas));
 			CK(cudaLaunchCooperativeKernel((const void *)k_ss_refine_loop, dim3(grid), dim3(SS_THREADS), args, 0, st));
 		}
 		c->launches++;
-		k_ss_scan<<<ns, 256, 0, st>>>((const SsScan *)c->ss_scans.p, sb.nblk, sb.first_blk);
-		k_ss_decode<SS_WRITE><<<nw, SS_THREADS, 0, st>>>(SS_ARGS); /* entry states: side sb.result[0] */
+		k_ss_scan<<<ns, 256, 0, st>>>(dscans, sb.nblk, sb.first_blk);
+		k_ss_decode<SS_WRITE><<<ndw, SS_THREADS, 0, st>>>(SS_ARGS); /* entry states: side sb.result[0] */
 		k_ss_dc<<<dim3(ns, 4), SS_DC_THREADS, 0, st>>>((const SsScan *)c->ss_scans.p, (const jcu_scan *)c->scans.p, d_img, (int16_t *)c->coef.p);
 		c->launches += 3;
 #undef SS_ARGS

@@ -39,7 +39,10 @@
 
 #define SS_THREADS 128
 #define SS_SLOT_STRIDE 136 /* bytes between the block-assembly slots of neighbouring threads (write pass) */
-#define SS_SUB_BYTES 256 /* raw bytes per unstuffing thread AND unstuffed bytes per decoding subsequence */
+#ifndef SS_MIN_SUB
+#define SS_MIN_SUB 64u /* shortest decoding subsequence (bytes); measured on ONE 512 x 512 file: 16 / 32 / 64 / 128 / 256 -> 0.69 / 0.64 / 0.60 / 0.77 / 0.95 ms */
+#endif
+#define SS_SUB_BYTES 256 /* raw bytes per unstuffing thread; also the largest decoding subsequence (SsBuffers.sub_bytes) */
 
 /* entry / exit state of a subsequence: everything a decoder needs to resume, and nothing that depends on its history */
 struct SsState
@@ -79,6 +82,16 @@ struct SsBuffers
 	int32_t *changed;			  /* [3] rotating flags: round t sets changed[t % 3] when an exit state changed */
 	uint32_t *sync;			  /* [0] arrivals at the grid barrier of k_ss_refine_loop, [1] its generation */
 	int32_t *result;			  /* [0] ping-pong side that holds the final exit states, [1] rounds run */
+	uint32_t sub_bytes;		  /* unstuffed bytes per decoding subsequence: 32 .. 256, chosen per batch (jpeg_cuda.cu) */
+};
+
+/* write pass: one entry per block of an MCU (k_ss_decode<SS_WRITE>) */
+struct __align__(16) SsBlockInfo
+{
+	long long base;	 /* element offset of the block at unit (0, 0): component plane + position inside the unit */
+	int32_t sx, sy;	 /* elements per unit column / unit row */
+	uint32_t dc_tab, ac_tab, zq; /* shared-memory addresses: lookup tables, zig-zag/dequantiser table */
+	uint32_t pad;
 };
 
 /* per self-sync scan */
@@ -340,26 +353,50 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 	const jcu_scan *sc = &scans[w.scan];
 	const jcu_image *im = &images[sc->image];
 	entb_setup(sh, sc, im, huff, tid, SS_THREADS);
-	if ((uint32_t)tid >= w.count)
+	/* WRITE: per block of an MCU, what a thread needs when it starts that block -- the block's address is
+	   coef + base + ux * sx + uy * sy (elements), the shared-memory addresses of its tables */
+	__shared__ SsBlockInfo s_bi[MODE == SS_WRITE ? ENTB_MAX_MCU_BLOCKS : 1];
+	if (MODE == SS_WRITE)
+	{
+		if (tid < sh.nblk)
+		{
+			const uint32_t ent = sh.blk[tid];
+			const int sl = (int)(ent & 15u);
+			SsBlockInfo bi;
+			bi.base = (long long)sh.coff[sl] + ((long long)((ent >> 8) & 15u) * sh.bw[sl] + (long long)((ent >> 4) & 15u)) * 64;
+			bi.sx = sh.hn[sl] * 64;
+			bi.sy = sh.vn[sl] * sh.bw[sl] * 64;
+			bi.dc_tab = (uint32_t)__cvta_generic_to_shared(sh.dc[(ent >> 12) & 3u].fast);
+			bi.ac_tab = (uint32_t)__cvta_generic_to_shared(sh.ac[(ent >> 16) & 3u].fast);
+			bi.zq = (uint32_t)__cvta_generic_to_shared(sh.zq[sl]);
+			bi.pad = 0u;
+			s_bi[tid] = bi;
+		}
+		__syncthreads();
+	}
+	/* the write pass flushes blocks warp-wide, so every thread of the CTA stays until the end; the others leave here */
+	const bool has_work = (uint32_t)tid < w.count;
+	if (MODE != SS_WRITE && !has_work)
 		return;
 	const uint32_t slot = (uint32_t)__cvta_generic_to_shared(s_slot) + (uint32_t)tid * SS_SLOT_STRIDE;
 	if (MODE == SS_WRITE)
 		for (int q = 0; q < 16; ++q)
 			asm volatile("st.shared.v2.u32 [%0], {%1, %1};" ::"r"(slot + 8u * (uint32_t)q), "r"(0u) : "memory");
 
-	const uint32_t i = w.first + (uint32_t)tid, gi = w.scan_base + i;
+	const uint32_t i = w.first + (uint32_t)(has_work ? tid : 0), gi = w.scan_base + i;
 	const uint32_t scan_start = seg_start[sc->seg_first];
 	const uint32_t ul = useg_len[sc->seg_first];
 	const uint32_t exact = (ul & ~15u) - (ul & 15u); /* bytes of the scan once the stuffing is gone */
 	SsReader rd;
 	rd.src = reinterpret_cast<const uint32_t *>(uslab + entb_useg_off(im->data_off, scan_start, (uint32_t)sc->seg_first));
 	rd.nwords = (ul & ~15u) >> 2;
-	const uint32_t nsub_real = max(1u, (exact + SS_SUB_BYTES - 1u) / SS_SUB_BYTES); /* subsequences that hold data */
+	const uint32_t sub = sb.sub_bytes;
+	const uint32_t nsub_real = max(1u, (exact + sub - 1u) / sub); /* subsequences that hold data */
 	const bool last = i + 1u == nsub_real;
-	const uint32_t limit = (i + 1u) * (SS_SUB_BYTES * 8u);
+	const uint32_t limit = (i + 1u) * (sub * 8u);
 	const int nblk_mcu = sh.nblk;
 
-	uint32_t bp = i * (SS_SUB_BYTES * 8u);
+	uint32_t bp = i * (sub * 8u);
 	int b = 0, k = 0;
 	if (MODE == SS_WRITE && i > 0)
 	{
@@ -369,7 +406,8 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 		k = (int)(en.aux & 255u);
 		b = (int)((en.aux >> 8) & 0xfffu);
 	}
-	if (i >= nsub_real)
+	const bool alive = has_work && i < nsub_real;
+	if (MODE != SS_WRITE && !alive)
 	{
 		/* behind the data (the raw scan was longer than the unstuffed one): nothing to decode; pass the state on */
 		if (MODE == SS_GUESS)
@@ -416,10 +454,11 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 	}
 	else
 	{
-		/* One instruction path for DC and AC symbols (table, prefix width, target position and multiplier are selected),
-		   so the lanes of a warp -- at unrelated places of their blocks -- only diverge at the end of a block, where the
-		   next block's address is formed from counters that are carried along instead of divided out again. */
-		const uint32_t sh_addr = (uint32_t)__cvta_generic_to_shared(&sh);
+		/* One instruction path for DC and AC symbols (table, prefix width, target position and multiplier are selected):
+		   the lanes of a warp stand at unrelated places of their blocks.  The end of a block is arithmetic as well -- the
+		   counters step under a predicate and the next block's address and tables come from s_bi -- and the completed
+		   blocks of a step are written by the WHOLE warp, one 128-byte line per block (round 2 first had each lane flush its
+		   own block: 41 % of the warp instructions ran with 2.7 active lanes). */
 		int ux = 0, uy = 0;
 		if (g < total_blocks)
 		{
@@ -427,94 +466,109 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 			ux = (int)(m % (uint32_t)upr);
 			uy = (int)(m / (uint32_t)upr);
 		}
-		/* A block this thread STARTS is assembled in its shared-memory slot and leaves as eight 16-byte stores when it
-		   is complete (whole sectors: no read-modify-write of the zeroed slab, 8 requests instead of one per non-zero
-		   coefficient).  The block it enters in the middle of (the predecessor began it) and the one it leaves
-		   unfinished go coefficient by coefficient into the zeroed slab, as two threads share them. */
-		bool in_slot = k == 0;
-		while (g < total_blocks && (last || bp < limit))
+		uint32_t dc_tab, ac_tab, zq_addr;
 		{
-			const uint32_t ent = sh.blk[b];
-			const bool dc = k == 0;
-			const uint32_t top = __funnelshift_l(rd.nxt, rd.cur, bp);
-			const uint32_t tdc = (ent >> 12) & 3u, tac = (ent >> 16) & 3u;
-			const uint32_t tab = dc ? (uint32_t)offsetof(EntbShared, dc) + tdc * (uint32_t)sizeof(EntbDc)
-											: (uint32_t)offsetof(EntbShared, ac) + tac * (uint32_t)sizeof(EntbAc);
-			const uint32_t idx = dc ? top >> (32 - ENTB_DC_BITS) : top >> (32 - ENTB_AC_BITS);
-			uint32_t e = lds_u16(sh_addr + tab + (idx << 1));
-			bool ok = true;
-			if (e == 0u)
+			const SsBlockInfo bi = s_bi[b];
+			dc_tab = bi.dc_tab;
+			ac_tab = bi.ac_tab;
+			zq_addr = bi.zq;
+		}
+		/* A block this thread STARTS is assembled in its shared-memory slot and leaves as one 128-byte line when it is
+		   complete (whole sectors: no read-modify-write of the zeroed slab).  The block it enters in the middle of (the
+		   predecessor began it) and the one it leaves unfinished go coefficient by coefficient into the zeroed slab, as
+		   two threads share them. */
+		bool in_slot = k == 0;
+		const uint32_t lane = (uint32_t)tid & 31u;
+		const uint32_t warp_slots = (uint32_t)__cvta_generic_to_shared(s_slot) + (uint32_t)(tid & ~31) * SS_SLOT_STRIDE + 4u * lane;
+		bool active = alive && g < total_blocks && (last || bp < limit);
+		while (__any_sync(0xffffffffu, active))
+		{
+			bool done = false;
+			if (active)
 			{
-				const uint32_t t16 = top >> 16;
-				const uint32_t *lim = dc ? sh.dc[tdc].limit : sh.ac[tac].limit;
-				const int32_t *basep = dc ? sh.dc[tdc].base : sh.ac[tac].base;
-				const uint8_t *vals = dc ? sh.dc[tdc].vals : sh.ac[tac].vals;
-				int l = (dc ? ENTB_DC_BITS : ENTB_AC_BITS) + 1;
-				while (t16 >= lim[l])
-					++l;
-				ok = l <= 16;
-				/* invalid code: 16 bits are consumed (jpeg.c:226-230) and the block goes on by one position */
-				e = ok ? entb_entry(vals[(basep[l] + (int)(t16 >> (16 - l))) & 255], l, dc) : (1u | (16u << 11));
+				const bool dc = k == 0;
+				const uint32_t top = __funnelshift_l(rd.nxt, rd.cur, bp);
+				const uint32_t idx = dc ? top >> (32 - ENTB_DC_BITS) : top >> (32 - ENTB_AC_BITS);
+				uint32_t e = lds_u16((dc ? dc_tab : ac_tab) + (idx << 1));
+				bool ok = true;
+				if (e == 0u)
+				{
+					const uint32_t ent = sh.blk[b];
+					const uint32_t tdc = (ent >> 12) & 3u, tac = (ent >> 16) & 3u;
+					const uint32_t t16 = top >> 16;
+					const uint32_t *lim = dc ? sh.dc[tdc].limit : sh.ac[tac].limit;
+					const int32_t *basep = dc ? sh.dc[tdc].base : sh.ac[tac].base;
+					const uint8_t *vals = dc ? sh.dc[tdc].vals : sh.ac[tac].vals;
+					int l = (dc ? ENTB_DC_BITS : ENTB_AC_BITS) + 1;
+					while (t16 >= lim[l])
+						++l;
+					ok = l <= 16;
+					/* invalid code: 16 bits are consumed (jpeg.c:226-230) and the block goes on by one position */
+					e = ok ? entb_entry(vals[(basep[l] + (int)(t16 >> (16 - l))) & 255], l, dc) : (1u | (16u << 11));
+				}
+				const uint32_t len = ENTB_E_LEN(e), size = ENTB_E_SIZE(e);
+				const int kadv = (int)ENTB_E_KADV(e);
+				const uint32_t after = top << len;
+				const uint32_t s32 = 32u - size;
+				const uint32_t v = shr_clamp(after, s32), mask = shr_clamp(0xffffffffu, s32);
+				const int t = (int)after >> 31;
+				const int val = (int)v - (int)(mask & ~(uint32_t)t);
+				ssr_advance(rd, bp, len + size);
+				failed |= !ok;
+				/* DC: the raw difference at position 0 (phase 5 turns it into (short)(dc * q)); AC: (short)(value * q) */
+				const uint32_t zqe = lds_u32(zq_addr + 4u * (uint32_t)(dc ? 0 : ((k + kadv - 1) & 127)));
+				const int mul = dc ? 1 : (int)(zqe >> 16);
+				if (ok && (dc || val))
+				{
+					const int nat = dc ? 0 : (int)ENTB_ZQ_NAT(zqe);
+					if (in_slot)
+						sts_u16(slot + 2u * (uint32_t)nat, (uint32_t)(val * mul));
+					else
+						blk[coef_pos(nat, key)] = (int16_t)(val * mul);
+				}
+				k = dc ? 1 : k + kadv;
+				done = k >= 64;
 			}
-			const uint32_t len = ENTB_E_LEN(e), size = ENTB_E_SIZE(e);
-			const int kadv = (int)ENTB_E_KADV(e);
-			const uint32_t after = top << len;
-			const uint32_t s32 = 32u - size;
-			const uint32_t v = shr_clamp(after, s32), mask = shr_clamp(0xffffffffu, s32);
-			const int t = (int)after >> 31;
-			const int val = (int)v - (int)(mask & ~(uint32_t)t);
-			ssr_advance(rd, bp, len + size);
-			failed |= !ok;
-			/* DC: the raw difference at position 0 (phase 5 turns it into (short)(dc * q)); AC: (short)(value * q) */
-			const uint32_t zqe = sh.zq[ent & 15u][dc ? 0 : ((k + kadv - 1) & 127)];
-			const int mul = dc ? 1 : (int)(zqe >> 16);
-			if (ok && (dc || val))
+			/* ---- completed blocks that sit in a slot: lane l moves word l of each (chunk r = l / 4 goes to chunk position
+			   r ^ key of the block, jpeg_coef_layout.cuh) and clears it for the owner's next block ---- */
+			unsigned fm = __ballot_sync(0xffffffffu, done && in_slot);
+			if (fm)
 			{
-				const int nat = dc ? 0 : (int)ENTB_ZQ_NAT(zqe);
-				if (in_slot)
-					sts_u16(slot + 2u * (uint32_t)nat, (uint32_t)(val * mul));
-				else
-					blk[coef_pos(nat, key)] = (int16_t)(val * mul);
+				__syncwarp();
+				do
+				{
+					const int L = __ffs(fm) - 1;
+					fm &= fm - 1u;
+					uint32_t *d = reinterpret_cast<uint32_t *>(__shfl_sync(0xffffffffu, (unsigned long long)blk, L));
+					const uint32_t sa = warp_slots + (uint32_t)L * SS_SLOT_STRIDE;
+					const uint32_t wv = lds_u32(sa);
+					asm volatile("st.shared.u32 [%0], %1;" ::"r"(sa), "r"(0u) : "memory");
+					d[((((lane >> 2) ^ coef_key(d)) << 2) | (lane & 3u))] = wv;
+				} while (fm);
+				__syncwarp();
 			}
-			k = dc ? 1 : k + kadv;
-			if (k >= 64)
+			/* ---- the next block starts here ---- */
 			{
-				if (in_slot)
+				g += done ? 1u : 0u;
+				const bool wrap_b = b + 1 == nblk_mcu;
+				const bool step_x = done && wrap_b;
+				b = done ? (wrap_b ? 0 : b + 1) : b;
+				ux += step_x ? 1 : 0;
+				const bool wrap_x = step_x && ux == upr;
+				ux = wrap_x ? 0 : ux;
+				uy += wrap_x ? 1 : 0;
+				k = done ? 0 : k;
+				in_slot = in_slot || done;
+				if (done)
 				{
-					/* flush: chunk r (coefficient row r) goes to chunk position r ^ key of the block (jpeg_coef_layout.cuh) */
-					uint4 *dst = reinterpret_cast<uint4 *>(blk);
-#pragma unroll
-					for (int r = 0; r < 8; ++r)
-					{
-						uint32_t a0, a1, a2, a3;
-						asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(a0), "=r"(a1) : "r"(slot + 16u * (uint32_t)r));
-						asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(a2), "=r"(a3) : "r"(slot + 16u * (uint32_t)r + 8u));
-						dst[r ^ (int)key] = make_uint4(a0, a1, a2, a3);
-						asm volatile("st.shared.v2.u32 [%0], {%1, %1};" ::"r"(slot + 16u * (uint32_t)r), "r"(0u) : "memory");
-						asm volatile("st.shared.v2.u32 [%0], {%1, %1};" ::"r"(slot + 16u * (uint32_t)r + 8u), "r"(0u) : "memory");
-					}
-				}
-				in_slot = true; /* the next block starts here */
-				k = 0;
-				++g;
-				if (++b == nblk_mcu)
-				{
-					b = 0;
-					if (++ux == upr)
-					{
-						ux = 0;
-						++uy;
-					}
-				}
-				if (g < total_blocks)
-				{
-					const uint32_t en = sh.blk[b];
-					const int sl = (int)(en & 15u);
-					const int bx = ux * sh.hn[sl] + (int)((en >> 4) & 15u), by = uy * sh.vn[sl] + (int)((en >> 8) & 15u);
-					blk = coef + sh.coff[sl] + ((size_t)by * sh.bw[sl] + bx) * 64;
-					key = coef_key(blk);
+					const SsBlockInfo bi = s_bi[b];
+					blk = coef + (bi.base + (long long)ux * bi.sx + (long long)uy * bi.sy);
+					dc_tab = bi.dc_tab;
+					ac_tab = bi.ac_tab;
+					zq_addr = bi.zq;
 				}
 			}
+			active = active && g < total_blocks && (last || bp < limit);
 		}
 		in_slot_at_exit = in_slot;
 	}
@@ -522,13 +576,16 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 	{
 		/* left in the middle of a block (the successor finishes it): if this thread started it, what was assembled so far
 		   goes into the zeroed slab coefficient by coefficient, like the parts two threads share */
-		if (k != 0 && in_slot_at_exit && g < total_blocks)
+		if (alive && k != 0 && in_slot_at_exit && g < total_blocks)
+		{
+			key = coef_key(blk);
 			for (int n = 0; n < 64; ++n)
 			{
 				const uint32_t v = lds_u16(slot + 2u * (uint32_t)n);
 				if (v)
 					blk[coef_pos(n, key)] = (int16_t)v;
 			}
+		}
 		if (failed)
 			report_failure(img_err, sc, 0u, JCU_ERR_BAD_HUFFMAN);
 		else if (g_entry < total_blocks && g >= total_blocks)
@@ -587,10 +644,10 @@ __device__ __forceinline__ bool ss_refine_item(EntbShared &sh, SsState *s_exit, 
 	SsReader rd;
 	rd.src = reinterpret_cast<const uint32_t *>(uslab + entb_useg_off(im->data_off, seg_start[sc->seg_first], (uint32_t)sc->seg_first));
 	rd.nwords = (ul & ~15u) >> 2;
-	const uint32_t nsub_real = max(1u, (exact + SS_SUB_BYTES - 1u) / SS_SUB_BYTES);
+	const uint32_t nsub_real = max(1u, (exact + sb.sub_bytes - 1u) / sb.sub_bytes);
 	const bool valid = (uint32_t)tid < w.count;
 	const bool live = valid && i < nsub_real; /* subsequences behind the data only pass their entry state on */
-	const uint32_t limit = (i + 1u) * (SS_SUB_BYTES * 8u);
+	const uint32_t limit = (i + 1u) * (sb.sub_bytes * 8u);
 	const SsState *cur = parity ? sb.exit_b : sb.exit_a;
 	SsState *nxt = parity ? sb.exit_a : sb.exit_b;
 

@@ -145,6 +145,7 @@ typedef struct
 	int force_generic;	 /* every image takes the generic two-pass output path */
 	int rows_per_band;	 /* > 0: MCU rows per band of the 4:2:0 strip kernel */
 	int debug_guards;		 /* canaries behind every device buffer, see stbi_jpeg_batch_debug_guards */
+	int selfsync_sub_bytes; /* 32 / 64 / 128 / 256: bytes per subsequence of the self-synchronising decoder (0 = by batch size) */
 } stbi_jpeg_batch_params;
 
 /* per-image status values written by the batch calls */

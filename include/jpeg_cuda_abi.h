@@ -159,7 +159,8 @@ typedef struct
 	int32_t force_generic; /* 1 = every image takes the generic two-pass output path (parity tests of that path) */
 	int32_t rows_per_band; /* > 0 = MCU rows per band of the 4:2:0 strip kernel instead of the batch-size heuristic */
 	int32_t guard;			  /* 1 = every device buffer carries a canary behind its logical size (jcu_debug_guards_ok) */
-	int32_t reserved[2];
+	int32_t selfsync_sub_bytes; /* 32 / 64 / 128 / 256 = bytes per subsequence of the self-synchronising decoder instead of the batch-size heuristic */
+	int32_t reserved[1];
 } jcu_ctx_options;
 JCU_API int jcu_ctx_create_opts(const jcu_ctx_options *o, jcu_ctx **out);
 JCU_API void jcu_ctx_destroy(jcu_ctx *c);

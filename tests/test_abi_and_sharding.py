@@ -38,7 +38,7 @@ def test_library_exports_every_declared_symbol():
 def test_abi_struct_sizes_match_python_binding():
     from image_codecs_b200 import api
 
-    assert C.sizeof(api.Params) == 12 * 4
+    assert C.sizeof(api.Params) == 13 * 4
     assert C.sizeof(api.Timings) == 6 * 4 + 3 * 8 + 6 * 4
 
 

@@ -283,6 +283,28 @@ def test_selfsync_full_size_444_and_gray(oracle, decoder):
     print("self-sync:", tm["selfsync_scans"], "scans,", tm["selfsync_rounds"], "refine rounds")
 
 
+@pytest.mark.parametrize("sub_bytes", [32, 64, 128, 256])
+def test_selfsync_subsequence_sizes(oracle, sub_bytes):
+    """The self-synchronising decoder cuts a scan into subsequences of 32 ... 256 unstuffed bytes (short ones for small
+    batches: the latency of every phase is the subsequence length; 256 when the batch fills the GPU).  Every size must
+    give the reference's pixels: tiny forced scans (fewer bytes than one subsequence), blocks that span several
+    subsequences (q100 dense noise), 4:4:4 / grey / 4:2:0 / 4:1:1 at sizes around 1080p."""
+    from tools import testenc as te
+
+    datas = [S.stream(f, w, h, k) for f, w, h, k in S.small_matrix() if f in ("420", "444", "gray", "411", "420_q100", "cmyk")]
+    datas += te.encode_many(1, 1920, 1080, kind=-1, base_seed=91, quality=90, subsampling="444")
+    datas += te.encode_many(1, 1283, 727, kind=-1, base_seed=92, quality=90, colorspace=te.CS_GRAY)
+    datas += te.encode_many(1, 1000, 700, kind=-1, base_seed=93, quality=100, subsampling="420", optimize=True)
+    datas += te.encode_many(1, 640, 360, kind=1, base_seed=94, quality=30, subsampling="420")  # few bits per block
+    d = ic.BatchDecoder(device=0, entropy_mode=2, selfsync_sub_bytes=sub_bytes)
+    for rc in (3, 0):
+        outs = d.decode(datas, rc)
+        for i, (data, got) in enumerate(zip(datas, outs)):
+            _check(oracle, got, data, rc, f"sub{sub_bytes} #{i} req{rc}")
+    assert d.timings()["selfsync_scans"] >= len(datas), d.timings()
+    d.close()
+
+
 @pytest.mark.parametrize("entropy_mode", [0, 1])
 def test_progressive_restartless_scans(oracle, entropy_mode):
     """BASELINE.json configs[3]: progressive streams without restart markers.  entropy_mode 0 = warp-cooperative

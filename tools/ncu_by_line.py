@@ -31,7 +31,9 @@ for l in txt[i0 + 1:]:
     m = re.match(r"\s+/\*([0-9a-f]{4,})\*/\s+(.*?);", l)
     if m:
         addr2line[int(m.group(1), 16)] = (cur, m.group(2))
-out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", f"regex:{kregex}"], capture_output=True, text=True).stdout
+# NCU_SKIP=n: skip the first n launches that match (e.g. the other instantiation of a template)
+out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", f"regex:{kregex}", "--launch-skip",
+                      os.environ.get("NCU_SKIP", "0"), "--launch-count", "1"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
 h = [i for i, r in enumerate(rows) if "Address" in r and "Source" in r][0]
 hdr = rows[h]

@@ -64,7 +64,8 @@ struct jcu_ctx
 	uint32_t ss_nsub_total = 0, ss_max_nsub = 0; /* raw 256-byte chunks (unstuffing) */
 	uint32_t ss_dsub_total = 0, ss_max_dsub = 0, ss_sub_bytes = SS_SUB_BYTES; /* decoding subsequences */
 	int ss_rounds = 0; /* refine rounds the last run needed (read back with the per-image errors) */
-	int ss_coop_ctas = 0; /* CTAs of k_ss_refine_loop that are resident at once on this device */
+	int ss_coop_ctas = 0, ss_coop_ctas2 = 0; /* CTAs of k_ss_refine_loop<4 + 4 tables / 2 + 2 tables> that are resident at once on this device */
+	bool ss_two = true;	 /* every self-sync scan of the batch uses <= 2 distinct DC and <= 2 distinct AC tables */
 	int pc_resident = 1024; /* CTAs of k_prog_coop that are resident at once */
 	/* batch metadata kept on the host */
 	int n_images = 0, n_waves = 0, n_scans = 0;
@@ -207,9 +208,11 @@ extern "C" int jcu_ctx_create_opts(const jcu_ctx_options *o, jcu_ctx **out)
 	cudaFuncSetAttribute(k_entropy_baseline<4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ENTB_DYN_SMEM);
 	{
 		int per_sm = 0, sms = 0;
-		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ss_refine_loop, SS_THREADS, 0);
 		cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ss_refine_loop<EntbShared>, SS_THREADS, 0);
 		c->ss_coop_ctas = std::max(1, per_sm * sms);
+		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ss_refine_loop<EntbShared2>, SS_THREADS, 0);
+		c->ss_coop_ctas2 = std::max(1, per_sm * sms);
 		per_sm = 0;
 		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_prog_coop, PC_THREADS, 0);
 		c->pc_resident = std::max(64, per_sm * sms);
@@ -456,10 +459,25 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 		   per-image stbi_load of ONE 512 x 512 file is 409 of them) takes shorter ones, down to 32 bytes -- every phase is
 		   one dependent chain per thread, so its latency is the subsequence length, and idle SMs cost nothing. */
 		unsigned long long total = 0;
+		c->ss_two = true;
 		for (const SsScan &e : c->ss_scan_h)
 		{
 			const jcu_scan &sc = b->scans[e.scan];
 			total += sc.data_end - b->seg_start[sc.seg_first];
+			int nd = 0, na = 0;
+			for (int i = 0; i < sc.ncomp; ++i)
+			{
+				bool newd = true, newa = true;
+				for (int j = 0; j < i; ++j)
+				{
+					newd = newd && sc.dc_spec[j] != sc.dc_spec[i];
+					newa = newa && sc.ac_spec[j] != sc.ac_spec[i];
+				}
+				nd += newd;
+				na += newa;
+			}
+			if (nd > 2 || na > 2)
+				c->ss_two = false; /* the kernels then hold four tables of each kind: fewer CTAs per SM */
 		}
 		uint32_t sub = SS_SUB_BYTES;
 		while (sub > SS_MIN_SUB && total / sub < 131072ull)
@@ -899,7 +917,10 @@ extern "C" int jcu_run(jcu_ctx *c)
 		k_ss_scan<<<ns, 256, 0, st>>>((const SsScan *)c->ss_scans.p, sb.nblk, sb.first_blk);
 		k_ss_unstuff<true><<<nw, SS_THREADS, 0, st>>>(wk, (const jcu_scan *)c->scans.p, d_img, (const uint32_t *)c->segs.p,
 																	 (const uint8_t *)c->bits.p, (uint8_t *)c->uslab.p, (uint32_t *)c->useg_len.p, sb);
-		k_ss_decode<SS_GUESS><<<ndw, SS_THREADS, 0, st>>>(SS_ARGS);
+		if (c->ss_two)
+			k_ss_decode<SS_GUESS, EntbShared2><<<ndw, SS_THREADS, 0, st>>>(SS_ARGS);
+		else
+			k_ss_decode<SS_GUESS, EntbShared><<<ndw, SS_THREADS, 0, st>>>(SS_ARGS);
 		c->launches += 4;
 		/* the Jacobi rounds run to convergence inside ONE cooperative launch (grid barrier per round, jpeg_selfsync.cuh):
 		   no flag copy, no stream synchronisation, the host never learns the round count before jcu_image_errors */
@@ -913,12 +934,16 @@ extern "C" int jcu_run(jcu_ctx *c)
 			const uint8_t *a_uslab = (const uint8_t *)c->uslab.p;
 			const uint32_t *a_ulen = (const uint32_t *)c->useg_len.p;
 			void *args[] = {&a_work, &a_nw, &a_scans, &d_img, &a_segs, &a_huff, &a_uslab, &a_ulen, &sb, &a_max};
-			const unsigned grid = std::min<unsigned>(ndw, (unsigned)std::max(1, c->ss_coop_ctas));
-			CK(cudaLaunchCooperativeKernel((const void *)k_ss_refine_loop, dim3(grid), dim3(SS_THREADS), args, 0, st));
+			const unsigned grid = std::min<unsigned>(ndw, (unsigned)std::max(1, c->ss_two ? c->ss_coop_ctas2 : c->ss_coop_ctas));
+			const void *fn = c->ss_two ? (const void *)k_ss_refine_loop<EntbShared2> : (const void *)k_ss_refine_loop<EntbShared>;
+			CK(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(SS_THREADS), args, 0, st));
 		}
 		c->launches++;
 		k_ss_scan<<<ns, 256, 0, st>>>(dscans, sb.nblk, sb.first_blk);
-		k_ss_decode<SS_WRITE><<<ndw, SS_THREADS, 0, st>>>(SS_ARGS); /* entry states: side sb.result[0] */
+		if (c->ss_two) /* entry states: side sb.result[0] */
+			k_ss_decode<SS_WRITE, EntbShared2><<<ndw, SS_THREADS, 0, st>>>(SS_ARGS);
+		else
+			k_ss_decode<SS_WRITE, EntbShared><<<ndw, SS_THREADS, 0, st>>>(SS_ARGS);
 		k_ss_dc<<<dim3(ns, 4), SS_DC_THREADS, 0, st>>>((const SsScan *)c->ss_scans.p, (const jcu_scan *)c->scans.p, d_img, (int16_t *)c->coef.p);
 		c->launches += 3;
 #undef SS_ARGS

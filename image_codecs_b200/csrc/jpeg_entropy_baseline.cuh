@@ -86,6 +86,7 @@ struct EntbSharedT
 	int bw[4], hn[4], vn[4];	 /* per slot: blocks per plane row; blocks per MCU across / down (1 x 1 in single-component scans) */
 };
 typedef EntbSharedT<4, 4> EntbShared;
+typedef EntbSharedT<2, 2> EntbShared2; /* luma + chroma pair: the usual case, half the table space */
 #define ENTB_ZQ_NAT(e) (((e) & 0xffffu) >> 1)
 
 /* entry for symbol `sym` of code length l (l <= 9) */

@@ -277,15 +277,16 @@ __device__ __forceinline__ bool ss_symbol(SsReader &r, uint32_t &bp, const EntbL
  * selected, the block bookkeeping is arithmetic -- so the 32 subsequences of a warp, which stand at unrelated places of
  * their blocks, do not serialise on these cases.  Only a code longer than the table's prefix branches.
  */
-__device__ __forceinline__ void ss_skeleton_step(const EntbShared &sh, uint32_t sh_addr, SsReader &r, uint32_t &bp, int &k, int &b, uint32_t &nb,
+template <typename SH>
+__device__ __forceinline__ void ss_skeleton_step(const SH &sh, uint32_t sh_addr, SsReader &r, uint32_t &bp, int &k, int &b, uint32_t &nb,
 																 int nblk_mcu)
 {
 	const uint32_t ent = sh.blk[b];
 	const bool dc = k == 0;
 	const uint32_t top = __funnelshift_l(r.nxt, r.cur, bp);
 	const uint32_t tdc = (ent >> 12) & 3u, tac = (ent >> 16) & 3u;
-	const uint32_t tab = dc ? (uint32_t)offsetof(EntbShared, dc) + tdc * (uint32_t)sizeof(EntbDc)
-									: (uint32_t)offsetof(EntbShared, ac) + tac * (uint32_t)sizeof(EntbAc);
+	const uint32_t tab = dc ? (uint32_t)offsetof(SH, dc) + tdc * (uint32_t)sizeof(EntbDc)
+									: (uint32_t)offsetof(SH, ac) + tac * (uint32_t)sizeof(EntbAc);
 	const uint32_t idx = dc ? top >> (32 - ENTB_DC_BITS) : top >> (32 - ENTB_AC_BITS);
 	uint32_t e = lds_u16(sh_addr + tab + (idx << 1));
 	uint32_t adv;
@@ -337,14 +338,14 @@ enum
  * the exit state at the first symbol start past its end.  WRITE decodes from the converged entry state (the exit
  * state of the predecessor on side sb.result[0]) and stores coefficients.
  */
-template <int MODE>
+template <int MODE, typename SH>
 __global__ void __launch_bounds__(SS_THREADS)
 k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans, const jcu_image *__restrict__ images,
 				const uint32_t *__restrict__ seg_start, const jcu_huff_spec *__restrict__ huff,
 				const uint8_t *__restrict__ bitstream, const uint8_t *__restrict__ uslab, const uint32_t *__restrict__ useg_len,
 				int16_t *__restrict__ coef, int32_t *__restrict__ img_err, SsBuffers sb)
 {
-	__shared__ EntbShared sh;
+	__shared__ SH sh;
 	/* WRITE: one block under assembly per thread, natural order; 34 words apart so that the threads of a warp storing
 	   the same coefficient hit 16 different banks */
 	__shared__ __align__(8) unsigned char s_slot[MODE == SS_WRITE ? SS_THREADS * SS_SLOT_STRIDE : 8];
@@ -628,7 +629,8 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 #ifndef SS_INNER
 #define SS_INNER 16 /* measured on 256 x 1080p 4:4:4: 8 -> 6 rounds 12.06 ms, 16 -> 4 rounds 11.92 ms, 32 -> 3 rounds 11.88 ms */
 #endif
-__device__ __forceinline__ bool ss_refine_item(EntbShared &sh, SsState *s_exit, const SsWork w, const jcu_scan *__restrict__ scans,
+template <typename SH>
+__device__ __forceinline__ bool ss_refine_item(SH &sh, SsState *s_exit, const SsWork w, const jcu_scan *__restrict__ scans,
 															  const jcu_image *__restrict__ images, const uint32_t *__restrict__ seg_start,
 															  const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ uslab,
 															  const uint32_t *__restrict__ useg_len, const SsBuffers &sb, int parity, int32_t *changed_flag,
@@ -743,12 +745,13 @@ __device__ __forceinline__ void ss_grid_barrier(uint32_t *sync, unsigned nctas)
  * decoder is serial, jpeg.c:1198-1232); what this replaces is one kernel launch + one device-to-host flag copy + one
  * stream synchronisation per round.
  */
+template <typename SH>
 __global__ void __launch_bounds__(SS_THREADS)
 k_ss_refine_loop(const SsWork *__restrict__ work, unsigned nwork, const jcu_scan *__restrict__ scans, const jcu_image *__restrict__ images,
 					  const uint32_t *__restrict__ seg_start, const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ uslab,
 					  const uint32_t *__restrict__ useg_len, SsBuffers sb, unsigned max_rounds)
 {
-	__shared__ EntbShared sh;
+	__shared__ SH sh;
 	__shared__ SsState s_exit[SS_THREADS];
 	int parity = 0, have_scan = -1;
 	unsigned round = 0;

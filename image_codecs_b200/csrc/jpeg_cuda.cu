@@ -903,6 +903,7 @@ extern "C" int jcu_run(jcu_ctx *c)
 		sb.changed = (int32_t *)c->ss_changed.p;
 		sb.sync = (uint32_t *)c->ss_changed.p + 4;
 		sb.result = (int32_t *)c->ss_changed.p + 8;
+		sb.ticket = (uint32_t *)c->ss_changed.p + 12;
 		sb.sub_bytes = c->ss_sub_bytes;
 		const unsigned nw = (unsigned)c->ss_work_h.size(), ns = (unsigned)c->ss_scan_h.size();
 		const unsigned ndw = (unsigned)c->ss_dwork_h.size();

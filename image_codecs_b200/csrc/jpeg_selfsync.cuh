@@ -82,6 +82,7 @@ struct SsBuffers
 	int32_t *changed;			  /* [3] rotating flags: round t sets changed[t % 3] when an exit state changed */
 	uint32_t *sync;			  /* [0] arrivals at the grid barrier of k_ss_refine_loop, [1] its generation */
 	int32_t *result;			  /* [0] ping-pong side that holds the final exit states, [1] rounds run */
+	uint32_t *ticket;			  /* [3] rotating work-item counters of k_ss_refine_loop: round t hands out items from ticket[t % 3] */
 	uint32_t sub_bytes;		  /* unstuffed bytes per decoding subsequence: 32 .. 256, chosen per batch (jpeg_cuda.cu) */
 };
 
@@ -745,32 +746,63 @@ __device__ __forceinline__ void ss_grid_barrier(uint32_t *sync, unsigned nctas)
  * decoder is serial, jpeg.c:1198-1232); what this replaces is one kernel launch + one device-to-host flag copy + one
  * stream synchronisation per round.
  */
+#ifndef SS_REFINE_MIN_CTAS
+#define SS_REFINE_MIN_CTAS 8
+#endif
 template <typename SH>
-__global__ void __launch_bounds__(SS_THREADS)
+__global__ void __launch_bounds__(SS_THREADS, SS_REFINE_MIN_CTAS)
 k_ss_refine_loop(const SsWork *__restrict__ work, unsigned nwork, const jcu_scan *__restrict__ scans, const jcu_image *__restrict__ images,
 					  const uint32_t *__restrict__ seg_start, const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ uslab,
 					  const uint32_t *__restrict__ useg_len, SsBuffers sb, unsigned max_rounds)
 {
 	__shared__ SH sh;
 	__shared__ SsState s_exit[SS_THREADS];
+	__shared__ unsigned s_ticket;
 	int parity = 0, have_scan = -1;
 	unsigned round = 0;
+#ifdef SS_TRACE /* timing experiment only: per round, CTA 0's time in its items and at the barrier */
+	unsigned long long t_prev = 0;
+	asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_prev));
+#endif
 	for (; round < max_rounds; ++round)
 	{
 		int32_t *flag = sb.changed + round % 3u;
-		/* work items are dealt out round-robin (neighbouring items, i.e. one image, spread over the SMs) */
-		for (unsigned it = blockIdx.x; it < nwork; it += gridDim.x)
+		/* Work items are handed out by ticket: an item takes one to sixteen decoding passes, so a fixed deal left most
+		   CTAs waiting at the barrier for the unlucky ones (measured in the first round: 1.3 ms of work, 1.15 ms of
+		   waiting).  Neighbouring items (one image) still spread over the SMs. */
+		for (;;)
 		{
+			__syncthreads(); /* everybody has read the previous ticket */
+			if (threadIdx.x == 0)
+				s_ticket = atomicAdd(sb.ticket + round % 3u, 1u);
+			__syncthreads();
+			const unsigned it = s_ticket;
+			if (it >= nwork)
+				break;
 			const SsWork w = work[it];
 			if (ss_refine_item(sh, s_exit, w, scans, images, seg_start, huff, uslab, useg_len, sb, parity, flag, w.scan != have_scan))
 				have_scan = w.scan;
 		}
 		parity ^= 1;
+#ifdef SS_TRACE
+		unsigned long long t_work = 0, t_bar = 0;
+		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_work));
+#endif
 		ss_grid_barrier(sb.sync, gridDim.x);
+#ifdef SS_TRACE
+		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_bar));
+		if (threadIdx.x == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x / 2))
+			printf("refine cta %u round %u: own items %llu us, waited %llu us at the barrier\n", blockIdx.x, round, (t_work - t_prev) / 1000ull,
+					 (t_bar - t_work) / 1000ull);
+		t_prev = t_bar;
+#endif
 		const int32_t any = *reinterpret_cast<volatile int32_t *>(flag);
 		/* the flag of round + 2 was last read behind the barrier of round - 1, which everybody has left */
 		if (blockIdx.x == 0 && threadIdx.x == 0)
+		{
 			sb.changed[(round + 2u) % 3u] = 0;
+			sb.ticket[(round + 2u) % 3u] = 0u; /* last used in round - 1, whose item loop everybody left before that round's barrier */
+		}
 		if (!any)
 		{
 			++round;

@@ -65,7 +65,7 @@ if __name__ == "__main__":
                     msg = f"{len(dd)} bytes differ, first {dd[0]}"
                 else:
                     cats["same"] += 1
-                if msg and shown < 30 and "[entropy]" in tag:
+                if msg and shown < 30 and ("[entropy]" in tag or "fails" in msg):
                     shown += 1
                     print(f"mode{mode} {tag}: {msg}")
         print(f"mode {mode}: {dict(cats)}")

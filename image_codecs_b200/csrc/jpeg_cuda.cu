@@ -49,9 +49,15 @@ struct Bounce
 {
 	enum
 	{
-		NSLOT = 24,
-		NTHREADS = 6
+		NSLOT = 32
 	};
+	/* copier threads: one moves ~6 GB/s; measured on a 16-core host, 1024 x 1080p: 3 / 6 / 10 / 16 threads ->
+	   6.4 / 9.1 / 10.5 / 11.1 GMP/s (pinned buffers on the same box: 16.7) */
+	static int copier_threads()
+	{
+		const unsigned hc = std::thread::hardware_concurrency();
+		return (int)std::min(12u, std::max(4u, hc / 2u + 2u));
+	}
 	static constexpr size_t SLOT_BYTES = (size_t)2 << 20;
 	struct Job
 	{
@@ -111,7 +117,8 @@ struct Bounce
 				return e;
 			free_slots.push_back(i);
 		}
-		for (int t = 0; t < NTHREADS; ++t)
+		const int nt = copier_threads();
+		for (int t = 0; t < nt; ++t)
 			threads.emplace_back([this] { worker(); });
 		return cudaSuccess;
 	}

@@ -449,7 +449,7 @@ extern "C" const char *jcu_error_string(jcu_ctx *c) { return c ? c->errstr : "no
 extern "C" void *jcu_host_alloc(size_t bytes)
 {
 	void *p = nullptr;
-	if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess)
+	if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) /* page-locked for every device: the multi-device call shares one pair of buffers */
 	{
 		cudaGetLastError();
 		return nullptr;

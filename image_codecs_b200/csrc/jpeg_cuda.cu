@@ -42,9 +42,16 @@ struct DevBuf
  * Downloads into PAGEABLE caller memory (malloc'ed buffers: what a user of stbi_load has).  A cudaMemcpyAsync to
  * pageable memory is staged by the driver and blocks the calling thread for its whole duration (measured: 17.7 GB/s
  * and no overlap with the next chunk's parse).  Instead the copy engine writes 2 MB pieces into a ring of pinned
- * slots and a few host threads move each piece on to the caller's buffer as its event completes; jcu_sync waits for
- * the ring to drain.  Created on the first pageable download of a context.
+ * slots and a few host threads move each piece on to the caller's buffer as its event completes; jcu_sync waits
+ * until the pieces of ITS context have arrived.  ONE ring per device, shared by every context on it (the chunk
+ * pipeline has three, the per-image pool up to sixteen), created on the first pageable download and kept for the
+ * life of the process.
  */
+struct BounceOwner /* per context; both fields are guarded by the ring's mutex */
+{
+	int pending = 0;
+	cudaError_t failed = cudaSuccess;
+};
 struct Bounce
 {
 	enum
@@ -64,6 +71,7 @@ struct Bounce
 		int slot;
 		void *dst;
 		size_t bytes;
+		BounceOwner *owner;
 	};
 	int device = 0;
 	uint8_t *buf[NSLOT] = {nullptr};
@@ -72,9 +80,6 @@ struct Bounce
 	std::condition_variable cv_job, cv_free, cv_idle;
 	std::deque<Job> jobs;
 	std::vector<int> free_slots;
-	int outstanding = 0;
-	bool stop = false;
-	cudaError_t failed = cudaSuccess;
 	std::vector<std::thread> threads;
 
 	void worker()
@@ -85,21 +90,19 @@ struct Bounce
 			Job j;
 			{
 				std::unique_lock<std::mutex> lk(m);
-				cv_job.wait(lk, [&] { return stop || !jobs.empty(); });
-				if (jobs.empty())
-					return;
+				cv_job.wait(lk, [&] { return !jobs.empty(); });
 				j = jobs.front();
 				jobs.pop_front();
 			}
-			const cudaError_t e = cudaEventSynchronize(ev[j.slot]);
-			if (e == cudaSuccess)
+			const cudaError_t e = j.bytes ? cudaEventSynchronize(ev[j.slot]) : cudaSuccess;
+			if (e == cudaSuccess && j.bytes)
 				memcpy(j.dst, buf[j.slot], j.bytes);
 			{
 				std::lock_guard<std::mutex> lk(m);
-				if (e != cudaSuccess && failed == cudaSuccess)
-					failed = e;
+				if (e != cudaSuccess && j.owner->failed == cudaSuccess)
+					j.owner->failed = e;
 				free_slots.push_back(j.slot);
-				--outstanding;
+				--j.owner->pending;
 			}
 			cv_free.notify_one();
 			cv_idle.notify_all();
@@ -119,7 +122,7 @@ struct Bounce
 		}
 		const int nt = copier_threads();
 		for (int t = 0; t < nt; ++t)
-			threads.emplace_back([this] { worker(); });
+			threads.emplace_back([this] { worker(); }).detach(); /* they live as long as the process */
 		return cudaSuccess;
 	}
 	int take_slot()
@@ -130,46 +133,53 @@ struct Bounce
 		free_slots.pop_back();
 		return s;
 	}
-	void submit(int slot, void *dst, size_t bytes)
+	void submit(int slot, void *dst, size_t bytes, BounceOwner *owner)
 	{
 		{
 			std::lock_guard<std::mutex> lk(m);
-			jobs.push_back(Job{slot, dst, bytes});
-			++outstanding;
+			jobs.push_back(Job{slot, dst, bytes, owner});
+			++owner->pending;
 		}
 		cv_job.notify_one();
 	}
-	cudaError_t drain()
+	cudaError_t drain(BounceOwner *owner)
 	{
 		std::unique_lock<std::mutex> lk(m);
-		cv_idle.wait(lk, [&] { return outstanding == 0; });
-		const cudaError_t e = failed;
-		failed = cudaSuccess;
+		cv_idle.wait(lk, [&] { return owner->pending == 0; });
+		const cudaError_t e = owner->failed;
+		owner->failed = cudaSuccess;
 		return e;
 	}
-	~Bounce()
-	{
-		{
-			std::lock_guard<std::mutex> lk(m);
-			stop = true;
-		}
-		cv_job.notify_all();
-		for (auto &t : threads)
-			t.join();
-		for (int i = 0; i < NSLOT; ++i)
-		{
-			if (ev[i])
-				cudaEventDestroy(ev[i]);
-			if (buf[i])
-				cudaFreeHost(buf[i]);
-		}
-	}
 };
+#define JCU_MAX_DEVICES 64
+static Bounce *g_bounce[JCU_MAX_DEVICES];
+static std::mutex g_bounce_m;
+/* the device's ring (the device is current); nullptr + *err when the pinned slots cannot be had */
+static Bounce *bounce_for_device(int device, cudaError_t *err)
+{
+	*err = cudaSuccess;
+	if (device < 0 || device >= JCU_MAX_DEVICES)
+	{
+		*err = cudaErrorInvalidDevice;
+		return nullptr;
+	}
+	std::lock_guard<std::mutex> lk(g_bounce_m);
+	if (!g_bounce[device])
+	{
+		Bounce *b = new Bounce();
+		*err = b->start(device);
+		if (*err != cudaSuccess)
+			return nullptr; /* a half-built ring is left behind rather than torn down under its threads: the error is sticky anyway */
+		g_bounce[device] = b;
+	}
+	return g_bounce[device];
+}
 
 struct jcu_ctx
 {
 	int device = 0;
-	Bounce *bounce = nullptr; /* pinned ring + copier threads for pageable destinations (created on first use) */
+	Bounce *bounce = nullptr; /* the device's pinned ring + copier threads for pageable destinations (first use) */
+	BounceOwner bounce_own;	  /* this context's pieces in flight through it */
 	int profile = 0;
 	int entropy_mode = 0;
 	bool guard = false;
@@ -387,7 +397,8 @@ extern "C" void jcu_ctx_destroy(jcu_ctx *c)
 		if (ev)
 			cudaEventDestroy(ev);
 	cudaStreamSynchronize(c->dl_use);
-	delete c->bounce; /* joins its threads; every job has been drained by the last jcu_sync or completes now */
+	if (c->bounce)
+		c->bounce->drain(&c->bounce_own); /* no copier thread may still hold a pointer into this context */
 	if (c->pin_desc)
 		cudaFreeHost(c->pin_desc);
 	if (c->err_host)
@@ -1158,7 +1169,7 @@ extern "C" int jcu_sync(jcu_ctx *c)
 		c->dl_open = false;
 	}
 	if (c->bounce)
-		CK(c->bounce->drain()); /* pieces on their way from the pinned ring into pageable caller memory */
+		CK(c->bounce->drain(&c->bounce_own)); /* pieces on their way from the pinned ring into pageable caller memory */
 	return 0;
 }
 
@@ -1186,14 +1197,10 @@ extern "C" int jcu_download(jcu_ctx *c, size_t off, size_t bytes, void *dst)
 	{
 		if (!c->bounce)
 		{
-			c->bounce = new Bounce();
-			const cudaError_t e = c->bounce->start(c->device);
-			if (e != cudaSuccess)
-			{
-				delete c->bounce;
-				c->bounce = nullptr;
+			cudaError_t e = cudaSuccess;
+			c->bounce = bounce_for_device(c->device, &e);
+			if (!c->bounce)
 				return set_err(c, e, "jcu_download: pinned staging ring");
-			}
 		}
 		for (size_t done = 0; done < bytes; done += Bounce::SLOT_BYTES)
 		{
@@ -1202,7 +1209,7 @@ extern "C" int jcu_download(jcu_ctx *c, size_t off, size_t bytes, void *dst)
 			cudaError_t e = cudaMemcpyAsync(c->bounce->buf[slot], (const uint8_t *)c->out.p + off + done, n, cudaMemcpyDeviceToHost, c->dl_use);
 			if (e == cudaSuccess)
 				e = cudaEventRecord(c->bounce->ev[slot], c->dl_use);
-			c->bounce->submit(slot, (uint8_t *)dst + done, e == cudaSuccess ? n : 0); /* the slot goes back through the workers either way */
+			c->bounce->submit(slot, (uint8_t *)dst + done, e == cudaSuccess ? n : 0, &c->bounce_own); /* the slot goes back through the workers either way */
 			CK(e);
 		}
 		return 0;

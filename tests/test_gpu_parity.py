@@ -759,6 +759,50 @@ def test_per_image_calls_are_reentrant(oracle):
     assert not errors, errors[:3]
 
 
+def test_pageable_destinations_go_through_the_shared_pinned_ring(oracle):
+    """Downloads of 1 MB and more into malloc'ed (pageable) memory leave the device in 2 MB pieces through ONE ring of
+    pinned slots per device, shared by every context on it (csrc/jpeg_cuda.cu, struct Bounce): the batched call with
+    numpy buffers, and 6 threads of per-image loads (each borrows its own pooled context) at the same time.  Sizes with
+    a ragged last piece; every byte against the reference."""
+    import threading
+    from tools import testenc as te
+
+    datas = te.encode_many(3, 1920, 1080, kind=-1, base_seed=301, quality=90, subsampling="420", restart_interval=16)
+    datas += te.encode_many(2, 1283, 727, kind=-1, base_seed=302, quality=90, subsampling="444")
+    datas += te.encode_many(1, 801, 601, kind=-1, base_seed=303, quality=90, colorspace=te.CS_GRAY)
+    wants = [oracle.load_from_memory(s_, 3)[0] for s_ in datas]
+    errors = []
+
+    def loads(t):
+        try:
+            for k in range(6):
+                i = (t + k) % len(datas)
+                got = ic.stbi_load_from_memory(datas[i], 3)[0]
+                if got is None or not np.array_equal(got, wants[i]):
+                    errors.append(("per-image", t, k, i))
+        except Exception as e:  # pragma: no cover
+            errors.append((t, repr(e)))
+
+    def batches():
+        try:
+            d = ic.BatchDecoder(device=0, profile=False)
+            for k in range(3):
+                outs = d.decode(datas * 4, 3)  # numpy arrays: pageable
+                for j, got in enumerate(outs):
+                    if got is None or not np.array_equal(got, wants[j % len(datas)]):
+                        errors.append(("batch", k, j))
+            d.close()
+        except Exception as e:  # pragma: no cover
+            errors.append(("batch", repr(e)))
+
+    ths = [threading.Thread(target=loads, args=(t,)) for t in range(6)] + [threading.Thread(target=batches)]
+    for th in ths:
+        th.start()
+    for th in ths:
+        th.join()
+    assert not errors, errors[:3]
+
+
 def test_multi_device_entry_point_in_c(oracle):
     """stbi_jpeg_decode_batch_multi: the split (contiguous, byte-balanced), one host thread + pipeline per device and
     the join all happen in C.  Two 'devices' are always driven -- the same GPU twice where the box has one, two

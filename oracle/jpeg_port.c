@@ -98,10 +98,15 @@ typedef struct
 {
 	const u8 *buf;
 	size_t len, pos;
-	/* bit reader (stbi__grow_buffer_unsafe semantics, jpeg.c:167) */
-	uint64_t bits;
-	int nbits;
-	int stop;	 /* marker reached: zeros from now on */
+	/* bit reader, kept exactly like the reference's (jpeg.c:42-47, 167-187): a 32-bit left-aligned buffer that is
+	   refilled at the same places to the same level.  On damaged streams WHERE a refill happens decides what the
+	   decoder does: the refill that meets a marker returns without adding a single bit (jpeg.c:176-182), so a Huffman
+	   code that straddles the end of the data fails with "bad huffman code" (jpeg.c:218, 237) unless an earlier refill
+	   has already met the marker; and how far the reader stands ahead of the decoder at the end of a restart interval
+	   decides whether the RSTn is seen (jpeg.c:1183-1187). */
+	uint32_t cbuf;
+	int cbits;	 /* valid bits at the top of cbuf; may go negative behind a marker, as in the reference */
+	int stop;	 /* marker reached: zeros from now on ("nomore") */
 	int marker; /* the marker that stopped us, 0xff = none */
 
 	unsigned short dq[4][64];
@@ -120,88 +125,143 @@ static int get16(dec *d)
 }
 static int at_eof(dec *d) { return d->pos >= d->len; }
 
-static void fill_bits(dec *d)
+static const uint32_t BMASK[17] = {0, 1, 3, 7, 15, 31, 63, 127, 255, 511, 1023, 2047, 4095, 8191, 16383, 32767, 65535};
+
+/* stbi__grow_buffer_unsafe, jpeg.c:167-187: bytes until more than 24 bits are buffered; FF 00 -> FF, FF FF.. fill,
+   FF xx -> remember the marker and return AT ONCE (no bits added by this call; later calls add zero bytes) */
+static void grow(dec *d)
 {
-	while (d->nbits <= 56)
+	do
 	{
-		unsigned b = 0;
-		if (!d->stop)
+		unsigned b = d->stop ? 0u : (unsigned)get8(d);
+		if (b == 0xff)
 		{
-			b = (unsigned)get8(d);
-			if (b == 0xff)
+			int c = get8(d);
+			while (c == 0xff)
+				c = get8(d);
+			if (c != 0)
 			{
-				int c = get8(d);
-				while (c == 0xff)
-					c = get8(d);
-				if (c != 0)
-				{
-					d->marker = c;
-					d->stop = 1;
-					b = 0;
-				}
+				d->marker = c;
+				d->stop = 1;
+				return;
 			}
 		}
-		d->bits |= (uint64_t)b << (56 - d->nbits);
-		d->nbits += 8;
-	}
+		/* cbits < 0 only behind a marker, where b == 0; the count is masked like the x86 shift the reference compiles to */
+		d->cbuf |= b << ((24 - d->cbits) & 31);
+		d->cbits += 8;
+	} while (d->cbits <= 24);
 }
-static unsigned peek(dec *d, int n)
-{
-	if (d->nbits < n)
-		fill_bits(d);
-	return (unsigned)(d->bits >> (64 - n));
-}
-static void drop(dec *d, int n)
-{
-	d->bits <<= n;
-	d->nbits -= n;
-}
+/* n raw bits: stbi__jpeg_get_bits, jpeg.c:268-278 (n in 1..16) */
 static int take(dec *d, int n)
 {
-	unsigned v;
+	uint32_t k;
 	if (n == 0)
 		return 0;
-	v = peek(d, n);
-	drop(d, n);
-	return (int)v;
+	if (d->cbits < n)
+		grow(d);
+	k = (d->cbuf << n) | (d->cbuf >> (32 - n));
+	d->cbuf = k & ~BMASK[n];
+	d->cbits -= n;
+	return (int)(k & BMASK[n]);
+}
+/* one bit: stbi__jpeg_get_bit, jpeg.c:280-289 */
+static int take1(dec *d)
+{
+	uint32_t k;
+	if (d->cbits < 1)
+		grow(d);
+	k = d->cbuf;
+	d->cbuf <<= 1;
+	--d->cbits;
+	return (k & 0x80000000u) != 0;
 }
 static void reset_entropy(dec *d) /* stbi__jpeg_reset, jpeg.c:1142 */
 {
-	d->bits = 0;
-	d->nbits = 0;
+	d->cbuf = 0;
+	d->cbits = 0;
 	d->stop = 0;
 	d->marker = 0xff;
 	d->c[0].dc_pred = d->c[1].dc_pred = d->c[2].dc_pred = d->c[3].dc_pred = 0;
 	d->eobrun = 0;
 }
 
+/* stbi__jpeg_huff_decode, jpeg.c:193-243.  The reference finds the code through a 9-bit table and a maxcode walk; the
+   canonical search below finds the same (length, symbol).  What matters on damaged data is kept literally: refill
+   below 16 bits, "no such code" eats 16 bits, and a code longer than the bits actually buffered fails. */
 static int decode_sym(dec *d, const htab *t)
 {
-	unsigned code = 0;
+	unsigned window, code;
 	int l;
-	unsigned window = peek(d, 16);
+	if (d->cbits < 16)
+		grow(d);
+	window = d->cbuf >> 16;
 	for (l = 1; l <= 16; ++l)
 	{
 		code = window >> (16 - l);
 		if (t->count[l] && code >= t->first[l] && code - t->first[l] < (unsigned)t->count[l])
 		{
-			drop(d, l);
+			if (l > d->cbits)
+				return -1; /* jpeg.c:218, 237 */
+			d->cbuf <<= l;
+			d->cbits -= l;
 			return t->sym[t->index[l] + (int)(code - t->first[l])];
 		}
 	}
-	drop(d, 16);
+	d->cbits -= 16; /* jpeg.c:229 */
 	return -1;
 }
 
-static int extend(dec *d, int n) /* stbi__extend_receive, jpeg.c:250 */
+/* stbi__extend_receive, jpeg.c:250-265.  n > 16 (a damaged DC table) still triggers the refill and then yields 0
+   without consuming anything; n == 16 reads past the reference's bias table (undefined there, 0 here). */
+static int extend(dec *d, int n)
 {
-	int v;
-	if (n == 0 || n > 16)
+	static const int BIAS[17] = {0, -1, -3, -7, -15, -31, -63, -127, -255, -511, -1023, -2047, -4095, -8191, -16383, -32767, 0};
+	uint32_t k;
+	int sgn;
+	if (d->cbits < n)
+		grow(d);
+	if (n < 0 || n >= 17)
 		return 0;
-	v = take(d, n);
-	if (v < (1 << (n - 1)))
-		v += (int)(~0u << n) + 1;
-	return v;
+	sgn = (int32_t)d->cbuf >> 31;
+	if (n == 0)
+		return 0;
+	k = (d->cbuf << n) | (d->cbuf >> (32 - n));
+	d->cbuf = k & ~BMASK[n];
+	k &= BMASK[n];
+	d->cbits -= n;
+	return (int)k + (BIAS[n] & ~sgn);
+}
+
+/* The reference's fast-AC table (stbi__build_fast_ac, jpeg.c:138-165; used at jpeg.c:335-346 and 427-437): when the top
+   9 bits hold a code of length l AND its s magnitude bits (s > 0, l + s <= 9) and the value fits -128..127, both are
+   consumed in one step WITHOUT the "code longer than the buffer" check.  Returns 1 and fills run / value, else 0. */
+static int fast_ac(dec *d, const htab *t, int *run, int *value)
+{
+	const unsigned top9 = d->cbuf >> 23;
+	int l;
+	for (l = 1; l <= 9; ++l)
+	{
+		const unsigned code = top9 >> (9 - l);
+		if (t->count[l] && code >= t->first[l] && code - t->first[l] < (unsigned)t->count[l])
+		{
+			const int rs = t->sym[t->index[l] + (int)(code - t->first[l])];
+			const int s = rs & 15;
+			int k;
+			if (s == 0 || l + s > 9)
+				return 0;
+			k = (int)((top9 << l) & 511u) >> (9 - s);
+			if (k < (1 << (s - 1)))
+				k += (int)(~0u << s) + 1;
+			if (k < -128 || k > 127)
+				return 0;
+			d->cbuf <<= l + s;
+			d->cbits -= l + s;
+			*run = (rs >> 4) & 15;
+			*value = k;
+			return 1;
+		}
+	}
+	return 0;
 }
 
 /* ---------------------------------------------------------------------------------------------- */
@@ -213,15 +273,28 @@ static int block_baseline(dec *d, short *blk, pcomp *c)
 {
 	const unsigned short *q = d->dq[c->tq];
 	int t, k;
-	memset(blk, 0, 64 * sizeof(short));
+	if (d->cbits < 16)
+		grow(d);
 	t = decode_sym(d, &d->dc[c->hd]);
-	if (t < 0 || t > 15)
+	if (t < 0)
 		return bad("bad huffman code");
-	c->dc_pred += extend(d, t);
+	memset(blk, 0, 64 * sizeof(short));
+	c->dc_pred += t ? extend(d, t) : 0;
 	blk[0] = (short)(c->dc_pred * q[0]);
 	for (k = 1; k < 64;)
 	{
-		int rs = decode_sym(d, &d->ac[c->ha]), r, s;
+		int rs, r, s;
+		if (d->cbits < 16)
+			grow(d);
+		if (fast_ac(d, &d->ac[c->ha], &r, &s))
+		{
+			int z;
+			k += r;
+			z = ZZ[k++];
+			blk[z] = (short)(s * q[z]);
+			continue;
+		}
+		rs = decode_sym(d, &d->ac[c->ha]);
 		if (rs < 0)
 			return bad("bad huffman code");
 		r = rs >> 4;
@@ -248,17 +321,19 @@ static int block_prog_dc(dec *d, short *blk, pcomp *c)
 {
 	if (d->se != 0)
 		return bad("can't merge dc and ac");
+	if (d->cbits < 16)
+		grow(d);
 	if (d->ah == 0)
 	{
 		int t;
 		memset(blk, 0, 64 * sizeof(short));
 		t = decode_sym(d, &d->dc[c->hd]);
-		if (t < 0 || t > 15)
-			return bad("can't merge dc and ac");
-		c->dc_pred += extend(d, t);
+		if (t < 0)
+			return bad("can't merge dc and ac"); /* the reference's text for this case, jpeg.c:388 */
+		c->dc_pred += t ? extend(d, t) : 0;
 		blk[0] = (short)(c->dc_pred * (1 << d->al));
 	}
-	else if (take(d, 1))
+	else if (take1(d))
 		blk[0] = (short)(blk[0] + (short)(1 << d->al));
 	return 1;
 }
@@ -280,7 +355,18 @@ static int block_prog_ac(dec *d, short *blk, const htab *h)
 		k = d->ss;
 		do
 		{
-			int rs = decode_sym(d, h), r, s;
+			int rs, r, s;
+			if (d->cbits < 16)
+				grow(d);
+			if (fast_ac(d, h, &r, &s))
+			{
+				int z;
+				k += r;
+				z = ZZ[k++];
+				blk[z] = (short)(s * (1 << shift));
+				continue;
+			}
+			rs = decode_sym(d, h);
 			if (rs < 0)
 				return bad("bad huffman code");
 			r = rs >> 4;
@@ -315,7 +401,7 @@ static int block_prog_ac(dec *d, short *blk, const htab *h)
 			for (k = d->ss; k <= d->se; ++k)
 			{
 				short *p = &blk[ZZ[k]];
-				if (*p != 0 && take(d, 1) && (*p & bit) == 0)
+				if (*p != 0 && take1(d) && (*p & bit) == 0)
 					*p = (short)(*p > 0 ? *p + bit : *p - bit);
 			}
 		}
@@ -344,14 +430,14 @@ static int block_prog_ac(dec *d, short *blk, const htab *h)
 				{
 					if (s != 1)
 						return bad("bad huffman code");
-					s = take(d, 1) ? bit : -bit;
+					s = take1(d) ? bit : -bit;
 				}
 				while (k <= d->se)
 				{
 					short *p = &blk[ZZ[k++]];
 					if (*p != 0)
 					{
-						if (take(d, 1) && (*p & bit) == 0)
+						if (take1(d) && (*p & bit) == 0)
 							*p = (short)(*p > 0 ? *p + bit : *p - bit);
 					}
 					else
@@ -422,8 +508,8 @@ static int scan_decode(dec *d)
 			if (--todo <= 0)
 			{
 				/* restart interval over (jpeg.c:1183-1191): the next marker must be RSTn, else the scan ends */
-				if (d->nbits < 24)
-					fill_bits(d);
+				if (d->cbits < 24)
+					grow(d);
 				if (!(d->marker >= 0xd0 && d->marker <= 0xd7))
 					return 1;
 				reset_entropy(d);
@@ -500,8 +586,8 @@ static int table_marker(dec *d, int m) /* stbi__process_marker */
 				counts[i] = (u8)get8(d);
 				n += counts[i];
 			}
-			if (n > 256)
-				return bad("bad DHT header");
+			if (n > 256) /* the reference has no such check: stbi__build_huffman overruns its size[257] array (undefined) and in practice ends in this string */
+				return bad("bad code lengths");
 			L -= 17;
 			for (i = 0; i < n; ++i)
 				syms[i] = (u8)get8(d);
@@ -641,8 +727,10 @@ static int scan_header(dec *d) /* stbi__process_scan_header */
 			return 0;
 		d->c[which].hd = q >> 4;
 		d->c[which].ha = q & 15;
-		if (d->c[which].hd > 3 || d->c[which].ha > 3)
-			return bad("bad huff");
+		if (d->c[which].hd > 3)
+			return bad("bad DC huff"); /* jpeg.c:1491 */
+		if (d->c[which].ha > 3)
+			return bad("bad AC huff"); /* jpeg.c:1494 */
 		d->order[i] = which;
 	}
 	d->ss = get8(d);

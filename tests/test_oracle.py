@@ -148,3 +148,38 @@ def test_port_equals_reference_build(port):
             a, b = ref.load_from_memory(data, rc), port.load_from_memory(data, rc)
             assert a[1:] == b[1:], (f, w, h, rc)
             assert np.array_equal(a[0], b[0]), (f, w, h, k, rc)
+
+
+def test_port_follows_the_reference_bit_reader_on_damaged_entropy_data(port):
+    """The port keeps the reference's 32-bit bit buffer and its refill points literally (jpeg.c:167-187, 205, 254, 271,
+    283, 1185), because on damaged data they decide the verdict: the refill that meets a marker adds no bits, so a
+    Huffman code that straddles the end of the data is "bad huffman code" (jpeg.c:218, 237) -- unless the fast-AC
+    table took it (jpeg.c:335) -- and how far the reader stands ahead at a restart boundary decides whether the
+    RSTn is seen (jpeg.c:1183).  Random damage inside the entropy-coded data (tables intact) of baseline files and
+    of progressive files without restart markers -- where the reference never branches on memory it has not
+    written: same verdict and same failure string, file by file."""
+    from oracle import oracle_lib
+    from tools import fuzz_probe as fp
+
+    try:
+        ref = oracle_lib.load("reference")
+    except Exception:
+        pytest.skip("oracle/_ref not present")
+    checked = fails = 0
+    for seed in (11, 12):
+        for tag, data in fp.gen_cases(seed, 40):
+            fmt = tag.split()[0]
+            if "[entropy]" not in tag or ("prog" in fmt and "rst" in fmt):
+                continue
+            ref.load_from_memory(b"junk", 3)  # the reference keeps a stale string where it fails without naming a reason
+            a = ref.load_from_memory(data, 3)[0]
+            ra = ref.failure_reason() if a is None else None
+            ra = None if ra == "unknown image type" else ra
+            b = port.load_from_memory(data, 3)[0]
+            rb = port.failure_reason() if b is None else None
+            assert (a is None) == (b is None), (tag, ra, rb)
+            if a is None:
+                assert ra == rb, (tag, ra, rb)
+                fails += 1
+            checked += 1
+    assert checked > 1500 and fails > 100, (checked, fails)

@@ -520,12 +520,41 @@ __device__ __noinline__ void replay_grow(ReplayReader &r)
 		r.cb += 8;
 	} while (r.cb <= 24);
 }
+enum
+{
+	REPLAY_FINE = 0,
+	REPLAY_TRIPS = 1, /* the reference leaves the scan without having seen the marker behind it and its marker loop runs into an 0xFF */
+	REPLAY_BAD = 2		/* "bad huffman code": no such code */
+};
+/* One symbol as the reference's reader consumes it.  The refill that MEETS the marker adds nothing (replay_grow), but
+   a baseline block refills below 16 bits itself (jpeg.c:313, 332) and stbi__jpeg_huff_decode does so again (:199):
+   behind a freshly met marker the second call pads with zeros, so a code that straddles the end of the data decodes
+   from zero bits ("bad huffman code" at jpeg.c:218, 237 cannot happen here; it can in a progressive AC refinement,
+   which has only the one refill).  AC symbols the reference's fast-AC table holds -- code + magnitude in 9
+   bits, 1..7 magnitude bits (8 would leave -128..127), jpeg.c:138-165 -- are consumed at :335-346 without a
+   further refill. */
 template <int BITS>
-__device__ __forceinline__ bool replay_symbol(ReplayReader &r, const EntbLutT<BITS> *__restrict__ L, bool is_dc, uint32_t &e)
+__device__ __forceinline__ int replay_symbol(ReplayReader &r, const EntbLutT<BITS> *__restrict__ L, bool is_dc, uint32_t &e)
 {
 	if (r.cb < 16)
 		replay_grow(r);
-	const uint32_t top = r.buf;
+	const bool fast_candidate = !is_dc;
+	uint32_t top = r.buf;
+	if (fast_candidate)
+	{
+		const uint32_t e9 = L->fast[top >> (32 - BITS)];
+		const int len9 = (int)ENTB_E_LEN(e9), size9 = (int)ENTB_E_SIZE(e9);
+		if (e9 != 0u && size9 >= 1 && size9 <= 7 && len9 + size9 <= 9)
+		{
+			e = e9;
+			r.buf <<= len9 + size9;
+			r.cb -= len9 + size9;
+			return REPLAY_FINE;
+		}
+	}
+	if (r.cb < 16)
+		replay_grow(r); /* stbi__jpeg_huff_decode's own refill */
+	top = r.buf;
 	e = L->fast[top >> (32 - BITS)];
 	if (e == 0u)
 	{
@@ -534,12 +563,12 @@ __device__ __forceinline__ bool replay_symbol(ReplayReader &r, const EntbLutT<BI
 		while (t16 >= L->limit[l])
 			++l;
 		if (l > 16)
-			return false;
+			return REPLAY_BAD; /* no such code, jpeg.c:226-230 */
 		e = entb_entry(L->vals[(L->base[l] + (int)(t16 >> (16 - l))) & 255], l, is_dc);
 	}
 	const int len = (int)ENTB_E_LEN(e), size = (int)ENTB_E_SIZE(e);
 	if (len > r.cb)
-		return false; /* jpeg.c:218, 237 */
+		return REPLAY_BAD; /* jpeg.c:218, 237: unreachable behind the two refills, kept for the letter of it */
 	r.buf <<= len;
 	r.cb -= len;
 	if (size)
@@ -549,11 +578,11 @@ __device__ __forceinline__ bool replay_symbol(ReplayReader &r, const EntbLutT<BI
 		r.buf <<= size;
 		r.cb -= size;
 	}
-	return true;
+	return REPLAY_FINE;
 }
 template <typename SH>
-__device__ __noinline__ bool entb_replay_trips(const SH &sh, const uint8_t *base, uint32_t len, uint32_t start, int n_units,
-															  bool at_restart, uint32_t data_end)
+__device__ __noinline__ int entb_replay(const SH &sh, const uint8_t *base, uint32_t len, uint32_t start, int n_units, bool at_restart,
+													 uint32_t data_end)
 {
 	ReplayReader r;
 	r.base = base;
@@ -568,24 +597,24 @@ __device__ __noinline__ bool entb_replay_trips(const SH &sh, const uint8_t *base
 		{
 			const uint32_t ent = sh.blk[b];
 			uint32_t e;
-			if (!replay_symbol<ENTB_DC_BITS>(r, &sh.dc[(ent >> 12) & 3u], true, e))
-				return false;
+			if (replay_symbol<ENTB_DC_BITS>(r, &sh.dc[(ent >> 12) & 3u], true, e) != REPLAY_FINE)
+				return REPLAY_BAD;
 			int k = 1;
 			do
 			{
-				if (!replay_symbol<ENTB_AC_BITS>(r, &sh.ac[(ent >> 16) & 3u], false, e))
-					return false;
+				if (replay_symbol<ENTB_AC_BITS>(r, &sh.ac[(ent >> 16) & 3u], false, e) != REPLAY_FINE)
+					return REPLAY_BAD;
 				k += (int)ENTB_E_KADV(e);
 			} while (k < 64);
 		}
 	if (at_restart && r.cb < 24)
 		replay_grow(r);
 	if (r.nomore)
-		return false;
+		return REPLAY_FINE;
 	for (uint32_t q = r.pos; q < len && q < data_end; ++q)
 		if (base[q] == 0xffu)
-			return true;
-	return false;
+			return REPLAY_TRIPS;
+	return REPLAY_FINE;
 }
 
 /*
@@ -771,9 +800,12 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 		const int exact = (int)(ul & ~15u) - (int)(ul & 15u), pos = (int)(br.bp - 64u);
 		const int R = 8 * exact - pos;
 		const bool at_restart = ri > 0 && total % ri == 0;
+		const bool inner = seg + 1 < sc->nseg || sc->end_rst; /* an RSTn follows this segment */
 		bool trips = false;
-		if (seg + 1 < sc->nseg || sc->end_rst)
-			trips = R >= 25; /* the marker loop runs into the RSTn itself */
+		if (inner)
+			/* the marker loop runs into the RSTn itself when the reader has not met it: 25 real bits and more behind the
+			   end position always; exactly 24 only if all 24 sat in the buffer already (no refill at jpeg.c:1185) */
+			trips = R >= 25 || (R == 24 && entb_replay(sh, bitstream + im->data_off, im->data_len, seg_start[g], u1 - u0, true, sc->data_end) == REPLAY_TRIPS);
 		else if (R >= 9)
 		{
 			/* last segment: the first 0xFF data byte (a stuffed FF 00 in the file) wholly behind the end position */
@@ -789,7 +821,7 @@ k_entropy_baseline(const EntWork *__restrict__ work, const jcu_scan *__restrict_
 				else if (at_restart)
 					trips = R >= 25 && 8 * f >= pos + leftover_ahead_bits(R, true);
 				else
-					trips = entb_replay_trips(sh, bitstream + im->data_off, im->data_len, seg_start[g], u1 - u0, false, sc->data_end);
+					trips = entb_replay(sh, bitstream + im->data_off, im->data_len, seg_start[g], u1 - u0, false, sc->data_end) == REPLAY_TRIPS;
 			}
 		}
 		if (trips)

@@ -605,7 +605,7 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 					if (ub[q ^ 3] == 0xffu)
 						f = q;
 				if (f >= 0 && (8 * f >= pos + 32 ||
-									entb_replay_trips(sh, bitstream + im->data_off, im->data_len, scan_start, sc->total_units, false, sc->data_end)))
+									entb_replay(sh, bitstream + im->data_off, im->data_len, scan_start, sc->total_units, false, sc->data_end) == REPLAY_TRIPS))
 					report_failure(img_err, sc, 0u, JCU_ERR_UNKNOWN_MARKER);
 			}
 		}

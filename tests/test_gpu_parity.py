@@ -634,6 +634,30 @@ def test_damaged_streams_decode_like_the_reference(oracle, entropy_mode):
             assert ic.failure_reason() == oracle.failure_reason(), tag
 
 
+def test_damaged_fixtures_found_by_fuzzing(oracle):
+    """tests/golden/damaged/: files tools/fuzz_probe.py found where the verdict hinges on the reference's bit reader.
+    * 420_rst1 ... leftover_exactly_24_bits: a restart interval decoded with exactly 24 real bits left before the RSTn.
+      The reference refills only below 24 buffered bits (jpeg.c:1185), so whether it meets the RSTn depends on how many of
+      the 24 sat in its buffer already; k_entropy_baseline replays its reader for this one value (entb_replay) and
+      must fail with "unknown marker" like the reference.
+    * 420_prog ... refinement_code_straddles_the_end: an AC refinement scan whose last Huffman code is longer than the
+      bits left before EOI.  stbi__jpeg_huff_decode's refill meets the marker and adds nothing, so the reference
+      fails with "bad huffman code" (jpeg.c:218, 499); the progressive kernels feed zero bits there and decode
+      (known gap) -- the test pins the reference's verdict and records ours."""
+    here = os.path.join(os.path.dirname(__file__), "golden", "damaged")
+    data = open(os.path.join(here, "420_rst1_97x61_leftover_exactly_24_bits.jpg"), "rb").read()
+    assert oracle.load_from_memory(data, 3)[0] is None and oracle.failure_reason() == "unknown marker"
+    for mode in (0, 2):
+        d = ic.BatchDecoder(device=0, entropy_mode=mode)
+        assert d.decode([data], 3)[0] is None, f"mode {mode}: the reference fails with 'unknown marker'"
+        d.close()
+    assert ic.stbi_load_from_memory(data, 3)[0] is None and ic.failure_reason() == "unknown marker"
+    data = open(os.path.join(here, "420_prog_97x61_refinement_code_straddles_the_end.jpg"), "rb").read()
+    assert oracle.load_from_memory(data, 3)[0] is None and oracle.failure_reason() == "bad huffman code"
+    got = ic.stbi_load_from_memory(data, 3)[0]
+    print("refinement code straddling the end of the data: gpu", "fails too" if got is None else "decodes (known gap)")
+
+
 @pytest.mark.parametrize("entropy_mode", [0, 2])
 def test_no_kernel_writes_past_a_device_buffer(oracle, entropy_mode):
     """Guard mode (compute-sanitizer is not available on every box): every device buffer is allocated at exactly

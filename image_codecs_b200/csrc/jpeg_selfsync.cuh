@@ -278,22 +278,38 @@ __device__ __forceinline__ bool ss_symbol(SsReader &r, uint32_t &bp, const EntbL
  * selected, the block bookkeeping is arithmetic -- so the 32 subsequences of a warp, which stand at unrelated places of
  * their blocks, do not serialise on these cases.  Only a code longer than the table's prefix branches.
  */
+/* per block of an MCU: shared-memory addresses of its DC / AC lookup tables (built once per CTA behind entb_setup) */
 template <typename SH>
-__device__ __forceinline__ void ss_skeleton_step(const SH &sh, uint32_t sh_addr, SsReader &r, uint32_t &bp, int &k, int &b, uint32_t &nb,
-																 int nblk_mcu)
+__device__ __forceinline__ void ss_build_tabs(const SH &sh, uint2 *s_tabs, int tid)
 {
-	const uint32_t ent = sh.blk[b];
+	if (tid < sh.nblk)
+	{
+		const uint32_t ent = sh.blk[tid];
+		s_tabs[tid] = make_uint2((uint32_t)__cvta_generic_to_shared(sh.dc[(ent >> 12) & 3u].fast),
+										 (uint32_t)__cvta_generic_to_shared(sh.ac[(ent >> 16) & 3u].fast));
+	}
+	__syncthreads();
+}
+__device__ __forceinline__ uint2 ss_load_tabs(uint32_t tabs_addr, int b)
+{
+	uint2 t;
+	asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(t.x), "=r"(t.y) : "r"(tabs_addr + 8u * (uint32_t)b));
+	return t;
+}
+template <typename SH>
+__device__ __forceinline__ void ss_skeleton_step(const SH &sh, uint32_t tabs_addr, uint2 &tabs, SsReader &r, uint32_t &bp, int &k, int &b,
+																 uint32_t &nb, int nblk_mcu)
+{
 	const bool dc = k == 0;
 	const uint32_t top = __funnelshift_l(r.nxt, r.cur, bp);
-	const uint32_t tdc = (ent >> 12) & 3u, tac = (ent >> 16) & 3u;
-	const uint32_t tab = dc ? (uint32_t)offsetof(SH, dc) + tdc * (uint32_t)sizeof(EntbDc)
-									: (uint32_t)offsetof(SH, ac) + tac * (uint32_t)sizeof(EntbAc);
 	const uint32_t idx = dc ? top >> (32 - ENTB_DC_BITS) : top >> (32 - ENTB_AC_BITS);
-	uint32_t e = lds_u16(sh_addr + tab + (idx << 1));
+	uint32_t e = lds_u16((dc ? tabs.x : tabs.y) + (idx << 1));
 	uint32_t adv;
 	int kadv;
 	if (e == 0u)
 	{
+		const uint32_t ent = sh.blk[b];
+		const uint32_t tdc = (ent >> 12) & 3u, tac = (ent >> 16) & 3u;
 		const uint32_t t16 = top >> 16;
 		const uint32_t *limit = dc ? sh.dc[tdc].limit : sh.ac[tac].limit;
 		const int32_t *basep = dc ? sh.dc[tdc].base : sh.ac[tac].base;
@@ -323,8 +339,11 @@ __device__ __forceinline__ void ss_skeleton_step(const SH &sh, uint32_t sh_addr,
 	const bool done = k >= 64;
 	k = done ? 0 : k;
 	nb += done ? 1u : 0u;
-	const int b1 = b + 1 == nblk_mcu ? 0 : b + 1;
-	b = done ? b1 : b;
+	if (done)
+	{
+		b = b + 1 == nblk_mcu ? 0 : b + 1;
+		tabs = ss_load_tabs(tabs_addr, b); /* needed by the next block's first symbol only */
+	}
 }
 
 enum
@@ -355,6 +374,9 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 	const jcu_scan *sc = &scans[w.scan];
 	const jcu_image *im = &images[sc->image];
 	entb_setup(sh, sc, im, huff, tid, SS_THREADS);
+	__shared__ uint2 s_tabs[MODE == SS_GUESS ? ENTB_MAX_MCU_BLOCKS : 1];
+	if (MODE == SS_GUESS)
+		ss_build_tabs(sh, s_tabs, tid);
 	/* WRITE: per block of an MCU, what a thread needs when it starts that block -- the block's address is
 	   coef + base + ux * sx + uy * sy (elements), the shared-memory addresses of its tables */
 	__shared__ SsBlockInfo s_bi[MODE == SS_WRITE ? ENTB_MAX_MCU_BLOCKS : 1];
@@ -450,9 +472,10 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 	bool failed = false, in_slot_at_exit = false;
 	if (MODE == SS_GUESS)
 	{
-		const uint32_t sh_addr = (uint32_t)__cvta_generic_to_shared(&sh);
+		const uint32_t tabs_addr = (uint32_t)__cvta_generic_to_shared(s_tabs);
+		uint2 tabs = ss_load_tabs(tabs_addr, b);
 		while (bp < limit)
-			ss_skeleton_step(sh, sh_addr, rd, bp, k, b, nb, nblk_mcu);
+			ss_skeleton_step(sh, tabs_addr, tabs, rd, bp, k, b, nb, nblk_mcu);
 	}
 	else
 	{
@@ -631,7 +654,7 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 #define SS_INNER 16 /* measured on 256 x 1080p 4:4:4: 8 -> 6 rounds 12.06 ms, 16 -> 4 rounds 11.92 ms, 32 -> 3 rounds 11.88 ms */
 #endif
 template <typename SH>
-__device__ __forceinline__ bool ss_refine_item(SH &sh, SsState *s_exit, const SsWork w, const jcu_scan *__restrict__ scans,
+__device__ __forceinline__ bool ss_refine_item(SH &sh, uint2 *s_tabs, SsState *s_exit, const SsWork w, const jcu_scan *__restrict__ scans,
 															  const jcu_image *__restrict__ images, const uint32_t *__restrict__ seg_start,
 															  const jcu_huff_spec *__restrict__ huff, const uint8_t *__restrict__ uslab,
 															  const uint32_t *__restrict__ useg_len, const SsBuffers &sb, int parity, int32_t *changed_flag,
@@ -640,7 +663,7 @@ __device__ __forceinline__ bool ss_refine_item(SH &sh, SsState *s_exit, const Ss
 	const int tid = threadIdx.x;
 	const jcu_scan *sc = &scans[w.scan];
 	const jcu_image *im = &images[sc->image];
-	const uint32_t sh_addr = (uint32_t)__cvta_generic_to_shared(&sh);
+	const uint32_t tabs_addr = (uint32_t)__cvta_generic_to_shared(s_tabs);
 	const uint32_t i = w.first + (uint32_t)tid, gi = w.scan_base + i;
 	const uint32_t ul = useg_len[sc->seg_first];
 	const uint32_t exact = (ul & ~15u) - (ul & 15u);
@@ -671,7 +694,10 @@ __device__ __forceinline__ bool ss_refine_item(SH &sh, SsState *s_exit, const Ss
 		return false;
 	}
 	if (rebuild) /* consecutive work items of a CTA often belong to one scan: its tables are built once */
+	{
 		entb_setup(sh, sc, im, huff, tid, SS_THREADS);
+		ss_build_tabs(sh, s_tabs, tid);
+	}
 	const int nblk_mcu = sh.nblk;
 	const SsState first = mine;
 	for (int it = 0; it < SS_INNER; ++it)
@@ -690,8 +716,9 @@ __device__ __forceinline__ bool ss_refine_item(SH &sh, SsState *s_exit, const Ss
 					int k = (int)(en.aux & 255u), b = (int)((en.aux >> 8) & 0xfffu);
 					uint32_t nb = 0;
 					ssr_prime(rd, bp);
+					uint2 tabs = ss_load_tabs(tabs_addr, b);
 					while (bp < limit)
-						ss_skeleton_step(sh, sh_addr, rd, bp, k, b, nb, nblk_mcu);
+						ss_skeleton_step(sh, tabs_addr, tabs, rd, bp, k, b, nb, nblk_mcu);
 					ex.bp = bp;
 					ex.aux = (uint32_t)k | ((uint32_t)b << 8);
 					sb.nblk[gi] = nb;
@@ -756,6 +783,7 @@ k_ss_refine_loop(const SsWork *__restrict__ work, unsigned nwork, const jcu_scan
 					  const uint32_t *__restrict__ useg_len, SsBuffers sb, unsigned max_rounds)
 {
 	__shared__ SH sh;
+	__shared__ uint2 s_tabs[ENTB_MAX_MCU_BLOCKS];
 	__shared__ SsState s_exit[SS_THREADS];
 	__shared__ unsigned s_ticket;
 	int parity = 0, have_scan = -1;
@@ -780,7 +808,7 @@ k_ss_refine_loop(const SsWork *__restrict__ work, unsigned nwork, const jcu_scan
 			if (it >= nwork)
 				break;
 			const SsWork w = work[it];
-			if (ss_refine_item(sh, s_exit, w, scans, images, seg_start, huff, uslab, useg_len, sb, parity, flag, w.scan != have_scan))
+			if (ss_refine_item(sh, s_tabs, s_exit, w, scans, images, seg_start, huff, uslab, useg_len, sb, parity, flag, w.scan != have_scan))
 				have_scan = w.scan;
 		}
 		parity ^= 1;

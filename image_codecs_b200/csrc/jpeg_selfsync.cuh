@@ -121,26 +121,79 @@ __device__ __forceinline__ uint4 ssu_load16(const uint8_t *__restrict__ base, ui
 	return __ldg(reinterpret_cast<const uint4 *>(base + p0));
 }
 
+/* Output side of the write pass: surviving bytes are collected big-endian in a 64-bit accumulator and leave as whole
+   32-bit words (byte j of the stream sits at j ^ 3, i.e. a word is stored as its big-endian value) -- into a
+   shared-memory image of the CTA's part of the output, which is contiguous (chunk i + 1 continues where chunk i
+   stopped) and goes to global memory as coalesced lines afterwards; per-thread global stores, 256 bytes apart from
+   lane to lane, left the kernel at 28 % issue.  The first word of a chunk may have been begun by the previous chunk
+   and the last one may be finished by the next: those bytes go one by one. */
+struct SsuOut
+{
+	uint32_t sm;	/* shared-memory address of the word with index jw_base */
+	uint32_t jw_base;
+	uint64_t acc;	/* pending bytes, first one in the top byte */
+	uint32_t nacc; /* 0..3 pending (at the start: bytes of the first word that belong to the previous chunk) */
+	uint32_t jw;	/* index of the word being filled */
+	uint32_t h0;	/* > 0 until the first word has left: its bytes below h0 are not ours */
+};
+__device__ __forceinline__ void ssu_sts8(const SsuOut &o, uint32_t jbyte, uint32_t v)
+{
+	asm volatile("st.shared.u8 [%0], %1;" ::"r"(o.sm + ((jbyte ^ 3u) - 4u * o.jw_base)), "r"(v) : "memory");
+}
+__device__ __forceinline__ void ssu_put(SsuOut &o, uint32_t x_top, uint32_t k) /* k = 1..4 bytes, left-aligned in x_top */
+{
+	o.acc |= (uint64_t)x_top << (32u - 8u * o.nacc);
+	o.nacc += k;
+	if (o.nacc >= 4u)
+	{
+		const uint32_t word = (uint32_t)(o.acc >> 32);
+		if (o.h0)
+		{
+			for (uint32_t b = o.h0; b < 4u; ++b)
+				ssu_sts8(o, 4u * o.jw + b, (word >> (24u - 8u * b)) & 255u);
+			o.h0 = 0u;
+		}
+		else
+			asm volatile("st.shared.u32 [%0], %1;" ::"r"(o.sm + 4u * (o.jw - o.jw_base)), "r"(word) : "memory");
+		++o.jw;
+		o.acc <<= 32;
+		o.nacc -= 4u;
+	}
+}
+
 template <bool WRITE>
 __global__ void __launch_bounds__(SS_THREADS)
 k_ss_unstuff(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans, const jcu_image *__restrict__ images,
 				 const uint32_t *__restrict__ seg_start, const uint8_t *__restrict__ bitstream, uint8_t *__restrict__ uslab,
 				 uint32_t *__restrict__ useg_len, SsBuffers sb)
 {
+	/* WRITE: the CTA's part of the output (at most SS_THREADS x 256 bytes + the word it shares with its predecessor) */
+	__shared__ uint32_t s_out[WRITE ? SS_THREADS * (SS_SUB_BYTES / 4) + 4 : 1];
+	__shared__ uint32_t s_jend;
 	const SsWork w = work[blockIdx.x];
-	if (threadIdx.x >= w.count)
+	const bool has_work = threadIdx.x < w.count;
+	if (!WRITE && !has_work)
 		return;
 	const jcu_scan *sc = &scans[w.scan];
 	const jcu_image *im = &images[sc->image];
-	const uint32_t i = w.first + threadIdx.x, gi = w.scan_base + i;
+	const uint32_t i = w.first + (has_work ? threadIdx.x : 0u), gi = w.scan_base + i;
 	const uint8_t *__restrict__ base = bitstream + im->data_off; /* 16-byte aligned */
 	const uint32_t scan_start = seg_start[sc->seg_first], end = sc->data_end;
 	/* chunks are cut on 256-byte boundaries of the FILE (the first one is shorter), so every chunk is 16 aligned loads */
 	const uint32_t a0 = scan_start & ~(SS_SUB_BYTES - 1u);
-	const uint32_t lo = max(scan_start, min(end, a0 + i * SS_SUB_BYTES)), hi = min(end, a0 + (i + 1u) * SS_SUB_BYTES);
-	uint8_t *dst = WRITE ? uslab + entb_useg_off(im->data_off, scan_start, (uint32_t)sc->seg_first) : nullptr;
-	uint32_t j = WRITE ? sb.first_blk[gi] : 0u;
-	uint32_t acc = 0u, nacc = 0u; /* WRITE: bytes collected for the next big-endian word (valid once j is word aligned) */
+	const uint32_t lo = max(scan_start, min(end, a0 + i * SS_SUB_BYTES));
+	const uint32_t hi = has_work ? min(end, a0 + (i + 1u) * SS_SUB_BYTES) : lo; /* threads without a chunk only help to copy */
+	const uint32_t j0 = WRITE ? sb.first_blk[gi] : 0u;
+	const uint32_t j_cta = WRITE ? sb.first_blk[w.scan_base + w.first] : 0u; /* first output byte of this CTA */
+	uint32_t j = j0; /* output bytes so far (count pass: survivors of this chunk) */
+	uint8_t *const dst = WRITE ? uslab + entb_useg_off(im->data_off, scan_start, (uint32_t)sc->seg_first) : nullptr;
+	SsuOut o;
+	o.sm = (uint32_t)__cvta_generic_to_shared(s_out);
+	o.jw_base = j_cta >> 2;
+	o.acc = 0ull;
+	o.nacc = j0 & 3u;
+	o.jw = j0 >> 2;
+	o.h0 = o.nacc;
 	if (lo < hi)
 	{
 		uint32_t prev = lo > scan_start ? (uint32_t)__ldg(base + lo - 1u) : 0u;
@@ -151,53 +204,91 @@ k_ss_unstuff(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans
 			const uint32_t after = p0 + 16u < end ? (uint32_t)__ldg(base + p0 + 16u) : 0u;
 			const uint32_t ws[5] = {v.x, v.y, v.z, v.w, after};
 #pragma unroll
-			for (int q = 0; q < 16; ++q)
+			for (int q4 = 0; q4 < 4; ++q4)
 			{
-				const uint32_t p = p0 + (uint32_t)q;
-				const uint32_t cur = (ws[q >> 2] >> (8 * (q & 3))) & 255u;
-				uint32_t nxt = (ws[(q + 1) >> 2] >> (8 * ((q + 1) & 3))) & 255u;
-				if (p + 1u >= end)
-					nxt = 0u;
-				if (p >= lo && p < hi)
+				const uint32_t wp = p0 + 4u * (uint32_t)q4, wd = ws[q4];
+				if (wp >= lo && wp + 4u <= hi)
 				{
-					const bool drop = (cur == 0u && prev == 0xffu) || (cur == 0xffu && nxt == 0xffu);
-					if (!drop)
+					/* a whole word of this chunk: per-byte flags in bit 7 of each byte */
+					const uint32_t ffm = ((wd & 0x7f7f7f7fu) + 0x01010101u) & wd & 0x80808080u;			/* byte == 0xFF */
+					const uint32_t zm = ~(((wd & 0x7f7f7f7fu) + 0x7f7f7f7fu) | wd) & 0x80808080u;			/* byte == 0x00 */
+					const uint32_t nb = wp + 4u >= end ? 0u : (ws[q4 + 1] & 255u);
+					const uint32_t prev_ff = (ffm << 8) | (prev == 0xffu ? 0x80u : 0u);
+					const uint32_t next_ff = (ffm >> 8) | (nb == 0xffu ? 0x80000000u : 0u);
+					const uint32_t drop = (zm & prev_ff) | (ffm & next_ff);
+					if (drop == 0u)
 					{
 						if (WRITE)
-						{
-							if ((j & 3u) || nacc) /* inside a word: collect; a word that starts before this chunk's bytes is byte-stored */
-							{
-								if (nacc == 0u) /* leading bytes of a word another chunk began */
-									dst[j ^ 3u] = (uint8_t)cur;
-								else
-								{
-									acc = (acc << 8) | cur;
-									if (++nacc == 4u)
-									{
-										*reinterpret_cast<uint32_t *>(dst + (j & ~3u)) = acc;
-										nacc = 0u;
-									}
-								}
-							}
-							else
-							{
-								acc = cur;
-								nacc = 1u;
-							}
-						}
-						++j;
+							ssu_put(o, __byte_perm(wd, 0, 0x0123), 4u);
+						j += 4u;
 					}
-					prev = cur;
+					else
+					{
+#pragma unroll
+						for (int q = 0; q < 4; ++q)
+							if (!((drop >> (8 * q + 7)) & 1u))
+							{
+								if (WRITE)
+									ssu_put(o, ((wd >> (8 * q)) & 255u) << 24, 1u);
+								++j;
+							}
+					}
+					prev = wd >> 24;
+				}
+				else
+				{
+					/* a word that straddles the first or the last byte of the scan: byte by byte */
+#pragma unroll
+					for (int q = 0; q < 4; ++q)
+					{
+						const uint32_t p = wp + (uint32_t)q;
+						const uint32_t cur = (wd >> (8 * q)) & 255u;
+						uint32_t nxt = q < 3 ? (wd >> (8 * (q + 1))) & 255u : ws[q4 + 1] & 255u;
+						if (p + 1u >= end)
+							nxt = 0u;
+						if (p >= lo && p < hi)
+						{
+							const bool dropped = (cur == 0u && prev == 0xffu) || (cur == 0xffu && nxt == 0xffu);
+							if (!dropped)
+							{
+								if (WRITE)
+									ssu_put(o, cur << 24, 1u);
+								++j;
+							}
+							prev = cur;
+						}
+					}
 				}
 			}
 		}
 	}
 	if (!WRITE)
 		sb.nblk[gi] = j;
-	/* trailing bytes of a word the next chunk completes */
-	for (uint32_t q = 0; WRITE && q < nacc; ++q)
-		dst[(j - nacc + q) ^ 3u] = (uint8_t)(acc >> (8 * (nacc - 1u - q)));
-	if (WRITE && hi == end && (lo < end || i == 0))
+	/* bytes of a last word the next chunk completes (and, if no word left at all, not the ones below h0) */
+	for (uint32_t b = o.h0; WRITE && b < o.nacc; ++b)
+		ssu_sts8(o, 4u * o.jw + b, (uint32_t)(o.acc >> (56u - 8u * b)) & 255u);
+	if (WRITE && threadIdx.x + 1u == w.count)
+		s_jend = j; /* chunks are in stream order: the last one ends the CTA's output */
+	if (WRITE)
+		__syncthreads();
+	if (WRITE)
+	{
+		/* shared -> global: whole words as coalesced lines; the bytes of a first / last word that another CTA shares, one by one */
+		const uint32_t j_end = s_jend;
+		const uint32_t head_end = min(j_end, (j_cta + 3u) & ~3u), tail_begin = max(head_end, j_end & ~3u);
+		const uint8_t *sb8 = reinterpret_cast<const uint8_t *>(s_out);
+		if (threadIdx.x == 0)
+			for (uint32_t q = j_cta; q < head_end && (j_cta & 3u); ++q)
+				dst[q ^ 3u] = sb8[(q ^ 3u) - 4u * o.jw_base];
+		if (threadIdx.x == 32u % SS_THREADS)
+			for (uint32_t q = tail_begin; q < j_end; ++q)
+				dst[q ^ 3u] = sb8[(q ^ 3u) - 4u * o.jw_base];
+		const uint32_t w0 = ((j_cta & 3u) ? head_end : j_cta) >> 2, w1 = tail_begin >> 2;
+		uint32_t *dst32 = reinterpret_cast<uint32_t *>(dst);
+		for (uint32_t q = w0 + threadIdx.x; q < w1; q += SS_THREADS)
+			dst32[q] = s_out[q - o.jw_base];
+	}
+	if (WRITE && has_work && hi == end && (lo < end || i == 0))
 	{
 		/* the chunk that reaches the end of the scan: pad to 16 bytes, add one all-zero unit, publish the length */
 		const uint32_t exact = j, padded = (exact + 15u) & ~15u;

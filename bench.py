@@ -189,6 +189,41 @@ def cpu_reference_run(streams, nthreads, target_s, req_comp=3):
     return mps, kind, desc
 
 
+_ZIGZAG = [0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7, 14, 21, 28, 35,
+           42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63]
+
+
+def huffman_symbols_per_bit(streams, max_streams=8):
+    """SURVEY 8(d) also asks for symbols/s of the entropy stage.  For baseline files the number of Huffman symbols
+    follows from the coefficients (stbi__jpeg_decode_block, jpeg.c:308-370): per block one DC symbol, one per non-zero
+    AC coefficient, one ZRL per 16 zeros inside a run, and an EOB unless position 63 is non-zero.  Counted with the
+    oracle's coefficient capture (checker use, outside every timed region) on a sample of the distinct streams;
+    returns (symbols per entropy-coded bit, description)."""
+    from oracle import oracle_lib as ol
+    import image_codecs_b200 as ic
+
+    o = ol.load()
+    zz = np.array(_ZIGZAG)
+    k = np.arange(64)
+    syms = bits = 0
+    n = 0
+    for st in streams[:max_streams]:
+        cap = o.decode_capture(st, 3)
+        info = ic.inspect(st, 3)
+        if cap is None or not info or info.get("progressive"):
+            return None, "baseline files only"
+        for coef in cap[1]:
+            a = coef.reshape(-1, 64)[:, zz] != 0
+            a[:, 0] = True  # the DC position anchors the first run
+            last = np.maximum.accumulate(np.where(a, k, 0), axis=1)  # index of the last non-zero at or before k
+            run = k[1:] - last[:, :-1] - 1  # zeros in front of position k (k = 1..63)
+            ac = a[:, 1:]
+            syms += a.shape[0] + int(ac.sum()) + int((run // 16)[ac].sum()) + int((last[:, 63] < 63).sum())
+        bits += 8 * info["entropy_bytes"]
+        n += 1
+    return syms / bits, f"{n} of the distinct streams, symbols counted from the oracle's coefficients (MCU-padded blocks)"
+
+
 def compare_with_oracle(stream, got, tag):
     """Checker use of the oracle (never timed here): abort the bench line when a decoded image differs."""
     from oracle import oracle_lib as ol
@@ -477,6 +512,12 @@ def main():
     ent_step_ms = ent_ms / args.steps
     sms = torch.cuda.get_device_properties(local_rank).multi_processor_count
     bits_per_s_sm = tm["entropy_bits"] * reps / (ent_step_ms / 1e3) / sms if ent_step_ms > 0 else 0.0
+    sym_per_bit, sym_desc = (None, "skipped (--no-cpu)")
+    if rank == 0 and not args.no_cpu and not args.progressive:
+        try:
+            sym_per_bit, sym_desc = huffman_symbols_per_bit(distinct)
+        except Exception as e:  # the symbol rate is an extra, never a reason to lose the line
+            sym_desc = f"unavailable: {e}"
     dec.close()
 
     # ---------------- e2e: host buffers in, host buffers out, copies inside the timed region
@@ -570,7 +611,8 @@ def main():
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": kgray if args.gray else (k444 + " + " + kgray) if args.mix_gray
                          else ("k_fused420_strip<3,%s>" % deq) if args.subsampling == "420"
-                         else k444 if args.subsampling == "444" else "k_generic_idct + k_generic_color", "achieved": achieved, "peak": peak,
+                         else k444 if args.subsampling == "444" else ("k_fused422_strip<3,%s>" % deq) if args.subsampling == "422"
+                         else "k_generic_idct + k_generic_color", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak if peak else None, "traffic": traffic,
                          "traffic_source": "ncu dram__bytes_read+write per image (profiles/traffic.json) x images",
                          "peak_source": peak_src, "algorithmic_bytes_per_launch": algo_bytes,
@@ -578,6 +620,8 @@ def main():
             "cpu_baseline": cpu,
             "stages": {"entropy_ms": ent_step_ms, "idct_color_ms": idct_ms / args.steps,
                        "entropy_bits_per_s_per_sm": bits_per_s_sm, "entropy_gbit_per_s": bits_per_s_sm * sms / 1e9,
+                       "entropy_gsymbols_per_s": (bits_per_s_sm * sms * sym_per_bit / 1e9) if sym_per_bit else None,
+                       "entropy_symbols_sample": sym_desc,
                        "selfsync_scans": tm.get("selfsync_scans"), "selfsync_rounds": tm.get("selfsync_rounds"),
                        "wall_ms_per_step": wall_ms / args.steps},
         }

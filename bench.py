@@ -533,6 +533,8 @@ def main():
         e2e_chunk = int(min(1024, max(64, 2 ** round(np.log2(3.2e9 / per)))))
         host_threads = max(2, min(ncores // world, len(os.sched_getaffinity(0))))  # ranks share the host cores
 
+        h2d_ms = [None]
+
         def run_e2e(pinned, steps):
             if pinned:
                 buf_in, buf_out = PinnedBuffer(in_bytes + 64), PinnedBuffer(per * n_call)
@@ -565,6 +567,27 @@ def main():
             got = np.array(a_out[:per]).reshape(args.height, args.width, 3)
             compare_with_oracle(e_streams[0], got, "e2e image 0 (%s buffers)" % ("pinned" if pinned else "pageable"))
             e_dec.close()
+            if pinned and n_call * per * 2.1 < 60e9:
+                # SURVEY 8(d) protocol point (b): parse + H2D + kernels, pixels stay in HBM (the staged form of the same API)
+                s_dec = ic.BatchDecoder(device=local_rank, profile=False, host_threads=host_threads)
+                xs, ys, cs = ((C.c_int * n_call)() for _ in range(3))
+                L = ic.api.lib()
+
+                def staged():
+                    if L.stbi_jpeg_batch_prepare(s_dec._h, bufs, lens, n_call, 3, xs, ys, cs, st) != n_call:
+                        raise SystemExit("bench.py: staged decode failed")
+                    s_dec.count = n_call
+                    s_dec.run()
+                    s_dec.sync()
+
+                staged()
+                barrier()
+                t0 = time.perf_counter()
+                for _ in range(max(1, steps) * calls):
+                    staged()
+                barrier()
+                h2d_ms[0] = max_over_ranks(1e3 * (time.perf_counter() - t0)) / max(1, steps)
+                s_dec.close()
             if pinned:
                 buf_in.free()
                 buf_out.free()
@@ -581,6 +604,9 @@ def main():
         e2e["d2h_ceiling_gbs_all_ranks"] = ceil_gbs
         e2e["d2h_achieved_gbs_all_ranks"] = e_px * 3 / 1e9 / (e_ms / 1e3)
         e2e["frac_of_d2h_ceiling"] = e2e["d2h_achieved_gbs_all_ranks"] / ceil_gbs if ceil_gbs else None
+        if h2d_ms[0]:
+            e2e["h2d_decode"] = {"value": e_px / 1e6 / (h2d_ms[0] / 1e3), "unit": UNIT, "ms_per_step": h2d_ms[0],
+                                 "what": "marker parse + H2D + kernels through the staged calls, pixels left in HBM"}
         if not args.no_pageable:
             p_ms = run_e2e(False, max(1, min(2, args.e2e_steps)))
             e2e["pageable"] = {"value": e_px / 1e6 / (p_ms / 1e3), "unit": UNIT, "ms_per_step": p_ms,

@@ -467,10 +467,12 @@ def main():
     t0 = time.perf_counter()
     dev_ms = ent_ms = idct_ms = 0.0
     launches = 0
+    per_launch_ms = []
     for _ in range(args.steps * reps):
         dec.run()
         dec.sync()
         tm = dec.timings()
+        per_launch_ms.append(tm["total_ms"])
         dev_ms += tm["total_ms"]
         ent_ms += tm["entropy_ms"]
         idct_ms += tm["idct_ms"]
@@ -649,7 +651,10 @@ def main():
                        "entropy_gsymbols_per_s": (bits_per_s_sm * sms * sym_per_bit / 1e9) if sym_per_bit else None,
                        "entropy_symbols_sample": sym_desc,
                        "selfsync_scans": tm.get("selfsync_scans"), "selfsync_rounds": tm.get("selfsync_rounds"),
-                       "wall_ms_per_step": wall_ms / args.steps},
+                       "wall_ms_per_step": wall_ms / args.steps,
+                       # best and median of the timed launches (device events around one whole batch / chunk)
+                       "device_ms_per_launch_best": min(per_launch_ms), "device_ms_per_launch_median": float(np.median(per_launch_ms)),
+                       "timed_launches": len(per_launch_ms)},
         }
         emit(line)
     if world > 1:

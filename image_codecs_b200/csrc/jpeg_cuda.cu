@@ -611,7 +611,8 @@ extern "C" int jcu_upload(jcu_ctx *c, const jcu_batch *b)
 	}
 	if (!c->ss_scan_h.empty())
 	{
-		c->need_clear = true; /* phase 4 writes single coefficients into zeroed blocks */
+		/* phase 4 writes single coefficients into the blocks that hold a subsequence boundary: k_ss_zero_shared clears
+		   exactly those (the whole slab is only cleared when the parser asks for it) */
 		/* Decoding subsequences: 256 unstuffed bytes when the batch fills the GPU with them; a small batch (the
 		   per-image stbi_load of ONE 512 x 512 file is 409 of them) takes shorter ones, down to 32 bytes -- every phase is
 		   one dependent chain per thread, so its latency is the subsequence length, and idle SMs cost nothing. */
@@ -1098,6 +1099,11 @@ extern "C" int jcu_run(jcu_ctx *c)
 		}
 		c->launches++;
 		k_ss_scan<<<ns, 256, 0, st>>>(dscans, sb.nblk, sb.first_blk);
+		if (!c->need_clear)
+		{
+			k_ss_zero_shared<<<ndw, SS_THREADS, 0, st>>>(dwk, (const jcu_scan *)c->scans.p, d_img, (int16_t *)c->coef.p, sb);
+			c->launches++;
+		}
 		if (c->ss_two) /* entry states: side sb.result[0] */
 			k_ss_decode<SS_WRITE, EntbShared2><<<ndw, SS_THREADS, 0, st>>>(SS_ARGS);
 		else

@@ -47,6 +47,41 @@ struct DevBuf
  * pipeline has three, the per-image pool up to sixteen), created on the first pageable download and kept for the
  * life of the process.
  */
+#if defined(__x86_64__) || defined(_M_X64)
+#include <emmintrin.h>
+/* pinned slot -> caller's pageable buffer with streaming stores: the destination lines are written whole, so fetching
+   them first (what a cached store does) only costs memory bandwidth the copier threads compete for */
+static void bounce_copy(void *dst, const void *src, size_t n)
+{
+	uint8_t *d = (uint8_t *)dst;
+	const uint8_t *s = (const uint8_t *)src;
+	const size_t head = (16u - ((uintptr_t)d & 15u)) & 15u;
+	if (n < 256 || head > n)
+	{
+		memcpy(d, s, n);
+		return;
+	}
+	memcpy(d, s, head);
+	d += head;
+	s += head;
+	n -= head;
+	const size_t blocks = n / 64;
+	for (size_t i = 0; i < blocks; ++i, d += 64, s += 64)
+	{
+		const __m128i a = _mm_loadu_si128((const __m128i *)s), b = _mm_loadu_si128((const __m128i *)(s + 16));
+		const __m128i c = _mm_loadu_si128((const __m128i *)(s + 32)), e = _mm_loadu_si128((const __m128i *)(s + 48));
+		_mm_stream_si128((__m128i *)d, a);
+		_mm_stream_si128((__m128i *)(d + 16), b);
+		_mm_stream_si128((__m128i *)(d + 32), c);
+		_mm_stream_si128((__m128i *)(d + 48), e);
+	}
+	_mm_sfence();
+	memcpy(d, s, n - blocks * 64);
+}
+#else
+static void bounce_copy(void *dst, const void *src, size_t n) { memcpy(dst, src, n); }
+#endif
+
 struct BounceOwner /* per context; both fields are guarded by the ring's mutex */
 {
 	int pending = 0;
@@ -96,7 +131,7 @@ struct Bounce
 			}
 			const cudaError_t e = j.bytes ? cudaEventSynchronize(ev[j.slot]) : cudaSuccess;
 			if (e == cudaSuccess && j.bytes)
-				memcpy(j.dst, buf[j.slot], j.bytes);
+				bounce_copy(j.dst, buf[j.slot], j.bytes);
 			{
 				std::lock_guard<std::mutex> lk(m);
 				if (e != cudaSuccess && j.owner->failed == cudaSuccess)

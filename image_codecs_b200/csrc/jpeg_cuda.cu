@@ -1243,9 +1243,11 @@ extern "C" int jcu_download(jcu_ctx *c, size_t off, size_t bytes, void *dst)
 			if (!c->bounce)
 				return set_err(c, e, "jcu_download: pinned staging ring");
 		}
-		for (size_t done = 0; done < bytes; done += Bounce::SLOT_BYTES)
+		/* a single image (a few MB) is cut into about eight pieces so that as many copier threads share it */
+		const size_t piece = std::min(Bounce::SLOT_BYTES, std::max((size_t)256 << 10, ((bytes / 8 + 4095) & ~(size_t)4095)));
+		for (size_t done = 0; done < bytes; done += piece)
 		{
-			const size_t n = std::min(Bounce::SLOT_BYTES, bytes - done);
+			const size_t n = std::min(piece, bytes - done);
 			const int slot = c->bounce->take_slot();
 			cudaError_t e = cudaMemcpyAsync(c->bounce->buf[slot], (const uint8_t *)c->out.p + off + done, n, cudaMemcpyDeviceToHost, c->dl_use);
 			if (e == cudaSuccess)

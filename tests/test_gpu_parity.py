@@ -189,6 +189,56 @@ def test_full_size_1080p_420_rst16(oracle, decoder):
         _check(oracle, got, data, 3, f"1080p #{i}")
 
 
+def test_full_batch_config_c2_every_image(oracle):
+    """BASELINE.json configs[1] at its FULL size: 1024 x 1920x1080 4:2:0 q90 restart-16 in one batched call (64 distinct
+    streams, cycled, as bench.py builds the batch).  Every one of the 1024 results -- 6.4 GB of pixels -- is compared
+    with the reference's decode of its stream, so a fault that only shows at a particular place of a large batch
+    (a CTA index, a chunk boundary of the pipeline, a slab offset beyond 4 GB) cannot hide behind a sample."""
+    import ctypes as C
+    from tools import testenc as te
+
+    distinct = te.encode_many(64, 1920, 1080, kind=-1, base_seed=1000, quality=90, subsampling="420", restart_interval=16)
+    wants = [oracle.load_from_memory(s_, 3)[0] for s_ in distinct]
+    n, per = 1024, 1920 * 1080 * 3
+    streams = [distinct[i % 64] for i in range(n)]
+    out = np.empty(n * per, dtype=np.uint8)
+    bufs, lens, keep = ic.BatchDecoder._inputs(streams)
+    outs = (C.c_void_p * n)(*[out.ctypes.data + i * per for i in range(n)])
+    caps = (C.c_size_t * n)(*([per] * n))
+    st = (C.c_int * n)()
+    d = ic.BatchDecoder(device=0, profile=False)
+    rc = d.decode_into(bufs, lens, n, 3, outs, caps, None, None, None, st)
+    d.close()
+    assert rc == n and all(st[i] == 1 for i in range(n)), rc
+    bad = [i for i in range(n) if not np.array_equal(out[i * per:(i + 1) * per].reshape(1080, 1920, 3), wants[i % 64])]
+    assert not bad, bad[:8]
+
+
+@pytest.mark.parametrize("config", ["c3", "c4"])
+def test_full_batch_configs_c3_c4_every_image(oracle, config):
+    """BASELINE.json configs[2] and [3] at their full batch size (256 x 1080p): c3 = 4:4:4 colour and 8-bit grey
+    alternating, no restart markers (self-synchronising decoder at its large-batch subsequence length); c4 =
+    progressive 4:2:0 without restart markers (all scans of an image pipelined in one launch).  Every image compared
+    with the reference's decode of its stream."""
+    from tools import testenc as te
+
+    if config == "c3":
+        col = te.encode_many(8, 1920, 1080, kind=-1, base_seed=1000, quality=90, subsampling="444")
+        gry = te.encode_many(8, 1920, 1080, kind=-1, base_seed=1500, quality=90, colorspace=te.CS_GRAY)
+        distinct = [x for pair in zip(col, gry) for x in pair]
+    else:
+        distinct = te.encode_many(16, 1920, 1080, kind=-1, base_seed=1000, quality=90, subsampling="420", progressive=1)
+    wants = [oracle.load_from_memory(s_, 3)[0] for s_ in distinct]
+    d = ic.BatchDecoder(device=0, profile=False)
+    outs = d.decode([distinct[i % 16] for i in range(256)], 3)
+    tm = d.timings()
+    d.close()
+    bad = [i for i, got in enumerate(outs) if got is None or not np.array_equal(got, wants[i % 16])]
+    assert not bad, bad[:8]
+    if config == "c3":
+        assert tm["selfsync_scans"] == 256, tm
+
+
 def test_full_size_2160p_config_c5(oracle, decoder):
     """BASELINE.json configs[4] geometry: 3840x2160 4:2:0 q90 (12 strips x 135 MCU rows, 194 400 blocks per image,
     reference driver jpeg.c:2224-2440) with restart interval 16 AND without restart markers (self-synchronising

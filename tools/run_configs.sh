@@ -10,6 +10,7 @@ run --config c3                                                              # C
 run --config c3 --mix-gray 0 --subsampling 444                               # C3, colour half alone
 run --config c3 --mix-gray 0 --gray 1                                        # C3, grayscale half alone
 run --config c3 --mix-gray 0 --subsampling 444 --restart 16                  # 4:4:4 with restart markers (for comparison)
+run --config c3 --mix-gray 0 --subsampling 420                               # 4:2:0 without restart markers: the commonest file type (self-sync + 4:2:0 strip kernel)
 run --config c4                                                              # C4: progressive 1080p without restart markers
 run --config c4 --restart 16                                                 # C4 with restart markers
 run --config c2 --images 256 --subsampling 422 --steps 10                    # N2: 4:2:2 (what most cameras emit)

@@ -1,3 +1,4 @@
+# Per-kernel device times of ONE per-image load (config C1): latency probe, then an ncu launch list of the same command.
 python tools/latency_probe.py 2>&1 | cut -c1-330
 ncu --metrics gpu__time_duration.sum --clock-control none -s 40 -c 14 --csv --log-file gpurun_out/c1_launches.csv python tools/latency_probe.py > /dev/null 2>&1
 python - <<'PY'

@@ -12,6 +12,8 @@ run --config c3 --mix-gray 0 --gray 1                                        # C
 run --config c3 --mix-gray 0 --subsampling 444 --restart 16                  # 4:4:4 with restart markers (for comparison)
 run --config c3 --mix-gray 0 --subsampling 420                               # 4:2:0 without restart markers: the commonest file type (self-sync + 4:2:0 strip kernel)
 run --config c4                                                              # C4: progressive 1080p without restart markers
+run --config c4 --images 1024 --steps 2                                      # C4 at the batch size of C2
+run --config c4 --images 4096 --steps 2 --no-e2e                             # C4: throughput regime (every scheduler holds several scans)
 run --config c4 --restart 16                                                 # C4 with restart markers
 run --config c2 --images 256 --subsampling 422 --steps 10                    # N2: 4:2:2 (what most cameras emit)
 run --config c5 --total-images 1024 --steps 3                                # C5 shape on one GPU: 1024 x 2160p in chunks of 256

@@ -154,6 +154,7 @@ static stbi_jpeg_batch *batch_create_with_pool(const stbi_jpeg_batch_params *par
 	o.rows_per_band = b->params.rows_per_band;
 	o.guard = b->params.debug_guards;
 	o.selfsync_sub_bytes = b->params.selfsync_sub_bytes;
+	o.host_threads = b->nthreads;
 	rc = jcu_ctx_create_opts(&o, &b->ctx);
 	if (rc != 0)
 	{

@@ -95,10 +95,13 @@ struct Bounce
 	};
 	/* copier threads: one moves ~6 GB/s; measured on a 16-core host, 1024 x 1080p: 3 / 6 / 10 / 16 threads ->
 	   6.4 / 9.1 / 10.5 / 11.1 GMP/s (pinned buffers on the same box: 16.7) */
-	static int copier_threads()
+	static int copier_threads(int hint)
 	{
-		const unsigned hc = std::thread::hardware_concurrency();
-		return (int)std::min(12u, std::max(4u, hc / 2u + 2u));
+		/* `hint` = host threads the first context that needs the ring was given: eight ranks on one box each get an
+		   eighth of the cores for their parser pool, and the copiers must shrink with it (measured at 8 GPUs: ten copier
+		   threads per rank on a 32-thread host lost 9 % against the driver's own staged copy) */
+		const unsigned hc = hint > 0 ? (unsigned)hint : std::thread::hardware_concurrency();
+		return (int)std::min(12u, std::max(2u, hc / 2u + 2u));
 	}
 	static constexpr size_t SLOT_BYTES = (size_t)2 << 20;
 	struct Job
@@ -143,7 +146,7 @@ struct Bounce
 			cv_idle.notify_all();
 		}
 	}
-	cudaError_t start(int dev)
+	cudaError_t start(int dev, int threads_hint)
 	{
 		device = dev;
 		for (int i = 0; i < NSLOT; ++i)
@@ -155,7 +158,7 @@ struct Bounce
 				return e;
 			free_slots.push_back(i);
 		}
-		const int nt = copier_threads();
+		const int nt = copier_threads(threads_hint);
 		for (int t = 0; t < nt; ++t)
 			threads.emplace_back([this] { worker(); }).detach(); /* they live as long as the process */
 		return cudaSuccess;
@@ -190,7 +193,7 @@ struct Bounce
 static Bounce *g_bounce[JCU_MAX_DEVICES];
 static std::mutex g_bounce_m;
 /* the device's ring (the device is current); nullptr + *err when the pinned slots cannot be had */
-static Bounce *bounce_for_device(int device, cudaError_t *err)
+static Bounce *bounce_for_device(int device, int threads_hint, cudaError_t *err)
 {
 	*err = cudaSuccess;
 	if (device < 0 || device >= JCU_MAX_DEVICES)
@@ -202,7 +205,7 @@ static Bounce *bounce_for_device(int device, cudaError_t *err)
 	if (!g_bounce[device])
 	{
 		Bounce *b = new Bounce();
-		*err = b->start(device);
+		*err = b->start(device, threads_hint);
 		if (*err != cudaSuccess)
 			return nullptr; /* a half-built ring is left behind rather than torn down under its threads: the error is sticky anyway */
 		g_bounce[device] = b;
@@ -220,6 +223,7 @@ struct jcu_ctx
 	bool guard = false;
 	int rows_per_band_forced = 0;
 	uint32_t ss_sub_forced = 0;
+	int host_threads_hint = 0;
 	cudaStream_t stream = nullptr;
 	/* downloads run on their own stream, behind an event of the compute stream */
 	cudaStream_t dl_own = nullptr, dl_use = nullptr;
@@ -372,6 +376,7 @@ extern "C" int jcu_ctx_create_opts(const jcu_ctx_options *o, jcu_ctx **out)
 	c->guard = o->guard != 0;
 	c->force_generic = o->force_generic != 0;
 	c->rows_per_band_forced = o->rows_per_band > 0 ? o->rows_per_band : 0;
+	c->host_threads_hint = o->host_threads > 0 ? o->host_threads : 0;
 	if (o->selfsync_sub_bytes == 32 || o->selfsync_sub_bytes == 64 || o->selfsync_sub_bytes == 128 || o->selfsync_sub_bytes == 256)
 		c->ss_sub_forced = (uint32_t)o->selfsync_sub_bytes;
 	e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
@@ -1239,7 +1244,7 @@ extern "C" int jcu_download(jcu_ctx *c, size_t off, size_t bytes, void *dst)
 		if (!c->bounce)
 		{
 			cudaError_t e = cudaSuccess;
-			c->bounce = bounce_for_device(c->device, &e);
+			c->bounce = bounce_for_device(c->device, c->host_threads_hint, &e);
 			if (!c->bounce)
 				return set_err(c, e, "jcu_download: pinned staging ring");
 		}

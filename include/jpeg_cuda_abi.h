@@ -160,7 +160,7 @@ typedef struct
 	int32_t rows_per_band; /* > 0 = MCU rows per band of the 4:2:0 strip kernel instead of the batch-size heuristic */
 	int32_t guard;			  /* 1 = every device buffer carries a canary behind its logical size (jcu_debug_guards_ok) */
 	int32_t selfsync_sub_bytes; /* 32 / 64 / 128 / 256 = bytes per subsequence of the self-synchronising decoder instead of the batch-size heuristic */
-	int32_t reserved[1];
+	int32_t host_threads; /* hint: host threads the caller gives this context (its parser pool); the copier threads of the pageable download ring are sized by it (0 = by the machine) */
 } jcu_ctx_options;
 JCU_API int jcu_ctx_create_opts(const jcu_ctx_options *o, jcu_ctx **out);
 JCU_API void jcu_ctx_destroy(jcu_ctx *c);

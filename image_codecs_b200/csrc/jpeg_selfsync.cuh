@@ -19,10 +19,12 @@
  *              one subsequence per round and, thanks to self-synchronisation, in practice converges in a few
  *              rounds; a thread whose entry state did not change skips the work.  Rounds stop when no exit
  *              state changed -- all inside ONE cooperative launch (grid barrier per round), no host round trip.
- *   3 scan     exclusive prefix sum of the number of blocks each subsequence completes.
+ *   3 scan     exclusive prefix sum of the number of blocks each subsequence completes; the one block per
+ *              subsequence boundary that two threads share is cleared (k_ss_zero_shared).
  *   4 write    every thread decodes its subsequence once more from its (now true) entry state and writes
- *              (short)(value * dequant) coefficients (jpeg.c:345,365) into the pre-zeroed slab; DC symbols are
- *              written as raw differences.
+ *              (short)(value * dequant) coefficients (jpeg.c:345,365): blocks it starts leave as whole 128-byte lines,
+ *              the shared ones coefficient by coefficient into the cleared block; DC symbols are written as raw
+ *              differences.
  *   5 dc       per component: prefix sum of the DC differences in decode order = the reference's running
  *              dc_pred (jpeg.c:323-325), stored as (short)(dc * dequant[0]).
  *
@@ -590,8 +592,8 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 			zq_addr = bi.zq;
 		}
 		/* A block this thread STARTS is assembled in its shared-memory slot and leaves as one 128-byte line when it is
-		   complete (whole sectors: no read-modify-write of the zeroed slab).  The block it enters in the middle of (the
-		   predecessor began it) and the one it leaves unfinished go coefficient by coefficient into the zeroed slab, as
+		   complete (whole sectors: no read-modify-write).  The block it enters in the middle of (the
+		   predecessor began it) and the one it leaves unfinished go coefficient by coefficient into a block k_ss_zero_shared cleared, as
 		   two threads share them. */
 		bool in_slot = k == 0;
 		const uint32_t lane = (uint32_t)tid & 31u;
@@ -691,7 +693,7 @@ k_ss_decode(const SsWork *__restrict__ work, const jcu_scan *__restrict__ scans,
 	if (MODE == SS_WRITE)
 	{
 		/* left in the middle of a block (the successor finishes it): if this thread started it, what was assembled so far
-		   goes into the zeroed slab coefficient by coefficient, like the parts two threads share */
+		   goes into the cleared block coefficient by coefficient, like the parts two threads share */
 		if (alive && k != 0 && in_slot_at_exit && g < total_blocks)
 		{
 			key = coef_key(blk);

@@ -174,7 +174,11 @@ JCU_API int jcu_reserve(jcu_ctx *c, size_t bitstream_bytes, size_t coef_elems, s
 JCU_API int jcu_upload(jcu_ctx *c, const jcu_batch *b);								  /* H2D, asynchronous on the ctx stream */
 JCU_API int jcu_run(jcu_ctx *c);															  /* entropy waves + output stage, asynchronous */
 JCU_API int jcu_sync(jcu_ctx *c);
-JCU_API int jcu_download(jcu_ctx *c, size_t off, size_t bytes, void *dst);	  /* async D2H on the context's download stream */
+/* Asynchronous D2H of out[off, off + bytes) on the context's download stream; complete after jcu_sync.  dst may be
+   page-locked (the copy engine writes it directly) or pageable: 1 MB and more into pageable memory goes through the
+   device's ring of pinned slots and copier threads (csrc/jpeg_cuda.cu, struct Bounce), which jcu_sync also drains.
+   No counterpart in the reference (its pixels are produced in host memory, jpeg.c:2293). */
+JCU_API int jcu_download(jcu_ctx *c, size_t off, size_t bytes, void *dst);
 JCU_API void jcu_share_download_stream(jcu_ctx *c, jcu_ctx *owner);				  /* queue c's downloads on owner's download stream (FIFO over a chunk pipeline) */
 /* per-image failure word: 0 = decoded; else JCU_ERR_CODE(word) says why (the earliest event in file order wins) */
 #define JCU_ERR_BAD_HUFFMAN 1u	 /* "bad huffman code", jpeg.c:317, 351, 446, 505, 549 */
